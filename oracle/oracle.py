@@ -1,0 +1,170 @@
+"""ctypes bindings for oracle/liboracle.so (C restatement, "port") and
+oracle/_ref/libvisnav_ref.so (the reference's own functions, "reference").
+
+TEST INFRASTRUCTURE ONLY -- see oracle/visnav_oracle.c.  Both libraries expose the
+same operations; `Oracle` hides the small signature differences so tests can run the
+same checks against either.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_u8p = C.POINTER(C.c_uint8)
+_f64p = C.POINTER(C.c_double)
+_f32p = C.POINTER(C.c_float)
+_u32p = C.POINTER(C.c_uint32)
+_i32p = C.POINTER(C.c_int32)
+
+
+def build(quiet=True):
+    """make -C oracle (liboracle.so always; _ref only where /root/reference exists)."""
+    subprocess.run(["make", "-C", _HERE], check=True,
+                   stdout=subprocess.DEVNULL if quiet else None)
+
+
+def _p(a, t):
+    return a.ctypes.data_as(t)
+
+
+def _img(img):
+    img = np.asarray(img)
+    assert img.dtype == np.uint8 and img.ndim == 2
+    if img.strides[1] != 1:
+        img = np.ascontiguousarray(img)
+    return img, img.shape[1], img.shape[0], img.strides[0]
+
+
+class Oracle:
+    """kind == "port": C restatement.  kind == "reference": reference's own code."""
+
+    def __init__(self, lib, kind):
+        self.lib, self.kind = lib, kind
+        pre = "vso_" if kind == "port" else "ref_"
+        self._pre = pre
+        f = getattr(lib, pre + "detect")
+        f.restype = C.c_int
+        f.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_int, _f64p, C.c_int]
+        f = getattr(lib, pre + "angles")
+        f.restype = None
+        f.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, _f64p, C.c_int, C.c_int, _f64p]
+        f = getattr(lib, pre + "describe")
+        f.restype = None
+        if kind == "port":
+            f.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, _f64p, _f64p, C.c_int, C.c_int, _u32p]
+        else:
+            f.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, _f64p, _f64p, C.c_int, _u32p]
+        f = getattr(lib, pre + "match")
+        f.restype = C.c_int
+        f.argtypes = [_u32p, C.c_int, _u32p, C.c_int, C.c_int, C.c_double, _i32p, C.c_int]
+        f = getattr(lib, pre + "detect_describe")
+        f.restype = C.c_int
+        if kind == "port":
+            f.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f64p, _f64p, _u32p, C.c_int]
+        else:
+            f.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f64p, _f64p, _u32p, C.c_int]
+        if kind == "port":
+            lib.vso_response.restype = C.c_int
+            lib.vso_response.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, _f32p]
+            lib.vso_gftt.restype = C.c_int
+            lib.vso_gftt.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, _f32p, C.c_int]
+            lib.vso_best2.restype = None
+            lib.vso_best2.argtypes = [_u32p, C.c_int, _u32p, C.c_int, _i32p]
+
+    # --- detection -------------------------------------------------------------------------
+    def response(self, img):
+        img, w, h, pitch = _img(img)
+        lam = np.empty((h, w), np.float32)
+        rc = self.lib.vso_response(_p(img, _u8p), w, h, pitch, _p(lam, _f32p))
+        assert rc == 0, rc
+        return lam
+
+    def gftt(self, img, max_corners, quality=0.01, min_distance=8.0):
+        img, w, h, pitch = _img(img)
+        cap = max_corners if max_corners > 0 else w * h
+        xy = np.empty((cap, 2), np.float32)
+        n = self.lib.vso_gftt(_p(img, _u8p), w, h, pitch, max_corners, quality, min_distance,
+                              _p(xy, _f32p), cap)
+        assert n >= 0, n
+        return xy[:n].copy()
+
+    def detect(self, img, num_features):
+        img, w, h, pitch = _img(img)
+        cap = num_features if num_features > 0 else w * h
+        xy = np.empty((cap, 2), np.float64)
+        n = getattr(self.lib, self._pre + "detect")(_p(img, _u8p), w, h, pitch, num_features,
+                                                    _p(xy, _f64p), cap)
+        assert 0 <= n <= cap, n
+        return xy[:n].copy()
+
+    # --- orientation / description -----------------------------------------------------------
+    def angles(self, img, xy, rotate=True):
+        img, w, h, pitch = _img(img)
+        xy = np.ascontiguousarray(xy, np.float64)
+        out = np.empty(len(xy), np.float64)
+        getattr(self.lib, self._pre + "angles")(_p(img, _u8p), w, h, pitch, _p(xy, _f64p), len(xy),
+                                                int(rotate), _p(out, _f64p))
+        return out
+
+    def describe(self, img, xy, angles, contract=True):
+        img, w, h, pitch = _img(img)
+        xy = np.ascontiguousarray(xy, np.float64)
+        angles = np.ascontiguousarray(angles, np.float64)
+        out = np.empty((len(xy), 8), np.uint32)
+        f = getattr(self.lib, self._pre + "describe")
+        if self.kind == "port":
+            f(_p(img, _u8p), w, h, pitch, _p(xy, _f64p), _p(angles, _f64p), len(xy), int(contract), _p(out, _u32p))
+        else:
+            f(_p(img, _u8p), w, h, pitch, _p(xy, _f64p), _p(angles, _f64p), len(xy), _p(out, _u32p))
+        return out
+
+    def detect_describe(self, img, num_features, rotate=True, contract=True):
+        img, w, h, pitch = _img(img)
+        cap = num_features if num_features > 0 else w * h
+        xy = np.empty((cap, 2), np.float64)
+        ang = np.empty(cap, np.float64)
+        desc = np.empty((cap, 8), np.uint32)
+        f = getattr(self.lib, self._pre + "detect_describe")
+        if self.kind == "port":
+            n = f(_p(img, _u8p), w, h, pitch, num_features, int(rotate), int(contract),
+                  _p(xy, _f64p), _p(ang, _f64p), _p(desc, _u32p), cap)
+        else:
+            n = f(_p(img, _u8p), w, h, pitch, num_features, int(rotate),
+                  _p(xy, _f64p), _p(ang, _f64p), _p(desc, _u32p), cap)
+        assert n >= 0, n
+        return xy[:n].copy(), ang[:n].copy(), desc[:n].copy()
+
+    # --- matching ----------------------------------------------------------------------------
+    def match(self, d1, d2, threshold=70, ratio=1.2):
+        d1 = np.ascontiguousarray(d1, np.uint32).reshape(-1, 8)
+        d2 = np.ascontiguousarray(d2, np.uint32).reshape(-1, 8)
+        cap = max(1, min(len(d1), len(d2)))
+        pairs = np.empty((cap, 2), np.int32)
+        n = getattr(self.lib, self._pre + "match")(_p(d1, _u32p), len(d1), _p(d2, _u32p), len(d2),
+                                                   int(threshold), float(ratio), _p(pairs, _i32p), cap)
+        assert 0 <= n <= cap, n
+        return pairs[:n].copy()
+
+    def best2(self, q, db):
+        q = np.ascontiguousarray(q, np.uint32).reshape(-1, 8)
+        db = np.ascontiguousarray(db, np.uint32).reshape(-1, 8)
+        out = np.empty((len(q), 3), np.int32)
+        self.lib.vso_best2(_p(q, _u32p), len(q), _p(db, _u32p), len(db), _p(out, _i32p))
+        return out
+
+
+def load_oracle():
+    path = os.path.join(_HERE, "liboracle.so")
+    if not os.path.exists(path):
+        build()
+    return Oracle(C.CDLL(path), "port")
+
+
+def load_ref():
+    """The reference's own functions, or None where oracle/_ref was not built/shipped."""
+    path = os.path.join(_HERE, "_ref", "libvisnav_ref.so")
+    if not os.path.exists(path):
+        return None
+    return Oracle(C.CDLL(path), "reference")
