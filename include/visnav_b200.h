@@ -1,0 +1,162 @@
+/*
+ * visnav_b200.h -- C ABI of the B200 (sm_100a) front-end hot path of visnav
+ * (yunjinli/visual-slam).  This is the drop-in boundary: plain pointers and
+ * sizes, no C++/torch types.  Everything below runs as hand-written CUDA; there
+ * is no CPU fallback -- every entry point fails with VSLAM_E_CUDA when no
+ * sm_100 device is usable.
+ *
+ * Reference interfaces replaced (all in /root/reference/include/visnav/keypoints.h):
+ *   detectKeypoints                :133-150  -> vslam_detect
+ *   computeAngles                  :152-189  -> vslam_angles
+ *   computeDescriptors             :191-221  -> vslam_describe
+ *   detectKeypointsAndDescriptors  :223-229  -> vslam_detect_describe
+ *   matchDescriptors (+isPQiffQP)  :323-369 (:278-313) -> vslam_match
+ * Batched forms of the same operations (frames / keyframe pairs are independent,
+ * slam.cpp:1125-1143, sim3.h:252,281, tracking.h:283,317) follow below.
+ *
+ * Data layouts (identical to the reference's containers, so the C++ shim in
+ * include/visnav/keypoints.h passes vector::data() straight through):
+ *   corners      N x 2 double  (x, y)   == std::vector<Eigen::Vector2d>
+ *   angles       N double               == std::vector<double>
+ *   descriptors  N x 8 uint32, bit i of the std::bitset<256> at word i/32, bit i%32
+ *                (libstdc++ in-memory layout, sizeof == 32)
+ *   matches      M x 2 int32 (id1, id2) == std::vector<std::pair<int,int>>
+ *
+ * Threading: one vslam_ctx per host thread / GPU.  Calls on one ctx are
+ * serialised by the caller; different ctxs are independent.  All calls are
+ * synchronous at return unless stated otherwise.
+ */
+#ifndef VISNAV_B200_H_
+#define VISNAV_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct vslam_ctx vslam_ctx;
+typedef struct vslam_stereo_plan vslam_stereo_plan;
+typedef struct vslam_desc_store vslam_desc_store;
+
+/* status codes */
+#define VSLAM_OK 0
+#define VSLAM_E_ARG (-1)      /* bad argument */
+#define VSLAM_E_CAPACITY (-2) /* caller-provided output capacity too small */
+#define VSLAM_E_CUDA (-3)     /* CUDA error / no usable device; see vslam_last_error */
+#define VSLAM_E_LIMIT (-4)    /* input exceeds a documented internal limit */
+
+/* options for vslam_set_option */
+#define VSLAM_OPT_FP_CONTRACT 1 /* 1 (default): rBRIEF rotation uses the fused form GCC emits for the
+                                   reference at -O3 on FMA hosts (x' = fma(c,x,-(s*y))); 0: two
+                                   multiplies + add (reference built with -ffp-contract=off) */
+#define VSLAM_OPT_MATCH_CSA 2   /* 1 (default): Hamming kernel folds words with carry-save adders
+                                   before POPC; 0: one POPC per 32-bit word.  Results identical. */
+
+/* ---- context ------------------------------------------------------------------------ */
+int vslam_create(int device, vslam_ctx** out);
+void vslam_destroy(vslam_ctx* ctx);
+const char* vslam_last_error(vslam_ctx* ctx);
+int vslam_set_option(vslam_ctx* ctx, int option, int value);
+/* the CUDA stream (cudaStream_t) all work of this ctx is issued on; for event timing */
+void* vslam_stream(vslam_ctx* ctx);
+int vslam_sync(vslam_ctx* ctx);
+/* number of kernels this ctx launched so far (bench.py's gpu_launches) */
+long long vslam_launch_count(vslam_ctx* ctx);
+/* pinned host memory, so that batched calls overlap copies with kernels */
+void* vslam_host_alloc(size_t bytes);
+void vslam_host_free(void* p);
+
+/* ---- single-image operations (host buffers in, host buffers out) --------------------- */
+/* keypoints.h:133-150.  img: h rows of w bytes, `pitch` bytes apart.  num_features <= 0: no cap.
+ * xy: cap x 2 doubles.  *n = number of corners written (<= cap). */
+int vslam_detect(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch, int num_features,
+                 double* xy, int cap, int* n);
+/* keypoints.h:152-189.  rotate == 0 -> all angles 0. */
+int vslam_angles(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch, const double* xy,
+                 int n, int rotate, double* angles);
+/* keypoints.h:191-221.  desc: n x 8 uint32. */
+int vslam_describe(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch, const double* xy,
+                   const double* angles, int n, uint32_t* desc);
+/* keypoints.h:223-229. */
+int vslam_detect_describe(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch,
+                          int num_features, int rotate, double* xy, double* angles, uint32_t* desc,
+                          int cap, int* n);
+/* keypoints.h:323-369.  pairs: cap x 2 int32, ascending id1.  *n = number of matches; if it
+ * exceeds cap only cap pairs are written and VSLAM_E_CAPACITY is returned. */
+int vslam_match(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_t* d2, int n2,
+                int threshold, double dist_2_best, int32_t* pairs, int cap, int* n);
+/* Row statistics of the scan in keypoints.h:331-354 for every query against `db`:
+ * out3[3*i..] = (best distance, lowest index attaining it, second best).  Relocalisation-shaped
+ * queries (BASELINE config 4) use this together with vslam_match. */
+int vslam_best2(vslam_ctx* ctx, const uint32_t* q, int nq, const uint32_t* db, int ndb,
+                int32_t* out3);
+/* Min-eigenvalue response map (the float image cv::goodFeaturesToTrack thresholds,
+ * OCV featureselect.cpp:411) -- exported for parity tests.  lam: h x w floats, dense. */
+int vslam_response(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch, float* lam);
+
+/* ---- batched detect+describe (independent images) -------------------------------------- */
+/* images: `count` images, image k at images + k*image_stride.  Outputs are fixed-stride slabs:
+ * xy [count][cap][2], angles [count][cap], desc [count][cap][8], n_kp [count].
+ * cap must be >= num_features (> 0). */
+int vslam_detect_describe_batch(vslam_ctx* ctx, const uint8_t* images, int count, int w, int h,
+                                int pitch, size_t image_stride, int num_features, int rotate,
+                                double* xy, double* angles, uint32_t* desc, int32_t* n_kp, int cap);
+
+/* ---- batched stereo front end: detect+describe both images, then matchDescriptors -------- */
+/* slam.cpp:1125-1143 for `count` independent stereo pairs.  images: [count][2] images (left,
+ * right) `image_stride` bytes apart.  Per image outputs as above with 2*count images; per pair:
+ * matches [count][cap][2], n_matches [count].  Any output pointer may be NULL (not copied back). */
+typedef struct {
+  int w, h, pitch;
+  size_t image_stride;
+  int num_features;
+  int rotate_features;
+  int match_threshold;
+  double match_dist_2_best;
+} vslam_stereo_params;
+
+int vslam_stereo_batch(vslam_ctx* ctx, const uint8_t* images, int count,
+                       const vslam_stereo_params* p, double* xy, double* angles, uint32_t* desc,
+                       int32_t* n_kp, int32_t* matches, int32_t* n_matches, int cap);
+
+/* The same pipeline split into upload / run / download so that a caller (bench.py) can time
+ * the device-resident part alone.  run() is asynchronous on vslam_stream(ctx). */
+int vslam_stereo_plan_create(vslam_ctx* ctx, int w, int h, int max_pairs, int cap,
+                             vslam_stereo_plan** out);
+void vslam_stereo_plan_destroy(vslam_stereo_plan* plan);
+int vslam_stereo_plan_upload(vslam_stereo_plan* plan, const uint8_t* images, int count, int pitch,
+                             size_t image_stride);
+int vslam_stereo_plan_run(vslam_stereo_plan* plan, int count, int num_features, int rotate,
+                          int match_threshold, double match_dist_2_best);
+int vslam_stereo_plan_download(vslam_stereo_plan* plan, int count, double* xy, double* angles,
+                               uint32_t* desc, int32_t* n_kp, int32_t* matches, int32_t* n_matches);
+/* time of the last run() on the device, CUDA events on the ctx stream: total and per stage
+ * (response, select, describe, match); ms[5]. */
+int vslam_stereo_plan_last_ms(vslam_stereo_plan* plan, float* ms);
+
+/* ---- batched matching against a device-resident descriptor store ----------------------- */
+/* Keyframe descriptors stay on the device (sim3.h:252,281 / tracking.h:283,317 match the same
+ * stored keyframes again and again).  sets: n_sets descriptor sets, set k has counts[k]
+ * descriptors starting at desc + offsets[k]*8 words. */
+int vslam_desc_store_create(vslam_ctx* ctx, const uint32_t* desc, const int64_t* offsets,
+                            const int32_t* counts, int n_sets, vslam_desc_store** out);
+void vslam_desc_store_destroy(vslam_desc_store* s);
+/* jobs: n_jobs x 2 int32 (set index of descriptors_1, set index of descriptors_2).
+ * Outputs: matches [n_jobs][cap][2], n_matches [n_jobs] (host; either may be NULL). */
+int vslam_match_batch(vslam_ctx* ctx, const vslam_desc_store* s, const int32_t* jobs, int n_jobs,
+                      int threshold, double dist_2_best, int32_t* matches, int32_t* n_matches,
+                      int cap);
+/* device time of the last vslam_match_batch / vslam_match / vslam_best2 kernels (ms) */
+float vslam_last_match_ms(vslam_ctx* ctx);
+
+/* ---- measurement helpers --------------------------------------------------------------- */
+/* Register-only POPC throughput microbenchmark: popc.b32 instructions per second (thread
+ * level) sustained over all SMs -- the measured denominator of the matching roofline. */
+int vslam_popc_peak(vslam_ctx* ctx, double* popc_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VISNAV_B200_H_ */

@@ -1,0 +1,142 @@
+"""GPU parity of detect / angles / describe and the batched front ends against the CPU oracle.
+Corners: ordered equality (integer coordinates).  Response map: bit-exact.  Angles: <= 1e-5 rad
+(north_star tolerance; fp64 atan2 of CUDA vs glibc differ by ulps).  Descriptors, given identical
+corners and angles: bit-exact."""
+import numpy as np
+import pytest
+
+import visnav_b200
+from visnav_b200 import workloads as wl
+from visnav_b200.keypoints import KeypointsData, VSLAM_OPT_FP_CONTRACT
+
+pytestmark = pytest.mark.gpu
+
+ANGLE_TOL = 1e-5
+
+SIZES = [(752, 480), (640, 481), (121, 97), (39, 39), (250, 64), (1920, 1080)]
+
+
+def _image(w, h, seed):
+    return wl.synth_image(seed, w, h)
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+def test_response_bit_exact(ctx, oracle_port, w, h):
+    img = _image(w, h, 7 + w)
+    got = ctx.response(img)
+    want = oracle_port.response(img)
+    assert got.shape == want.shape
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), float((got != want).mean())
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+@pytest.mark.parametrize("nf", [1500, 100, 0])
+def test_detect_ordered_equal(ctx, oracle_port, w, h, nf):
+    img = _image(w, h, 11 + h)
+    got = ctx.detect(img, nf)
+    want = oracle_port.detect(img, nf)
+    assert got.shape == want.shape and np.array_equal(got, want)
+
+
+def test_detect_special_images(ctx, oracle_port):
+    flat = np.full((120, 160), 77, np.uint8)              # constant: no response anywhere
+    assert len(ctx.detect(flat, 100)) == 0 == len(oracle_port.detect(flat, 100))
+    chk = ((np.indices((200, 240)).sum(0) // 8) % 2 * 255).astype(np.uint8)   # plateaus and exact ties
+    assert np.array_equal(ctx.detect(chk, 0), oracle_port.detect(chk, 0))
+    rng = np.random.default_rng(3)
+    noise = rng.integers(0, 256, (300, 333), dtype=np.uint8)                 # dense candidates
+    assert np.array_equal(ctx.detect(noise, 0), oracle_port.detect(noise, 0))
+    tiny = rng.integers(0, 256, (20, 30), dtype=np.uint8)                    # nothing survives the 19 px border
+    assert len(ctx.detect(tiny, 10)) == 0
+
+
+def test_detect_pitched_input(ctx, oracle_port):
+    big = _image(800, 500, 5)
+    view = big[10:490, 20:772]            # 752 x 480 view, pitch 800
+    assert np.array_equal(ctx.detect(view, 1500), oracle_port.detect(np.ascontiguousarray(view), 1500))
+
+
+@pytest.mark.parametrize("rotate", [True, False])
+def test_angles_and_descriptors(ctx, oracle_port, oracle_ref, rotate):
+    img = _image(752, 480, 21)
+    xy = oracle_port.detect(img, 1500)
+    ang_o = oracle_port.angles(img, xy, rotate)
+    ang_g = ctx.angles(img, xy, rotate)
+    assert np.abs(ang_g - ang_o).max() <= ANGLE_TOL
+    for contract in (1, 0):
+        ctx.set_option(VSLAM_OPT_FP_CONTRACT, contract)
+        got = ctx.describe(img, xy, ang_o)          # identical keypoints AND angles -> bit-exact
+        want = oracle_port.describe(img, xy, ang_o, contract=bool(contract))
+        assert np.array_equal(got, want), int((got != want).any(1).sum())
+    ctx.set_option(VSLAM_OPT_FP_CONTRACT, 1)
+    if oracle_ref is not None:
+        assert np.array_equal(ctx.describe(img, xy, ang_o), oracle_ref.describe(img, xy, ang_o))
+        assert np.abs(ctx.angles(img, xy, rotate) - oracle_ref.angles(img, xy, rotate)).max() <= ANGLE_TOL
+
+
+def test_describe_border_keypoints(ctx, oracle_port):
+    """Keypoints nearer than 19 px to the edge (never produced by detect): edge replication, like the oracle."""
+    img = _image(160, 120, 2)
+    xy = np.array([[0, 0], [159, 119], [5, 60], [80, 3], [150, 110], [80, 60]], np.float64)
+    ang = oracle_port.angles(img, xy, True)
+    assert np.abs(ctx.angles(img, xy, True) - ang).max() <= ANGLE_TOL
+    assert np.array_equal(ctx.describe(img, xy, ang), oracle_port.describe(img, xy, ang))
+
+
+def test_reference_api_mirror(ctx, oracle_port):
+    """The reference's call sequence (slam.cpp:1125-1143) through the mirrored free functions."""
+    left, right = wl.synth_stereo_pair(3)
+    kdl, kdr = KeypointsData(), KeypointsData()
+    visnav_b200.detectKeypointsAndDescriptors(left, kdl, 1500, True)
+    kd2 = KeypointsData()
+    visnav_b200.detectKeypoints(right, kd2, 1500)
+    visnav_b200.computeAngles(right, kd2, True)
+    visnav_b200.computeDescriptors(right, kd2)
+    visnav_b200.detectKeypointsAndDescriptors(right, kdr, 1500, True)
+    assert np.array_equal(kd2.corners, kdr.corners) and np.array_equal(kd2.corner_descriptors, kdr.corner_descriptors)
+    matches = [(-1, -1)]
+    visnav_b200.matchDescriptors(kdl.corner_descriptors, kdr.corner_descriptors, matches, 70, 1.2)
+    xl, al, dl = oracle_port.detect_describe(left, 1500)
+    xr, ar, dr = oracle_port.detect_describe(right, 1500)
+    assert np.array_equal(kdl.corners, xl) and np.array_equal(kdr.corners, xr)
+    assert np.abs(kdl.corner_angles - al).max() <= ANGLE_TOL
+    assert np.array_equal(kdl.corner_descriptors, dl) and np.array_equal(kdr.corner_descriptors, dr)
+    want = oracle_port.match(dl, dr, 70, 1.2)
+    assert matches == [(int(a), int(b)) for a, b in want] and len(matches) > 900
+
+
+def test_stereo_batch_matches_oracle(ctx, oracle_port):
+    n = 5
+    imgs = wl.synth_stereo_batch(n, workers=1)
+    out = ctx.stereo_batch(imgs, 1500, True, 70, 1.2)
+    xy2, ang2, desc2, nkp2 = ctx.detect_describe_batch(imgs.reshape(2 * n, 480, 752), 1500, True)
+    for k in range(n):
+        ds = []
+        for side in range(2):
+            i = 2 * k + side
+            x, a, d = oracle_port.detect_describe(imgs[k, side], 1500)
+            c = out["n_kp"][i]
+            assert c == len(x) == nkp2[i]
+            assert np.array_equal(out["xy"][i, :c], x) and np.array_equal(xy2[i, :c], x)
+            assert np.abs(out["angles"][i, :c] - a).max() <= ANGLE_TOL
+            assert np.array_equal(out["desc"][i, :c], d) and np.array_equal(desc2[i, :c], d)
+            ds.append(d)
+        want = oracle_port.match(ds[0], ds[1], 70, 1.2)
+        m = out["n_matches"][k]
+        assert m == len(want) and np.array_equal(out["matches"][k, :m], want)
+
+
+def test_stereo_batch_chunked_pipeline(ctx):
+    """More pairs than one pipeline chunk (128): results must not depend on the chunking."""
+    base = wl.synth_stereo_batch(3, workers=1)
+    n = 150
+    imgs = np.ascontiguousarray(base[np.arange(n) % 3])
+    out = ctx.stereo_batch(imgs, 1500)
+    for k in range(n):
+        r = k % 3
+        for side in range(2):
+            c = out["n_kp"][2 * k + side]
+            assert c == out["n_kp"][2 * r + side]
+            assert np.array_equal(out["desc"][2 * k + side, :c], out["desc"][2 * r + side, :c])
+        m = out["n_matches"][k]
+        assert m == out["n_matches"][r] and np.array_equal(out["matches"][k, :m], out["matches"][r, :m])

@@ -1,0 +1,111 @@
+"""GPU parity of vslam_match / vslam_best2 / vslam_match_batch against the CPU oracle
+(visnav::matchDescriptors, reference keypoints.h:323-369).  Bit-exact: integer work."""
+import numpy as np
+import pytest
+
+import visnav_b200
+from visnav_b200 import workloads as wl
+from visnav_b200.keypoints import DescStore, VSLAM_OPT_MATCH_CSA
+
+pytestmark = pytest.mark.gpu
+
+
+def _tied(n, seed, n_base=40, flips=6):
+    """Descriptors with heavy distance ties: few base patterns, few flipped bits."""
+    rng = np.random.default_rng(seed)
+    base = wl.random_descriptors(n_base, seed + 1)
+    d = base[rng.integers(0, n_base, n)]
+    return wl.flip_bits(d, flips, rng) if n else d
+
+
+CASES = [(1, 1), (1, 40), (40, 1), (31, 33), (64, 65), (257, 255), (1500, 1500), (1537, 1300), (3100, 700), (700, 3100)]
+
+
+@pytest.mark.parametrize("csa", [1, 0])
+@pytest.mark.parametrize("n1,n2", CASES)
+def test_match_random_correlated(ctx, oracle_port, n1, n2, csa):
+    ctx.set_option(VSLAM_OPT_MATCH_CSA, csa)
+    rng = np.random.default_rng(n1 * 7919 + n2)
+    d2 = wl.random_descriptors(n2, n1 + 3)
+    d1 = wl.random_descriptors(n1, n2 + 5)
+    k = min(n1, n2)
+    perm = rng.permutation(n2)[:k]
+    d1[:k] = wl.flip_bits(d2[perm], 20, rng)      # correlated part: produces matches
+    for thr, ratio in [(70, 1.2), (256, 1.0), (300, 1.0), (40, 2.0), (0, 1.2)]:
+        got = ctx.match(d1, d2, thr, ratio)
+        want = oracle_port.match(d1, d2, thr, ratio)
+        assert np.array_equal(got, want), (n1, n2, thr, ratio, len(got), len(want))
+    ctx.set_option(VSLAM_OPT_MATCH_CSA, 1)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_match_heavy_ties(ctx, oracle_port, seed):
+    n1, n2 = 300 + 37 * seed, 280 + 53 * seed
+    d1, d2 = _tied(n1, seed), _tied(n2, seed)   # same base patterns -> many equal distances
+    for thr, ratio in [(70, 1.2), (256, 1.0), (20, 1.0)]:
+        got = ctx.match(d1, d2, thr, ratio)
+        want = oracle_port.match(d1, d2, thr, ratio)
+        assert np.array_equal(got, want)
+    assert np.array_equal(ctx.best2(d1, d2), oracle_port.best2(d1, d2))
+
+
+def test_match_extremes(ctx, oracle_port):
+    z = np.zeros((5, 8), np.uint32)
+    f = np.full((7, 8), 0xFFFFFFFF, np.uint32)
+    # all distances 256: nothing updates (strict '<'), argmin stays 0
+    assert np.array_equal(ctx.best2(z, f), oracle_port.best2(z, f))
+    assert len(ctx.match(z, f, 300, 1.0)) == len(oracle_port.match(z, f, 300, 1.0))
+    assert np.array_equal(ctx.match(z, f, 300, 1.0), oracle_port.match(z, f, 300, 1.0))
+    # identical sets: every row ties at 0 with itself
+    d = wl.random_descriptors(100, 9)
+    assert np.array_equal(ctx.match(d, d, 70, 1.2), oracle_port.match(d, d, 70, 1.2))
+    dd = np.concatenate([d, d])  # duplicates: second best == best -> ratio test rejects
+    assert np.array_equal(ctx.match(dd, d, 70, 1.2), oracle_port.match(dd, d, 70, 1.2))
+    # empty inputs: matches.clear() and nothing else
+    e = np.zeros((0, 8), np.uint32)
+    assert len(ctx.match(e, d)) == 0 and len(ctx.match(d, e)) == 0 and len(ctx.match(e, e)) == 0
+
+
+def test_match_reference_library(ctx, oracle_ref):
+    if oracle_ref is None:
+        pytest.skip("oracle/_ref not shipped")
+    rng = np.random.default_rng(5)
+    d2 = wl.random_descriptors(900, 1)
+    d1 = wl.flip_bits(d2[rng.permutation(900)[:800]], 25, rng)
+    assert np.array_equal(ctx.match(d1, d2, 70, 1.2), oracle_ref.match(d1, d2, 70, 1.2))
+
+
+def test_match_large_split_path(ctx, oracle_port):
+    """Config 4 shape scaled down: queries vs a DB too big for one CTA (column ranges + merge)."""
+    q, db = wl.reloc_query(300, 20000, 25)
+    assert np.array_equal(ctx.best2(q, db), oracle_port.best2(q, db))
+    got = ctx.match(q, db, 70, 1.2)
+    want = oracle_port.match(q, db, 70, 1.2)
+    assert np.array_equal(got, want) and len(got) > 100
+    # and the transposed problem (many rows, few columns)
+    got = ctx.match(db[:12000], q, 70, 1.2, cap=300)
+    want = oracle_port.match(db[:12000], q, 70, 1.2)
+    assert np.array_equal(got, want)
+
+
+def test_match_full_size_properties(ctx):
+    """Config 4 at full size through size-independent properties: planted matches are found,
+    the predicate is symmetric under swapping the two sets."""
+    q, db = wl.reloc_query(1500, 200000, 25)
+    m = ctx.match(q, db, 70, 1.2)
+    assert len(m) == 1500
+    assert np.array_equal(m[:, 0], np.arange(1500)) and np.array_equal(m[:, 1], 133 * np.arange(1500))
+    mt = ctx.match(db, q, 70, 1.2, cap=1500)
+    assert np.array_equal(mt[np.argsort(mt[:, 1])][:, ::-1], m)
+
+
+def test_match_batch_store(ctx, oracle_port):
+    kf = wl.keyframe_descriptors(6, 700, 25)
+    kf_list = [kf[0], kf[1][:650], kf[2], kf[3][:10], kf[4], kf[5]]
+    store = DescStore(ctx, kf_list)
+    jobs = wl.keyframe_pair_jobs(6)
+    matches, counts = ctx.match_batch(store, jobs, 70, 1.2)
+    for (i, j), m, c in zip(jobs, matches, counts):
+        want = oracle_port.match(kf_list[i], kf_list[j], 70, 1.2)
+        assert c == len(want) and np.array_equal(m[:c], want), (i, j)
+    store.close()

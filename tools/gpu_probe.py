@@ -1,0 +1,64 @@
+#!/usr/bin/env python3
+"""Quick on-GPU probe: POPC peak, matcher throughput (configs 1/3/4 shapes), stereo plan stage times.
+Writes gpurun_out/probe.json.  Not a benchmark of record (bench.py is)."""
+import json, os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import visnav_b200
+from visnav_b200 import workloads as wl
+from visnav_b200.keypoints import DescStore, StereoPlan, VSLAM_OPT_MATCH_CSA
+
+out = {}
+ctx = visnav_b200.Context(0)
+out["popc_per_s"] = ctx.popc_peak()
+print("popc/s", out["popc_per_s"], flush=True)
+
+# config 3 sample: 40 keyframes -> 780 jobs of 1500 x 1500
+kf = wl.keyframe_descriptors(40, 1500, 25)
+store = DescStore(ctx, kf)
+jobs = wl.keyframe_pair_jobs(40)
+for csa in (1, 0):
+    ctx.set_option(VSLAM_OPT_MATCH_CSA, csa)
+    best = 1e9
+    for rep in range(4):
+        _, counts = ctx.match_batch(store, jobs, 70, 1.2, want_matches=False)
+        best = min(best, ctx.last_match_ms())
+    dist = len(jobs) * 1500.0 * 1500.0
+    out["c3_csa%d" % csa] = dict(ms=best, dist_per_s=dist / (best * 1e-3), popc_equiv_per_s=8 * dist / (best * 1e-3),
+                                 mean_matches=float(counts.mean()))
+    print("c3 csa", csa, out["c3_csa%d" % csa], flush=True)
+ctx.set_option(VSLAM_OPT_MATCH_CSA, 1)
+# config 4: 1500 x 200000
+q, db = wl.reloc_query()
+best = 1e9
+for rep in range(4):
+    m = ctx.match(q, db, 70, 1.2)
+    best = min(best, ctx.last_match_ms())
+out["c4"] = dict(ms=best, dist_per_s=1500 * 200000 / (best * 1e-3), matches=len(m))
+print("c4", out["c4"], flush=True)
+# config 1 single call latency
+d1, d2 = kf[0], kf[1]
+t = []
+for rep in range(20):
+    t0 = time.perf_counter(); ctx.match(d1, d2); t.append(time.perf_counter() - t0)
+out["c1_match_call_ms"] = 1e3 * float(np.median(t)); out["c1_match_kernel_ms"] = ctx.last_match_ms()
+print("c1", out["c1_match_call_ms"], out["c1_match_kernel_ms"], flush=True)
+
+# stereo plan: stage times
+npairs = int(os.environ.get("PROBE_PAIRS", "256"))
+imgs = wl.synth_stereo_batch(npairs)
+plan = StereoPlan(ctx, 752, 480, npairs, 1500)
+plan.upload(imgs)
+for rep in range(4):
+    plan.run(npairs)
+    ms = plan.last_ms()
+res = plan.download(npairs)
+out["stereo"] = dict(pairs=npairs, ms_total=ms[0], ms_response=ms[1], ms_select=ms[2], ms_describe=ms[3], ms_match=ms[4],
+                     pairs_per_s=npairs / (ms[0] * 1e-3), mean_kp=float(res["n_kp"].mean()),
+                     mean_matches=float(res["n_matches"].mean()), min_kp=int(res["n_kp"].min()))
+print("stereo", out["stereo"], flush=True)
+t0 = time.perf_counter(); ctx.stereo_batch(imgs); t1 = time.perf_counter()
+out["stereo_e2e_pageable_pairs_per_s"] = npairs / (t1 - t0)
+print("e2e pageable", out["stereo_e2e_pageable_pairs_per_s"])
+os.makedirs("gpurun_out", exist_ok=True)
+json.dump(out, open("gpurun_out/probe.json", "w"), indent=1)

@@ -1,0 +1,702 @@
+// api.cu -- the C ABI (include/visnav_b200.h): context, host<->device marshalling, batching.
+// No computation happens on the host here; every entry point launches the CUDA kernels of
+// detect.cu / describe.cu / match.cu and fails with VSLAM_E_CUDA when that is impossible.
+#include <new>
+#include <vector>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int kMinDistance = 8;      // keypoints.h:138: goodFeaturesToTrack(..., 0.01, 8, ...)
+constexpr double kQuality = 0.01;
+constexpr int kEdgeThreshold = 19;   // keypoints.h:50 EDGE_THRESHOLD
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+inline int dev_pitch(int w) { return (int)align_up((size_t)w, 128); }
+inline int cand_capacity(int w, int h) { return (w * h) / 4 + 1024; }
+
+// Image set in ctx scratch + detection workspace for `count` images.
+struct Scratch {
+  DevImages im;
+  DetectWorkspace ws;
+};
+
+int prepare_detect_ws(vslam_ctx* ctx, int w, int h, int count, DevBuf& cand, DevBuf& candcnt, DevBuf& imgmax,
+                      DevBuf& selws, DetectWorkspace* ws) {
+  const int ccap = cand_capacity(w, h);
+  const size_t wsb = detect_sel_ws_bytes(w, h, ccap, kMinDistance);
+  VS_CUDA(ctx, cand.reserve((size_t)count * ccap * sizeof(uint64_t)));
+  VS_CUDA(ctx, candcnt.reserve((size_t)count * sizeof(uint32_t)));
+  VS_CUDA(ctx, imgmax.reserve((size_t)count * sizeof(uint32_t)));
+  VS_CUDA(ctx, selws.reserve((size_t)count * wsb));
+  ws->cand = cand.as<uint64_t>();
+  ws->cand_cnt = candcnt.as<uint32_t>();
+  ws->img_max = imgmax.as<uint32_t>();
+  ws->cand_cap = ccap;
+  ws->sel_ws = selws.as<uint8_t>();
+  ws->sel_ws_stride = wsb;
+  return VSLAM_OK;
+}
+
+int upload_images(vslam_ctx* ctx, DevBuf& buf, const uint8_t* host, int count, int w, int h, int pitch,
+                  size_t image_stride, DevImages* im, cudaStream_t stream) {
+  const int dp = dev_pitch(w);
+  const size_t ds = (size_t)dp * h;
+  VS_CUDA(ctx, buf.reserve(ds * count));
+  im->base = buf.as<uint8_t>();
+  im->w = w; im->h = h; im->pitch = dp; im->stride = ds;
+  if (count > 1 && image_stride == (size_t)pitch * h) {
+    // images are back to back: one strided copy of count*h rows
+    VS_CUDA(ctx, cudaMemcpy2DAsync(buf.p, dp, host, pitch, w, (size_t)h * count, cudaMemcpyHostToDevice, stream));
+  } else {
+    for (int i = 0; i < count; ++i)
+      VS_CUDA(ctx, cudaMemcpy2DAsync(buf.as<uint8_t>() + ds * i, dp, host + image_stride * i, pitch, w, h,
+                                     cudaMemcpyHostToDevice, stream));
+  }
+  return VSLAM_OK;
+}
+
+int check_image(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch) {
+  if (!ctx) return VSLAM_E_ARG;
+  if (!img || w < 2 || h < 2 || pitch < w) return vs_fail(ctx, VSLAM_E_ARG, "bad image arguments");
+  if ((long long)w * h > (1LL << 30)) return vs_fail(ctx, VSLAM_E_LIMIT, "image larger than 2^30 pixels");
+  return VSLAM_OK;
+}
+
+int kp_status(vslam_ctx* ctx, int n) {
+  if (n == -1) return vs_fail(ctx, VSLAM_E_LIMIT, "corner candidate list overflowed (more than w*h/4 local maxima)");
+  if (n == -2) return vs_fail(ctx, VSLAM_E_CAPACITY, "more corners than the output capacity");
+  return VSLAM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int vslam_create(int device, vslam_ctx** out) {
+  if (!out) return VSLAM_E_ARG;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return VSLAM_E_CUDA;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return VSLAM_E_CUDA;
+  if (prop.major != 10) return VSLAM_E_CUDA;  // sm_100a SASS only; nothing else can run it
+  if (cudaSetDevice(device) != cudaSuccess) return VSLAM_E_CUDA;
+  vslam_ctx* ctx = new (std::nothrow) vslam_ctx();
+  if (!ctx) return VSLAM_E_CUDA;
+  ctx->device = device;
+  ctx->num_sms = prop.multiProcessorCount;
+  bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess;
+  for (int i = 0; i < 2 && ok; ++i) ok = cudaStreamCreateWithFlags(&ctx->copy_stream[i], cudaStreamNonBlocking) == cudaSuccess;
+  for (int i = 0; i < 8 && ok; ++i) ok = cudaEventCreate(&ctx->ev[i]) == cudaSuccess;
+  ok = ok && cudaMallocHost(&ctx->pinned, 4096) == cudaSuccess;
+  if (!ok) {
+    vslam_destroy(ctx);
+    return VSLAM_E_CUDA;
+  }
+  *out = ctx;
+  return VSLAM_OK;
+}
+
+void vslam_destroy(vslam_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  DevBuf* bufs[] = {&ctx->img, &ctx->xy, &ctx->ang, &ctx->desc, &ctx->cnt, &ctx->lam, &ctx->cand, &ctx->candcnt,
+                    &ctx->imgmax, &ctx->selws, &ctx->d1, &ctx->d2, &ctx->pairs, &ctx->mcnt, &ctx->rowpart,
+                    &ctx->colstat, &ctx->jobs};
+  for (DevBuf* b : bufs) b->release();
+  for (int i = 0; i < 8; ++i)
+    if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+  for (int i = 0; i < 2; ++i)
+    if (ctx->copy_stream[i]) cudaStreamDestroy(ctx->copy_stream[i]);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  delete ctx;
+}
+
+const char* vslam_last_error(vslam_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int vslam_set_option(vslam_ctx* ctx, int option, int value) {
+  if (!ctx) return VSLAM_E_ARG;
+  if (option == VSLAM_OPT_FP_CONTRACT) ctx->fp_contract = value != 0;
+  else if (option == VSLAM_OPT_MATCH_CSA) ctx->match_csa = value != 0;
+  else return vs_fail(ctx, VSLAM_E_ARG, "unknown option");
+  return VSLAM_OK;
+}
+
+void* vslam_stream(vslam_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+int vslam_sync(vslam_ctx* ctx) {
+  if (!ctx) return VSLAM_E_ARG;
+  VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return VSLAM_OK;
+}
+
+long long vslam_launch_count(vslam_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+void* vslam_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaMallocHost(&p, bytes) != cudaSuccess) return nullptr;
+  return p;
+}
+void vslam_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
+// ---- single image -------------------------------------------------------------------------------
+
+static int detect_on_device(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch, int num_features, int cap,
+                            DevImages* im) {
+  DetectWorkspace ws;
+  int rc = upload_images(ctx, ctx->img, img, 1, w, h, pitch, (size_t)pitch * h, im, ctx->stream);
+  if (rc) return rc;
+  rc = prepare_detect_ws(ctx, w, h, 1, ctx->cand, ctx->candcnt, ctx->imgmax, ctx->selws, &ws);
+  if (rc) return rc;
+  VS_CUDA(ctx, ctx->xy.reserve((size_t)cap * 16));
+  VS_CUDA(ctx, ctx->cnt.reserve(64));
+  rc = launch_response(ctx, *im, 1, ws, nullptr);
+  if (rc) return rc;
+  return launch_select(ctx, *im, 1, ws, num_features, kQuality, kMinDistance, kEdgeThreshold, ctx->xy.as<double>(),
+                       ctx->cnt.as<int32_t>(), cap);
+}
+
+int vslam_detect(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch, int num_features, double* xy, int cap,
+                 int* n) {
+  int rc = check_image(ctx, img, w, h, pitch);
+  if (rc) return rc;
+  if (!n || cap < 0 || (cap > 0 && !xy)) return vs_fail(ctx, VSLAM_E_ARG, "bad output arguments");
+  *n = 0;
+  if (w < 2 * kEdgeThreshold + 1 || h < 2 * kEdgeThreshold + 1) return VSLAM_OK;  // InBounds(.,.,19) keeps nothing
+  if (cap == 0) return vs_fail(ctx, VSLAM_E_CAPACITY, "cap == 0");
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  DevImages im;
+  rc = detect_on_device(ctx, img, w, h, pitch, num_features, cap, &im);
+  if (rc) return rc;
+  int32_t* hn = static_cast<int32_t*>(ctx->pinned);
+  VS_CUDA(ctx, cudaMemcpyAsync(hn, ctx->cnt.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if ((rc = kp_status(ctx, *hn))) return rc;
+  *n = *hn;
+  if (*n > 0) VS_CUDA(ctx, cudaMemcpy(xy, ctx->xy.p, (size_t)*n * 16, cudaMemcpyDeviceToHost));
+  return VSLAM_OK;
+}
+
+static int orient_describe_host(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch, const double* xy,
+                                int n, int mode, double* angles_io, uint32_t* desc) {
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  DevImages im;
+  int rc = upload_images(ctx, ctx->img, img, 1, w, h, pitch, (size_t)pitch * h, &im, ctx->stream);
+  if (rc) return rc;
+  VS_CUDA(ctx, ctx->xy.reserve((size_t)n * 16));
+  VS_CUDA(ctx, ctx->ang.reserve((size_t)n * 8));
+  VS_CUDA(ctx, ctx->cnt.reserve(64));
+  if (desc) VS_CUDA(ctx, ctx->desc.reserve((size_t)n * 32));
+  int32_t* hn = static_cast<int32_t*>(ctx->pinned);
+  *hn = n;
+  VS_CUDA(ctx, cudaMemcpyAsync(ctx->cnt.p, hn, 4, cudaMemcpyHostToDevice, ctx->stream));
+  VS_CUDA(ctx, cudaMemcpyAsync(ctx->xy.p, xy, (size_t)n * 16, cudaMemcpyHostToDevice, ctx->stream));
+  if (mode == 2) VS_CUDA(ctx, cudaMemcpyAsync(ctx->ang.p, angles_io, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
+  rc = launch_orient_describe(ctx, im, 1, ctx->xy.as<double>(), ctx->cnt.as<int32_t>(), n, mode, ctx->ang.as<double>(),
+                              desc ? ctx->desc.as<uint32_t>() : nullptr);
+  if (rc) return rc;
+  if (mode != 2) VS_CUDA(ctx, cudaMemcpyAsync(angles_io, ctx->ang.p, (size_t)n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  if (desc) VS_CUDA(ctx, cudaMemcpyAsync(desc, ctx->desc.p, (size_t)n * 32, cudaMemcpyDeviceToHost, ctx->stream));
+  VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return VSLAM_OK;
+}
+
+int vslam_angles(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch, const double* xy, int n, int rotate,
+                 double* angles) {
+  int rc = check_image(ctx, img, w, h, pitch);
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!xy || !angles))) return vs_fail(ctx, VSLAM_E_ARG, "bad keypoint arguments");
+  if (n == 0) return VSLAM_OK;
+  return orient_describe_host(ctx, img, w, h, pitch, xy, n, rotate ? 1 : 0, angles, nullptr);
+}
+
+int vslam_describe(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch, const double* xy,
+                   const double* angles, int n, uint32_t* desc) {
+  int rc = check_image(ctx, img, w, h, pitch);
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!xy || !angles || !desc))) return vs_fail(ctx, VSLAM_E_ARG, "bad keypoint arguments");
+  if (n == 0) return VSLAM_OK;
+  return orient_describe_host(ctx, img, w, h, pitch, xy, n, 2, const_cast<double*>(angles), desc);
+}
+
+int vslam_detect_describe(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch, int num_features, int rotate,
+                          double* xy, double* angles, uint32_t* desc, int cap, int* n) {
+  int rc = check_image(ctx, img, w, h, pitch);
+  if (rc) return rc;
+  if (!n || cap < 0 || (cap > 0 && (!xy || !angles || !desc))) return vs_fail(ctx, VSLAM_E_ARG, "bad output arguments");
+  *n = 0;
+  if (w < 2 * kEdgeThreshold + 1 || h < 2 * kEdgeThreshold + 1) return VSLAM_OK;
+  if (cap == 0) return vs_fail(ctx, VSLAM_E_CAPACITY, "cap == 0");
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  DevImages im;
+  rc = detect_on_device(ctx, img, w, h, pitch, num_features, cap, &im);
+  if (rc) return rc;
+  VS_CUDA(ctx, ctx->ang.reserve((size_t)cap * 8));
+  VS_CUDA(ctx, ctx->desc.reserve((size_t)cap * 32));
+  rc = launch_orient_describe(ctx, im, 1, ctx->xy.as<double>(), ctx->cnt.as<int32_t>(), cap, rotate ? 1 : 0,
+                              ctx->ang.as<double>(), ctx->desc.as<uint32_t>());
+  if (rc) return rc;
+  int32_t* hn = static_cast<int32_t*>(ctx->pinned);
+  VS_CUDA(ctx, cudaMemcpyAsync(hn, ctx->cnt.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if ((rc = kp_status(ctx, *hn))) return rc;
+  *n = *hn;
+  if (*n > 0) {
+    VS_CUDA(ctx, cudaMemcpyAsync(xy, ctx->xy.p, (size_t)*n * 16, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaMemcpyAsync(angles, ctx->ang.p, (size_t)*n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaMemcpyAsync(desc, ctx->desc.p, (size_t)*n * 32, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  return VSLAM_OK;
+}
+
+int vslam_response(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch, float* lam) {
+  int rc = check_image(ctx, img, w, h, pitch);
+  if (rc) return rc;
+  if (!lam) return vs_fail(ctx, VSLAM_E_ARG, "null output");
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  DevImages im;
+  DetectWorkspace ws;
+  rc = upload_images(ctx, ctx->img, img, 1, w, h, pitch, (size_t)pitch * h, &im, ctx->stream);
+  if (rc) return rc;
+  rc = prepare_detect_ws(ctx, w, h, 1, ctx->cand, ctx->candcnt, ctx->imgmax, ctx->selws, &ws);
+  if (rc) return rc;
+  VS_CUDA(ctx, ctx->lam.reserve((size_t)w * h * 4));
+  rc = launch_response(ctx, im, 1, ws, ctx->lam.as<float>());
+  if (rc) return rc;
+  VS_CUDA(ctx, cudaMemcpyAsync(lam, ctx->lam.p, (size_t)w * h * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return VSLAM_OK;
+}
+
+// ---- matching -------------------------------------------------------------------------------------
+
+static int match_common(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_t* d2, int n2, int threshold,
+                        double ratio, int32_t* pairs, int cap, int* n, int32_t* best2_out) {
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  VS_CUDA(ctx, ctx->d1.reserve((size_t)n1 * 32));
+  VS_CUDA(ctx, ctx->d2.reserve((size_t)n2 * 32));
+  const int dcap = best2_out ? 0 : (cap > 0 ? cap : 1);
+  VS_CUDA(ctx, ctx->pairs.reserve(best2_out ? (size_t)n1 * 12 : (size_t)dcap * 8));
+  VS_CUDA(ctx, ctx->mcnt.reserve(256));
+  VS_CUDA(ctx, cudaMemcpyAsync(ctx->d1.p, d1, (size_t)n1 * 32, cudaMemcpyHostToDevice, ctx->stream));
+  VS_CUDA(ctx, cudaMemcpyAsync(ctx->d2.p, d2, (size_t)n2 * 32, cudaMemcpyHostToDevice, ctx->stream));
+  VS_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+  int rc;
+  if (!best2_out && match_fits_fused(n1, n2)) {
+    VS_CUDA(ctx, ctx->jobs.reserve(sizeof(MatchJob)));
+    MatchJob job;
+    job.d1 = ctx->d1.as<uint32_t>(); job.d2 = ctx->d2.as<uint32_t>();
+    job.n1p = nullptr; job.n2p = nullptr; job.n1 = n1; job.n2 = n2;
+    job.pairs = ctx->pairs.as<int32_t>();
+    job.count = ctx->mcnt.as<int32_t>();
+    memcpy(static_cast<char*>(ctx->pinned) + 64, &job, sizeof job);
+    VS_CUDA(ctx, cudaMemcpyAsync(ctx->jobs.p, static_cast<char*>(ctx->pinned) + 64, sizeof job, cudaMemcpyHostToDevice,
+                                 ctx->stream));
+    rc = launch_match_jobs(ctx, ctx->jobs.as<MatchJob>(), 1, n1, n2, threshold, ratio, dcap);
+  } else {
+    rc = launch_match_large(ctx, ctx->d1.as<uint32_t>(), n1, ctx->d2.as<uint32_t>(), n2, threshold, ratio,
+                            ctx->pairs.as<int32_t>(), ctx->mcnt.as<int32_t>(), dcap,
+                            best2_out ? ctx->pairs.as<int32_t>() : nullptr);
+  }
+  if (rc) return rc;
+  VS_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+  if (best2_out) {
+    VS_CUDA(ctx, cudaMemcpyAsync(best2_out, ctx->pairs.p, (size_t)n1 * 12, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  } else {
+    int32_t* hn = static_cast<int32_t*>(ctx->pinned);
+    VS_CUDA(ctx, cudaMemcpyAsync(hn, ctx->mcnt.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *n = *hn;
+    const int m = *n < cap ? *n : cap;
+    if (m > 0) VS_CUDA(ctx, cudaMemcpy(pairs, ctx->pairs.p, (size_t)m * 8, cudaMemcpyDeviceToHost));
+  }
+  VS_CUDA(ctx, cudaEventElapsedTime(&ctx->last_match_ms, ctx->ev[0], ctx->ev[1]));
+  if (!best2_out && *n > cap) return vs_fail(ctx, VSLAM_E_CAPACITY, "more matches than the output capacity");
+  return VSLAM_OK;
+}
+
+int vslam_match(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_t* d2, int n2, int threshold,
+                double dist_2_best, int32_t* pairs, int cap, int* n) {
+  if (!ctx) return VSLAM_E_ARG;
+  if (!n || n1 < 0 || n2 < 0 || cap < 0 || (n1 > 0 && !d1) || (n2 > 0 && !d2) || (cap > 0 && !pairs))
+    return vs_fail(ctx, VSLAM_E_ARG, "bad match arguments");
+  *n = 0;
+  if (n1 == 0 || n2 == 0) return VSLAM_OK;  // keypoints.h:327 clear(); nothing can pass
+  return match_common(ctx, d1, n1, d2, n2, threshold, dist_2_best, pairs, cap, n, nullptr);
+}
+
+int vslam_best2(vslam_ctx* ctx, const uint32_t* q, int nq, const uint32_t* db, int ndb, int32_t* out3) {
+  if (!ctx) return VSLAM_E_ARG;
+  if (nq < 0 || ndb < 0 || (nq > 0 && (!q || !out3)) || (ndb > 0 && !db)) return vs_fail(ctx, VSLAM_E_ARG, "bad arguments");
+  if (nq == 0) return VSLAM_OK;
+  if (ndb == 0) {
+    for (int i = 0; i < nq; ++i) { out3[3 * i] = 256; out3[3 * i + 1] = 0; out3[3 * i + 2] = 256; }
+    return VSLAM_OK;
+  }
+  int dummy = 0;
+  return match_common(ctx, q, nq, db, ndb, 0, 0.0, nullptr, 0, &dummy, out3);
+}
+
+float vslam_last_match_ms(vslam_ctx* ctx) { return ctx ? ctx->last_match_ms : 0.f; }
+
+int vslam_popc_peak(vslam_ctx* ctx, double* popc_per_s) {
+  if (!ctx || !popc_per_s) return VSLAM_E_ARG;
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  return launch_popc_peak(ctx, popc_per_s);
+}
+
+}  // extern "C"
+
+// ---- stereo plan --------------------------------------------------------------------------------------
+
+struct vslam_stereo_plan {
+  vslam_ctx* ctx = nullptr;
+  int w = 0, h = 0, max_pairs = 0, cap = 0;
+  DevImages im{};
+  DevBuf images, xy, ang, desc, nkp, matches, nmatch, jobs;
+  DevBuf cand, candcnt, imgmax, selws;
+  DetectWorkspace ws{};
+  cudaEvent_t ev[5] = {};
+  cudaStream_t stream = nullptr;  // null: ctx stream
+  float ms[5] = {};
+  bool timed = false;
+};
+
+extern "C" {
+
+void vslam_stereo_plan_destroy(vslam_stereo_plan* plan) {
+  if (!plan) return;
+  cudaSetDevice(plan->ctx->device);
+  cudaDeviceSynchronize();
+  DevBuf* bufs[] = {&plan->images, &plan->xy, &plan->ang, &plan->desc, &plan->nkp, &plan->matches, &plan->nmatch,
+                    &plan->jobs, &plan->cand, &plan->candcnt, &plan->imgmax, &plan->selws};
+  for (DevBuf* b : bufs) b->release();
+  for (int i = 0; i < 5; ++i)
+    if (plan->ev[i]) cudaEventDestroy(plan->ev[i]);
+  if (plan->stream) cudaStreamDestroy(plan->stream);
+  delete plan;
+}
+
+static int plan_create_impl(vslam_ctx* ctx, int w, int h, int max_pairs, int cap, bool own_stream,
+                            vslam_stereo_plan** out) {
+  if (!ctx || !out || w < 2 || h < 2 || max_pairs <= 0 || cap <= 0) return vs_fail(ctx, VSLAM_E_ARG, "bad plan arguments");
+  *out = nullptr;
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  vslam_stereo_plan* p = new (std::nothrow) vslam_stereo_plan();
+  if (!p) return VSLAM_E_CUDA;
+  p->ctx = ctx; p->w = w; p->h = h; p->max_pairs = max_pairs; p->cap = cap;
+  const int nimg = 2 * max_pairs;
+  const int dp = dev_pitch(w);
+  p->im.w = w; p->im.h = h; p->im.pitch = dp; p->im.stride = (size_t)dp * h;
+  int rc = VSLAM_OK;
+  auto fail = [&](int code) {
+    vslam_stereo_plan_destroy(p);
+    return code;
+  };
+#define PLAN_CUDA(call)                                   \
+  do {                                                    \
+    if ((call) != cudaSuccess) {                          \
+      ctx->err = std::string("plan: ") + #call + ": " + cudaGetErrorString(cudaGetLastError()); \
+      return fail(VSLAM_E_CUDA);                          \
+    }                                                     \
+  } while (0)
+  PLAN_CUDA(p->images.reserve(p->im.stride * nimg));
+  p->im.base = p->images.as<uint8_t>();
+  PLAN_CUDA(p->xy.reserve((size_t)nimg * cap * 16));
+  PLAN_CUDA(p->ang.reserve((size_t)nimg * cap * 8));
+  PLAN_CUDA(p->desc.reserve((size_t)nimg * cap * 32));
+  PLAN_CUDA(p->nkp.reserve((size_t)nimg * 4));
+  PLAN_CUDA(p->matches.reserve((size_t)max_pairs * cap * 8));
+  PLAN_CUDA(p->nmatch.reserve((size_t)max_pairs * 4));
+  PLAN_CUDA(p->jobs.reserve((size_t)max_pairs * sizeof(MatchJob)));
+  rc = prepare_detect_ws(ctx, w, h, nimg, p->cand, p->candcnt, p->imgmax, p->selws, &p->ws);
+  if (rc) return fail(rc);
+  for (int i = 0; i < 5; ++i) PLAN_CUDA(cudaEventCreate(&p->ev[i]));
+  if (own_stream) PLAN_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+  // the stereo jobs only depend on the plan's buffers: build them once
+  std::vector<MatchJob> jobs(max_pairs);
+  for (int k = 0; k < max_pairs; ++k) {
+    MatchJob& j = jobs[k];
+    j.d1 = p->desc.as<uint32_t>() + (size_t)(2 * k) * cap * 8;
+    j.d2 = p->desc.as<uint32_t>() + (size_t)(2 * k + 1) * cap * 8;
+    j.n1p = p->nkp.as<int32_t>() + 2 * k;
+    j.n2p = p->nkp.as<int32_t>() + 2 * k + 1;
+    j.n1 = j.n2 = 0;
+    j.pairs = p->matches.as<int32_t>() + (size_t)k * cap * 2;
+    j.count = p->nmatch.as<int32_t>() + k;
+  }
+  PLAN_CUDA(cudaMemcpy(p->jobs.p, jobs.data(), jobs.size() * sizeof(MatchJob), cudaMemcpyHostToDevice));
+#undef PLAN_CUDA
+  *out = p;
+  return VSLAM_OK;
+}
+
+int vslam_stereo_plan_create(vslam_ctx* ctx, int w, int h, int max_pairs, int cap, vslam_stereo_plan** out) {
+  return plan_create_impl(ctx, w, h, max_pairs, cap, false, out);
+}
+
+static cudaStream_t plan_stream(vslam_stereo_plan* p) { return p->stream ? p->stream : p->ctx->stream; }
+
+int vslam_stereo_plan_upload(vslam_stereo_plan* plan, const uint8_t* images, int count, int pitch,
+                             size_t image_stride) {
+  if (!plan) return VSLAM_E_ARG;
+  vslam_ctx* ctx = plan->ctx;
+  if (!images || count < 0 || count > plan->max_pairs || pitch < plan->w) return vs_fail(ctx, VSLAM_E_ARG, "bad upload arguments");
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  DevImages im;
+  return upload_images(ctx, plan->images, images, 2 * count, plan->w, plan->h, pitch, image_stride, &im, plan_stream(plan));
+}
+
+int vslam_stereo_plan_run(vslam_stereo_plan* plan, int count, int num_features, int rotate, int match_threshold,
+                          double match_dist_2_best) {
+  if (!plan) return VSLAM_E_ARG;
+  vslam_ctx* ctx = plan->ctx;
+  if (count < 0 || count > plan->max_pairs) return vs_fail(ctx, VSLAM_E_ARG, "bad pair count");
+  if (num_features <= 0 || num_features > plan->cap) return vs_fail(ctx, VSLAM_E_ARG, "num_features must be in [1, cap]");
+  if (count == 0) return VSLAM_OK;
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t saved = ctx->stream;
+  ctx->stream = plan_stream(plan);
+  const int nimg = 2 * count;
+  int rc = VSLAM_OK;
+  cudaEventRecord(plan->ev[0], ctx->stream);
+  if (plan->w < 2 * kEdgeThreshold + 1 || plan->h < 2 * kEdgeThreshold + 1) {
+    cudaMemsetAsync(plan->nkp.p, 0, (size_t)nimg * 4, ctx->stream);
+    cudaEventRecord(plan->ev[1], ctx->stream);
+    cudaEventRecord(plan->ev[2], ctx->stream);
+  } else {
+    rc = launch_response(ctx, plan->im, nimg, plan->ws, nullptr);
+    cudaEventRecord(plan->ev[1], ctx->stream);
+    if (!rc)
+      rc = launch_select(ctx, plan->im, nimg, plan->ws, num_features, kQuality, kMinDistance, kEdgeThreshold,
+                         plan->xy.as<double>(), plan->nkp.as<int32_t>(), plan->cap);
+    cudaEventRecord(plan->ev[2], ctx->stream);
+  }
+  if (!rc)
+    rc = launch_orient_describe(ctx, plan->im, nimg, plan->xy.as<double>(), plan->nkp.as<int32_t>(), plan->cap,
+                                rotate ? 1 : 0, plan->ang.as<double>(), plan->desc.as<uint32_t>());
+  cudaEventRecord(plan->ev[3], ctx->stream);
+  if (!rc)
+    rc = launch_match_jobs(ctx, plan->jobs.as<MatchJob>(), count, plan->cap, plan->cap, match_threshold,
+                           match_dist_2_best, plan->cap);
+  cudaEventRecord(plan->ev[4], ctx->stream);
+  plan->timed = true;
+  ctx->stream = saved;
+  return rc;
+}
+
+int vslam_stereo_plan_download(vslam_stereo_plan* plan, int count, double* xy, double* angles, uint32_t* desc,
+                               int32_t* n_kp, int32_t* matches, int32_t* n_matches) {
+  if (!plan) return VSLAM_E_ARG;
+  vslam_ctx* ctx = plan->ctx;
+  if (count < 0 || count > plan->max_pairs) return vs_fail(ctx, VSLAM_E_ARG, "bad pair count");
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t s = plan_stream(plan);
+  const size_t nimg = 2 * (size_t)count, cap = plan->cap;
+  if (xy) VS_CUDA(ctx, cudaMemcpyAsync(xy, plan->xy.p, nimg * cap * 16, cudaMemcpyDeviceToHost, s));
+  if (angles) VS_CUDA(ctx, cudaMemcpyAsync(angles, plan->ang.p, nimg * cap * 8, cudaMemcpyDeviceToHost, s));
+  if (desc) VS_CUDA(ctx, cudaMemcpyAsync(desc, plan->desc.p, nimg * cap * 32, cudaMemcpyDeviceToHost, s));
+  if (n_kp) VS_CUDA(ctx, cudaMemcpyAsync(n_kp, plan->nkp.p, nimg * 4, cudaMemcpyDeviceToHost, s));
+  if (matches) VS_CUDA(ctx, cudaMemcpyAsync(matches, plan->matches.p, (size_t)count * cap * 8, cudaMemcpyDeviceToHost, s));
+  if (n_matches) VS_CUDA(ctx, cudaMemcpyAsync(n_matches, plan->nmatch.p, (size_t)count * 4, cudaMemcpyDeviceToHost, s));
+  VS_CUDA(ctx, cudaStreamSynchronize(s));
+  return VSLAM_OK;
+}
+
+int vslam_stereo_plan_last_ms(vslam_stereo_plan* plan, float* ms) {
+  if (!plan || !ms) return VSLAM_E_ARG;
+  vslam_ctx* ctx = plan->ctx;
+  if (!plan->timed) return vs_fail(ctx, VSLAM_E_ARG, "plan has not run");
+  VS_CUDA(ctx, cudaEventSynchronize(plan->ev[4]));
+  VS_CUDA(ctx, cudaEventElapsedTime(&ms[0], plan->ev[0], plan->ev[4]));
+  for (int i = 0; i < 4; ++i) VS_CUDA(ctx, cudaEventElapsedTime(&ms[1 + i], plan->ev[i], plan->ev[i + 1]));
+  return VSLAM_OK;
+}
+
+// ---- batched front ends on host buffers -------------------------------------------------------------
+
+int vslam_stereo_batch(vslam_ctx* ctx, const uint8_t* images, int count, const vslam_stereo_params* sp, double* xy,
+                       double* angles, uint32_t* desc, int32_t* n_kp, int32_t* matches, int32_t* n_matches, int cap) {
+  if (!ctx) return VSLAM_E_ARG;
+  if (!images || !sp || count < 0 || cap <= 0) return vs_fail(ctx, VSLAM_E_ARG, "bad batch arguments");
+  if (sp->w < 2 || sp->h < 2 || sp->pitch < sp->w || sp->num_features <= 0 || sp->num_features > cap)
+    return vs_fail(ctx, VSLAM_E_ARG, "bad stereo parameters (num_features must be in [1, cap])");
+  if (count == 0) return VSLAM_OK;
+  // Two plans on two streams: while chunk k computes, chunk k+1 uploads and chunk k-1 downloads.
+  const int chunk = count < 128 ? count : 128;
+  vslam_stereo_plan* plans[2] = {nullptr, nullptr};
+  int rc = VSLAM_OK;
+  const int nplans = count > chunk ? 2 : 1;
+  for (int i = 0; i < nplans && !rc; ++i) rc = plan_create_impl(ctx, sp->w, sp->h, chunk, cap, true, &plans[i]);
+  int bad_kp = 0;
+  for (int c0 = 0, k = 0; c0 < count && !rc; c0 += chunk, ++k) {
+    vslam_stereo_plan* p = plans[k % nplans];
+    const int nc = count - c0 < chunk ? count - c0 : chunk;
+    // stream order on p->stream serialises this chunk after the plan's previous download
+    rc = vslam_stereo_plan_upload(p, images + sp->image_stride * 2 * (size_t)c0, nc, sp->pitch, sp->image_stride);
+    if (!rc) rc = vslam_stereo_plan_run(p, nc, sp->num_features, sp->rotate_features, sp->match_threshold, sp->match_dist_2_best);
+    if (rc) break;
+    cudaStream_t s = p->stream;
+    const size_t i0 = 2 * (size_t)c0, ni = 2 * (size_t)nc, cp = cap;
+    if (xy) VS_CUDA(ctx, cudaMemcpyAsync(xy + i0 * cp * 2, p->xy.p, ni * cp * 16, cudaMemcpyDeviceToHost, s));
+    if (angles) VS_CUDA(ctx, cudaMemcpyAsync(angles + i0 * cp, p->ang.p, ni * cp * 8, cudaMemcpyDeviceToHost, s));
+    if (desc) VS_CUDA(ctx, cudaMemcpyAsync(desc + i0 * cp * 8, p->desc.p, ni * cp * 32, cudaMemcpyDeviceToHost, s));
+    if (n_kp) VS_CUDA(ctx, cudaMemcpyAsync(n_kp + i0, p->nkp.p, ni * 4, cudaMemcpyDeviceToHost, s));
+    if (matches) VS_CUDA(ctx, cudaMemcpyAsync(matches + (size_t)c0 * cp * 2, p->matches.p, (size_t)nc * cp * 8, cudaMemcpyDeviceToHost, s));
+    if (n_matches) VS_CUDA(ctx, cudaMemcpyAsync(n_matches + c0, p->nmatch.p, (size_t)nc * 4, cudaMemcpyDeviceToHost, s));
+  }
+  for (int i = 0; i < nplans; ++i)
+    if (plans[i]) cudaStreamSynchronize(plans[i]->stream);
+  if (!rc && n_kp)
+    for (size_t i = 0; i < 2 * (size_t)count; ++i)
+      if (n_kp[i] < 0) bad_kp = n_kp[i];
+  for (int i = 0; i < nplans; ++i) vslam_stereo_plan_destroy(plans[i]);
+  if (!rc && bad_kp) rc = kp_status(ctx, bad_kp);
+  return rc;
+}
+
+int vslam_detect_describe_batch(vslam_ctx* ctx, const uint8_t* images, int count, int w, int h, int pitch,
+                                size_t image_stride, int num_features, int rotate, double* xy, double* angles,
+                                uint32_t* desc, int32_t* n_kp, int cap) {
+  int rc = check_image(ctx, images, w, h, pitch);
+  if (rc) return rc;
+  if (count < 0 || cap <= 0 || num_features <= 0 || num_features > cap || !xy || !angles || !desc || !n_kp)
+    return vs_fail(ctx, VSLAM_E_ARG, "bad batch arguments");
+  if (count == 0) return VSLAM_OK;
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (w < 2 * kEdgeThreshold + 1 || h < 2 * kEdgeThreshold + 1) {
+    for (int i = 0; i < count; ++i) n_kp[i] = 0;
+    return VSLAM_OK;
+  }
+  const int chunk = 256;
+  for (int c0 = 0; c0 < count; c0 += chunk) {
+    const int nc = count - c0 < chunk ? count - c0 : chunk;
+    DevImages im;
+    DetectWorkspace ws;
+    rc = upload_images(ctx, ctx->img, images + image_stride * (size_t)c0, nc, w, h, pitch, image_stride, &im, ctx->stream);
+    if (rc) return rc;
+    rc = prepare_detect_ws(ctx, w, h, nc, ctx->cand, ctx->candcnt, ctx->imgmax, ctx->selws, &ws);
+    if (rc) return rc;
+    VS_CUDA(ctx, ctx->xy.reserve((size_t)nc * cap * 16));
+    VS_CUDA(ctx, ctx->ang.reserve((size_t)nc * cap * 8));
+    VS_CUDA(ctx, ctx->desc.reserve((size_t)nc * cap * 32));
+    VS_CUDA(ctx, ctx->cnt.reserve((size_t)nc * 4));
+    rc = launch_response(ctx, im, nc, ws, nullptr);
+    if (!rc) rc = launch_select(ctx, im, nc, ws, num_features, kQuality, kMinDistance, kEdgeThreshold, ctx->xy.as<double>(), ctx->cnt.as<int32_t>(), cap);
+    if (!rc) rc = launch_orient_describe(ctx, im, nc, ctx->xy.as<double>(), ctx->cnt.as<int32_t>(), cap, rotate ? 1 : 0, ctx->ang.as<double>(), ctx->desc.as<uint32_t>());
+    if (rc) return rc;
+    const size_t cp = cap;
+    VS_CUDA(ctx, cudaMemcpyAsync(xy + (size_t)c0 * cp * 2, ctx->xy.p, (size_t)nc * cp * 16, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaMemcpyAsync(angles + (size_t)c0 * cp, ctx->ang.p, (size_t)nc * cp * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaMemcpyAsync(desc + (size_t)c0 * cp * 8, ctx->desc.p, (size_t)nc * cp * 32, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaMemcpyAsync(n_kp + c0, ctx->cnt.p, (size_t)nc * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < nc; ++i)
+      if ((rc = kp_status(ctx, n_kp[c0 + i]))) return rc;
+  }
+  return VSLAM_OK;
+}
+
+}  // extern "C"
+
+// ---- descriptor store + batched matching --------------------------------------------------------------
+
+struct vslam_desc_store {
+  vslam_ctx* ctx = nullptr;
+  DevBuf desc, offsets, counts;
+  int n_sets = 0;
+  int max_count = 0;
+};
+
+extern "C" {
+
+void vslam_desc_store_destroy(vslam_desc_store* s) {
+  if (!s) return;
+  cudaSetDevice(s->ctx->device);
+  cudaDeviceSynchronize();
+  s->desc.release();
+  s->offsets.release();
+  s->counts.release();
+  delete s;
+}
+
+int vslam_desc_store_create(vslam_ctx* ctx, const uint32_t* desc, const int64_t* offsets, const int32_t* counts,
+                            int n_sets, vslam_desc_store** out) {
+  if (!ctx) return VSLAM_E_ARG;
+  if (!out || !desc || !offsets || !counts || n_sets <= 0) return vs_fail(ctx, VSLAM_E_ARG, "bad store arguments");
+  *out = nullptr;
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  int64_t total = 0;
+  int maxc = 0;
+  for (int i = 0; i < n_sets; ++i) {
+    if (counts[i] < 0 || offsets[i] < 0) return vs_fail(ctx, VSLAM_E_ARG, "negative offset/count");
+    if (offsets[i] + counts[i] > total) total = offsets[i] + counts[i];
+    if (counts[i] > maxc) maxc = counts[i];
+  }
+  vslam_desc_store* s = new (std::nothrow) vslam_desc_store();
+  if (!s) return VSLAM_E_CUDA;
+  s->ctx = ctx; s->n_sets = n_sets; s->max_count = maxc;
+  cudaError_t e = s->desc.reserve((size_t)(total > 0 ? total : 1) * 32);
+  if (e == cudaSuccess) e = s->offsets.reserve((size_t)n_sets * 8);
+  if (e == cudaSuccess) e = s->counts.reserve((size_t)n_sets * 4);
+  if (e == cudaSuccess && total > 0) e = cudaMemcpy(s->desc.p, desc, (size_t)total * 32, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(s->offsets.p, offsets, (size_t)n_sets * 8, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(s->counts.p, counts, (size_t)n_sets * 4, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    ctx->err = std::string("desc store: ") + cudaGetErrorString(e);
+    vslam_desc_store_destroy(s);
+    return VSLAM_E_CUDA;
+  }
+  *out = s;
+  return VSLAM_OK;
+}
+
+int vslam_match_batch(vslam_ctx* ctx, const vslam_desc_store* s, const int32_t* jobs, int n_jobs, int threshold,
+                      double dist_2_best, int32_t* matches, int32_t* n_matches, int cap) {
+  if (!ctx) return VSLAM_E_ARG;
+  if (!s || s->ctx != ctx || !jobs || n_jobs < 0 || cap <= 0) return vs_fail(ctx, VSLAM_E_ARG, "bad batch arguments");
+  if (n_jobs == 0) return VSLAM_OK;
+  if (!match_fits_fused(s->max_count, s->max_count))
+    return vs_fail(ctx, VSLAM_E_LIMIT, "descriptor sets too large for batched matching; use vslam_match");
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  // bounded device footprint: jobs run in chunks whose match slabs are copied back as they finish
+  const size_t per_job = (size_t)cap * 8;
+  int chunk = (int)((size_t)(1u << 30) / per_job);
+  if (chunk < 1) chunk = 1;
+  if (chunk > n_jobs) chunk = n_jobs;
+  VS_CUDA(ctx, ctx->pairs.reserve((size_t)chunk * per_job));
+  VS_CUDA(ctx, ctx->mcnt.reserve((size_t)chunk * 4));
+  VS_CUDA(ctx, ctx->jobs.reserve((size_t)chunk * (sizeof(MatchJob) + 8)));
+  MatchJob* jobs_dev = ctx->jobs.as<MatchJob>();
+  int32_t* ji_dev = reinterpret_cast<int32_t*>(jobs_dev + chunk);
+  float total_ms = 0.f;
+  for (int c0 = 0; c0 < n_jobs; c0 += chunk) {
+    const int nc = n_jobs - c0 < chunk ? n_jobs - c0 : chunk;
+    VS_CUDA(ctx, cudaMemcpyAsync(ji_dev, jobs + 2 * (size_t)c0, (size_t)nc * 8, cudaMemcpyHostToDevice, ctx->stream));
+    VS_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+    int rc = launch_build_store_jobs(ctx, ji_dev, nc, s->desc.as<uint32_t>(), s->offsets.as<int64_t>(),
+                                     s->counts.as<int32_t>(), s->n_sets, ctx->pairs.as<int32_t>(),
+                                     ctx->mcnt.as<int32_t>(), cap, jobs_dev);
+    if (!rc) rc = launch_match_jobs(ctx, jobs_dev, nc, s->max_count, s->max_count, threshold, dist_2_best, cap);
+    if (rc) return rc;
+    VS_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+    if (matches) VS_CUDA(ctx, cudaMemcpyAsync(matches + (size_t)c0 * cap * 2, ctx->pairs.p, (size_t)nc * per_job, cudaMemcpyDeviceToHost, ctx->stream));
+    if (n_matches) VS_CUDA(ctx, cudaMemcpyAsync(n_matches + c0, ctx->mcnt.p, (size_t)nc * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    float ms = 0.f;
+    VS_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
+    total_ms += ms;
+  }
+  ctx->last_match_ms = total_ms;
+  return VSLAM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,117 @@
+// common.cuh -- context, workspace and error plumbing shared by the kernels' host launchers.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+
+#include "../../include/visnav_b200.h"
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  // grow-only scratch; contents are not preserved
+  cudaError_t reserve(size_t need) {
+    if (need <= bytes) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+    size_t want = need + need / 4 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) bytes = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+  }
+  template <class T>
+  T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct vslam_ctx {
+  int device = 0;
+  int num_sms = 0;
+  cudaStream_t stream = nullptr;
+  cudaStream_t copy_stream[2] = {nullptr, nullptr};
+  cudaEvent_t ev[8] = {};
+  std::string err;
+  int fp_contract = 1;
+  int match_csa = 1;
+  long long launches = 0;
+  float last_match_ms = 0.f;
+  // scratch for the single-call entry points
+  DevBuf img, xy, ang, desc, cnt, lam;
+  DevBuf cand, candcnt, imgmax, selws;
+  DevBuf d1, d2, pairs, mcnt, rowpart, colstat, jobs;
+  void* pinned = nullptr;  // small pinned staging block for counts
+};
+
+#define VS_CUDA(ctx, call)                                                              \
+  do {                                                                                  \
+    cudaError_t e_ = (call);                                                            \
+    if (e_ != cudaSuccess) {                                                            \
+      char b_[512];                                                                     \
+      snprintf(b_, sizeof b_, "%s:%d: %s: %s", __FILE__, __LINE__, #call,               \
+               cudaGetErrorString(e_));                                                 \
+      (ctx)->err = b_;                                                                  \
+      return VSLAM_E_CUDA;                                                              \
+    }                                                                                   \
+  } while (0)
+
+static inline int vs_fail(vslam_ctx* ctx, int code, const char* msg) {
+  if (ctx) ctx->err = msg;
+  return code;
+}
+
+// ---- image set on the device: count images of h rows, pitch (multiple of 128) bytes apart ----
+struct DevImages {
+  const uint8_t* base;
+  int w, h, pitch;
+  size_t stride;  // bytes between images (>= pitch*h, multiple of 128)
+};
+
+// ---- launchers (each file's kernels stay private to it) ----
+// detect.cu
+struct DetectWorkspace {
+  uint64_t* cand;      // [count][cand_cap] keys (float bits << 32 | pixel index)
+  uint32_t* cand_cnt;  // [count]
+  uint32_t* img_max;   // [count] ordered-int encoding of the max response
+  int cand_cap;
+  uint8_t* sel_ws;     // global fallback workspace for select, [count][sel_ws_stride]
+  size_t sel_ws_stride;
+};
+size_t detect_sel_ws_bytes(int w, int h, int cand_cap, int cell);
+int launch_response(vslam_ctx* ctx, const DevImages& im, int count, const DetectWorkspace& ws,
+                    float* lam_out /*optional, [count][h][w]*/);
+int launch_select(vslam_ctx* ctx, const DevImages& im, int count, const DetectWorkspace& ws,
+                  int num_features, double quality, int min_distance, int border, double* xy,
+                  int32_t* n_kp, int cap);
+// describe.cu
+int launch_orient_describe(vslam_ctx* ctx, const DevImages& im, int count, const double* xy,
+                           const int32_t* n_kp, int cap, int mode_angles /*0: zero, 1: compute, 2: given*/,
+                           double* angles, uint32_t* desc /*nullable*/);
+// match.cu
+struct MatchJob {
+  const uint32_t* d1;
+  const uint32_t* d2;
+  const int32_t* n1p;  // device counts (used when non-null)
+  const int32_t* n2p;
+  int n1, n2;
+  int32_t* pairs;  // [cap][2]
+  int32_t* count;  // out
+};
+int launch_match_jobs(vslam_ctx* ctx, const MatchJob* jobs_dev, int n_jobs, int max_n1, int max_n2,
+                      int threshold, double ratio, int cap);
+int launch_match_large(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_t* d2, int n2,
+                       int threshold, double ratio, int32_t* pairs, int32_t* count, int cap,
+                       int32_t* best2_out /*nullable: [n1][3], skips the match predicate*/);
+bool match_fits_fused(int n1, int n2);
+// jobs_i2: [n_jobs][2] set indices into (offsets, counts); fills MatchJob records on the device
+int launch_build_store_jobs(vslam_ctx* ctx, const int32_t* jobs_i2, int n_jobs, const uint32_t* desc,
+                            const int64_t* offsets, const int32_t* counts, int n_sets, int32_t* pairs,
+                            int32_t* out_counts, int cap, MatchJob* out);
+int launch_popc_peak(vslam_ctx* ctx, double* popc_per_s);

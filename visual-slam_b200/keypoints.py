@@ -1,0 +1,402 @@
+"""Host-side mirror of the reference's operator interface for the hot path, over the C ABI.
+
+Same names and argument meaning as /root/reference/include/visnav/keypoints.h:
+  detectKeypoints(img, kd, num_features)                       :133-150
+  computeAngles(img, kd, rotate_features)                      :152-189
+  computeDescriptors(img, kd)                                  :191-221
+  detectKeypointsAndDescriptors(img, kd, num_features, rotate) :223-229
+  matchDescriptors(desc1, desc2, matches, threshold, dist_2_best) :323-369
+`KeypointsData` mirrors include/visnav/common_types.h:111-122 with numpy arrays in place of the
+std::vectors (corners N x 2 float64, corner_angles N float64, corner_descriptors N x 8 uint32 =
+std::bitset<256> words).  `matches` is a python list that is cleared and refilled with (id1, id2)
+tuples, like the reference's std::vector<std::pair<int,int>>.
+
+Everything here calls libvisnav_b200.so through ctypes; there is no CPU implementation.  A missing
+library or GPU raises VslamError.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+PATCH_SIZE = 31          # keypoints.h:49
+HALF_PATCH_SIZE = 15     # keypoints.h:50
+EDGE_THRESHOLD = 19      # keypoints.h:51
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+ABI_SYMBOLS = [
+    "vslam_create", "vslam_destroy", "vslam_last_error", "vslam_set_option", "vslam_stream", "vslam_sync",
+    "vslam_launch_count", "vslam_host_alloc", "vslam_host_free", "vslam_detect", "vslam_angles",
+    "vslam_describe", "vslam_detect_describe", "vslam_match", "vslam_best2", "vslam_response",
+    "vslam_detect_describe_batch", "vslam_stereo_batch", "vslam_stereo_plan_create",
+    "vslam_stereo_plan_destroy", "vslam_stereo_plan_upload", "vslam_stereo_plan_run",
+    "vslam_stereo_plan_download", "vslam_stereo_plan_last_ms", "vslam_desc_store_create",
+    "vslam_desc_store_destroy", "vslam_match_batch", "vslam_last_match_ms", "vslam_popc_peak",
+]
+
+VSLAM_OPT_FP_CONTRACT = 1
+VSLAM_OPT_MATCH_CSA = 2
+
+
+class VslamError(RuntimeError):
+    pass
+
+
+class StereoParams(C.Structure):
+    _fields_ = [("w", C.c_int), ("h", C.c_int), ("pitch", C.c_int), ("image_stride", C.c_size_t),
+                ("num_features", C.c_int), ("rotate_features", C.c_int), ("match_threshold", C.c_int),
+                ("match_dist_2_best", C.c_double)]
+
+
+def lib_path():
+    return os.path.join(_HERE, "csrc", "libvisnav_b200.so")
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen the C-ABI library and declare its prototypes.  No GPU needed for this."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not os.path.exists(path):
+        raise VslamError("libvisnav_b200.so is not built (run __graft_entry__.build()); there is no CPU fallback")
+    L = C.CDLL(path)
+    vp, i, d, sz = C.c_void_p, C.c_int, C.c_double, C.c_size_t
+    L.vslam_create.argtypes = [i, C.POINTER(vp)]
+    L.vslam_destroy.argtypes = [vp]
+    L.vslam_destroy.restype = None
+    L.vslam_last_error.argtypes = [vp]
+    L.vslam_last_error.restype = C.c_char_p
+    L.vslam_set_option.argtypes = [vp, i, i]
+    L.vslam_stream.argtypes = [vp]
+    L.vslam_stream.restype = vp
+    L.vslam_sync.argtypes = [vp]
+    L.vslam_launch_count.argtypes = [vp]
+    L.vslam_launch_count.restype = C.c_longlong
+    L.vslam_host_alloc.argtypes = [sz]
+    L.vslam_host_alloc.restype = vp
+    L.vslam_host_free.argtypes = [vp]
+    L.vslam_host_free.restype = None
+    L.vslam_detect.argtypes = [vp, vp, i, i, i, i, vp, i, C.POINTER(i)]
+    L.vslam_angles.argtypes = [vp, vp, i, i, i, vp, i, i, vp]
+    L.vslam_describe.argtypes = [vp, vp, i, i, i, vp, vp, i, vp]
+    L.vslam_detect_describe.argtypes = [vp, vp, i, i, i, i, i, vp, vp, vp, i, C.POINTER(i)]
+    L.vslam_match.argtypes = [vp, vp, i, vp, i, i, d, vp, i, C.POINTER(i)]
+    L.vslam_best2.argtypes = [vp, vp, i, vp, i, vp]
+    L.vslam_response.argtypes = [vp, vp, i, i, i, vp]
+    L.vslam_detect_describe_batch.argtypes = [vp, vp, i, i, i, i, sz, i, i, vp, vp, vp, vp, i]
+    L.vslam_stereo_batch.argtypes = [vp, vp, i, C.POINTER(StereoParams), vp, vp, vp, vp, vp, vp, i]
+    L.vslam_stereo_plan_create.argtypes = [vp, i, i, i, i, C.POINTER(vp)]
+    L.vslam_stereo_plan_destroy.argtypes = [vp]
+    L.vslam_stereo_plan_destroy.restype = None
+    L.vslam_stereo_plan_upload.argtypes = [vp, vp, i, i, sz]
+    L.vslam_stereo_plan_run.argtypes = [vp, i, i, i, i, d]
+    L.vslam_stereo_plan_download.argtypes = [vp, i, vp, vp, vp, vp, vp, vp]
+    L.vslam_stereo_plan_last_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    L.vslam_desc_store_create.argtypes = [vp, vp, vp, vp, i, C.POINTER(vp)]
+    L.vslam_desc_store_destroy.argtypes = [vp]
+    L.vslam_desc_store_destroy.restype = None
+    L.vslam_match_batch.argtypes = [vp, vp, vp, i, i, d, vp, vp, i]
+    L.vslam_last_match_ms.argtypes = [vp]
+    L.vslam_last_match_ms.restype = C.c_float
+    L.vslam_popc_peak.argtypes = [vp, C.POINTER(d)]
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _img(img):
+    """(array kept alive, w, h, pitch) of a 2-D uint8 image; rows may be strided (pitch)."""
+    img = np.asarray(img)
+    if img.dtype != np.uint8 or img.ndim != 2:
+        raise VslamError("image must be a 2-D uint8 array")
+    if img.strides[1] != 1 or img.strides[0] < img.shape[1]:
+        img = np.ascontiguousarray(img)
+    return img, img.shape[1], img.shape[0], img.strides[0]
+
+
+class KeypointsData:
+    """include/visnav/common_types.h:111-122."""
+
+    def __init__(self):
+        self.corners = np.zeros((0, 2), np.float64)
+        self.corner_angles = np.zeros(0, np.float64)
+        self.corner_descriptors = np.zeros((0, 8), np.uint32)
+
+
+class Context:
+    """One vslam_ctx (one GPU, one host thread)."""
+
+    def __init__(self, device=0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.vslam_create(int(device), C.byref(h))
+        if rc != 0 or not h:
+            raise VslamError("vslam_create(device=%d) failed (%d): no usable sm_100 GPU; there is no CPU fallback"
+                             % (device, rc))
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.vslam_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise VslamError("vslam error %d: %s" % (rc, self.lib.vslam_last_error(self.h).decode()))
+
+    def set_option(self, opt, value):
+        self._check(self.lib.vslam_set_option(self.h, opt, int(value)))
+
+    def stream(self):
+        return self.lib.vslam_stream(self.h)
+
+    def sync(self):
+        self._check(self.lib.vslam_sync(self.h))
+
+    def launch_count(self):
+        return int(self.lib.vslam_launch_count(self.h))
+
+    # ---- single image ----------------------------------------------------------------------
+    def detect(self, img, num_features):
+        img, w, h, pitch = _img(img)
+        cap = num_features if num_features > 0 else w * h
+        xy = np.empty((max(cap, 1), 2), np.float64)
+        n = C.c_int(0)
+        self._check(self.lib.vslam_detect(self.h, _ptr(img), w, h, pitch, int(num_features), _ptr(xy), cap, C.byref(n)))
+        return xy[:n.value].copy()
+
+    def angles(self, img, xy, rotate=True):
+        img, w, h, pitch = _img(img)
+        xy = np.ascontiguousarray(xy, np.float64).reshape(-1, 2)
+        out = np.empty(len(xy), np.float64)
+        self._check(self.lib.vslam_angles(self.h, _ptr(img), w, h, pitch, _ptr(xy), len(xy), int(bool(rotate)), _ptr(out)))
+        return out
+
+    def describe(self, img, xy, angles):
+        img, w, h, pitch = _img(img)
+        xy = np.ascontiguousarray(xy, np.float64).reshape(-1, 2)
+        angles = np.ascontiguousarray(angles, np.float64)
+        if len(angles) != len(xy):
+            raise VslamError("corners and corner_angles differ in length")
+        out = np.empty((len(xy), 8), np.uint32)
+        self._check(self.lib.vslam_describe(self.h, _ptr(img), w, h, pitch, _ptr(xy), _ptr(angles), len(xy), _ptr(out)))
+        return out
+
+    def detect_describe(self, img, num_features, rotate=True):
+        img, w, h, pitch = _img(img)
+        cap = num_features if num_features > 0 else w * h
+        xy = np.empty((max(cap, 1), 2), np.float64)
+        ang = np.empty(max(cap, 1), np.float64)
+        desc = np.empty((max(cap, 1), 8), np.uint32)
+        n = C.c_int(0)
+        self._check(self.lib.vslam_detect_describe(self.h, _ptr(img), w, h, pitch, int(num_features), int(bool(rotate)),
+                                                   _ptr(xy), _ptr(ang), _ptr(desc), cap, C.byref(n)))
+        n = n.value
+        return xy[:n].copy(), ang[:n].copy(), desc[:n].copy()
+
+    def response(self, img):
+        img, w, h, pitch = _img(img)
+        lam = np.empty((h, w), np.float32)
+        self._check(self.lib.vslam_response(self.h, _ptr(img), w, h, pitch, _ptr(lam)))
+        return lam
+
+    def match(self, d1, d2, threshold=70, dist_2_best=1.2, cap=None):
+        d1 = np.ascontiguousarray(d1, np.uint32).reshape(-1, 8)
+        d2 = np.ascontiguousarray(d2, np.uint32).reshape(-1, 8)
+        if cap is None:
+            cap = max(1, min(len(d1), len(d2)))
+        pairs = np.empty((cap, 2), np.int32)
+        n = C.c_int(0)
+        self._check(self.lib.vslam_match(self.h, _ptr(d1), len(d1), _ptr(d2), len(d2), int(threshold),
+                                         float(dist_2_best), _ptr(pairs), cap, C.byref(n)))
+        return pairs[:n.value].copy()
+
+    def best2(self, q, db):
+        q = np.ascontiguousarray(q, np.uint32).reshape(-1, 8)
+        db = np.ascontiguousarray(db, np.uint32).reshape(-1, 8)
+        out = np.empty((len(q), 3), np.int32)
+        self._check(self.lib.vslam_best2(self.h, _ptr(q), len(q), _ptr(db), len(db), _ptr(out)))
+        return out
+
+    def last_match_ms(self):
+        return float(self.lib.vslam_last_match_ms(self.h))
+
+    def popc_peak(self):
+        v = C.c_double(0)
+        self._check(self.lib.vslam_popc_peak(self.h, C.byref(v)))
+        return v.value
+
+    # ---- batches ----------------------------------------------------------------------------
+    def detect_describe_batch(self, images, num_features, rotate=True, cap=None):
+        images = np.ascontiguousarray(images, np.uint8)
+        count, h, w = images.shape
+        cap = cap or num_features
+        xy = np.empty((count, cap, 2), np.float64)
+        ang = np.empty((count, cap), np.float64)
+        desc = np.empty((count, cap, 8), np.uint32)
+        nkp = np.empty(count, np.int32)
+        self._check(self.lib.vslam_detect_describe_batch(self.h, _ptr(images), count, w, h, w, w * h, int(num_features),
+                                                         int(bool(rotate)), _ptr(xy), _ptr(ang), _ptr(desc), _ptr(nkp), cap))
+        return xy, ang, desc, nkp
+
+    def stereo_batch(self, images, num_features=1500, rotate=True, threshold=70, dist_2_best=1.2, cap=None,
+                     out=None):
+        """images: [count, 2, h, w] uint8 (C-contiguous; pinned memory makes the copies asynchronous).
+        Returns dict(xy, angles, desc, n_kp, matches, n_matches) of fixed-stride slabs."""
+        images = np.asarray(images)
+        if images.dtype != np.uint8 or images.ndim != 4 or images.shape[1] != 2 or not images.flags.c_contiguous:
+            raise VslamError("images must be a C-contiguous [count, 2, h, w] uint8 array")
+        count, _, h, w = images.shape
+        cap = cap or num_features
+        if out is None:
+            out = dict(xy=np.empty((count * 2, cap, 2), np.float64), angles=np.empty((count * 2, cap), np.float64),
+                       desc=np.empty((count * 2, cap, 8), np.uint32), n_kp=np.empty(count * 2, np.int32),
+                       matches=np.empty((count, cap, 2), np.int32), n_matches=np.empty(count, np.int32))
+        p = StereoParams(w, h, w, w * h, int(num_features), int(bool(rotate)), int(threshold), float(dist_2_best))
+        self._check(self.lib.vslam_stereo_batch(self.h, _ptr(images), count, C.byref(p), _ptr(out.get("xy")),
+                                                _ptr(out.get("angles")), _ptr(out.get("desc")), _ptr(out.get("n_kp")),
+                                                _ptr(out.get("matches")), _ptr(out.get("n_matches")), cap))
+        return out
+
+    def match_batch(self, store, jobs, threshold=70, dist_2_best=1.2, cap=None, want_matches=True):
+        jobs = np.ascontiguousarray(jobs, np.int32).reshape(-1, 2)
+        cap = cap or store.max_count
+        n = len(jobs)
+        matches = np.empty((n, cap, 2), np.int32) if want_matches else None
+        counts = np.empty(n, np.int32)
+        self._check(self.lib.vslam_match_batch(self.h, store.h, _ptr(jobs), n, int(threshold), float(dist_2_best),
+                                               _ptr(matches), _ptr(counts), cap))
+        return matches, counts
+
+
+class DescStore:
+    """Device-resident descriptor sets (keyframes) for Context.match_batch."""
+
+    def __init__(self, ctx, sets):
+        """sets: [n_sets, n, 8] uint32 array, or a list of [n_k, 8] arrays."""
+        self.ctx = ctx
+        if isinstance(sets, np.ndarray) and sets.ndim == 3:
+            flat = np.ascontiguousarray(sets, np.uint32).reshape(-1, 8)
+            counts = np.full(sets.shape[0], sets.shape[1], np.int32)
+        else:
+            sets = [np.ascontiguousarray(s, np.uint32).reshape(-1, 8) for s in sets]
+            counts = np.array([len(s) for s in sets], np.int32)
+            flat = np.concatenate(sets) if len(sets) else np.zeros((0, 8), np.uint32)
+        offsets = np.concatenate([[0], np.cumsum(counts[:-1], dtype=np.int64)]).astype(np.int64)
+        self.max_count = int(counts.max()) if len(counts) else 0
+        h = C.c_void_p()
+        ctx._check(ctx.lib.vslam_desc_store_create(ctx.h, _ptr(flat), _ptr(offsets), _ptr(counts), len(counts), C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.ctx.lib.vslam_desc_store_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class StereoPlan:
+    """Upload / run / download split of the stereo front end (bench.py times run() alone)."""
+
+    def __init__(self, ctx, w, h, max_pairs, cap):
+        self.ctx, self.w, self.h, self.max_pairs, self.cap = ctx, w, h, max_pairs, cap
+        h_ = C.c_void_p()
+        ctx._check(ctx.lib.vslam_stereo_plan_create(ctx.h, w, h, max_pairs, cap, C.byref(h_)))
+        self.p = h_
+
+    def upload(self, images):
+        images = np.asarray(images)
+        assert images.dtype == np.uint8 and images.flags.c_contiguous and images.shape[1:] == (2, self.h, self.w)
+        self.ctx._check(self.ctx.lib.vslam_stereo_plan_upload(self.p, _ptr(images), images.shape[0], self.w, self.w * self.h))
+
+    def run(self, count, num_features=1500, rotate=True, threshold=70, dist_2_best=1.2):
+        self.ctx._check(self.ctx.lib.vslam_stereo_plan_run(self.p, count, int(num_features), int(bool(rotate)),
+                                                           int(threshold), float(dist_2_best)))
+
+    def download(self, count):
+        cap = self.cap
+        out = dict(xy=np.empty((count * 2, cap, 2), np.float64), angles=np.empty((count * 2, cap), np.float64),
+                   desc=np.empty((count * 2, cap, 8), np.uint32), n_kp=np.empty(count * 2, np.int32),
+                   matches=np.empty((count, cap, 2), np.int32), n_matches=np.empty(count, np.int32))
+        self.ctx._check(self.ctx.lib.vslam_stereo_plan_download(self.p, count, _ptr(out["xy"]), _ptr(out["angles"]),
+                                                                _ptr(out["desc"]), _ptr(out["n_kp"]), _ptr(out["matches"]),
+                                                                _ptr(out["n_matches"])))
+        return out
+
+    def last_ms(self):
+        ms = (C.c_float * 5)()
+        self.ctx._check(self.ctx.lib.vslam_stereo_plan_last_ms(self.p, ms))
+        return list(ms)
+
+    def close(self):
+        if getattr(self, "p", None):
+            self.ctx.lib.vslam_stereo_plan_destroy(self.p)
+            self.p = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_default = None
+
+
+def default_context():
+    global _default
+    if _default is None:
+        _default = Context(int(os.environ.get("LOCAL_RANK", "0")))
+    return _default
+
+
+# ---- the reference's free functions ------------------------------------------------------------
+
+def detectKeypoints(img_raw, kd, num_features):
+    """keypoints.h:133-150: clears kd, fills kd.corners."""
+    kd.corners = default_context().detect(img_raw, num_features)
+    kd.corner_angles = np.zeros(0, np.float64)
+    kd.corner_descriptors = np.zeros((0, 8), np.uint32)
+
+
+def computeAngles(img_raw, kd, rotate_features):
+    """keypoints.h:152-189."""
+    kd.corner_angles = default_context().angles(img_raw, kd.corners, rotate_features)
+
+
+def computeDescriptors(img_raw, kd):
+    """keypoints.h:191-221."""
+    kd.corner_descriptors = default_context().describe(img_raw, kd.corners, kd.corner_angles)
+
+
+def detectKeypointsAndDescriptors(img_raw, kd, num_features, rotate_features):
+    """keypoints.h:223-229 -- one device round trip instead of three."""
+    kd.corners, kd.corner_angles, kd.corner_descriptors = default_context().detect_describe(
+        img_raw, num_features, rotate_features)
+
+
+def matchDescriptors(corner_descriptors_1, corner_descriptors_2, matches, threshold, dist_2_best):
+    """keypoints.h:323-369: matches.clear(), then (id1, id2) in ascending id1."""
+    del matches[:]
+    pairs = default_context().match(corner_descriptors_1, corner_descriptors_2, threshold, dist_2_best)
+    matches.extend((int(a), int(b)) for a, b in pairs)
