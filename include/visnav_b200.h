@@ -152,6 +152,10 @@ int vslam_match_batch(vslam_ctx* ctx, const vslam_desc_store* s, const int32_t* 
 float vslam_last_match_ms(vslam_ctx* ctx);
 
 /* ---- measurement helpers --------------------------------------------------------------- */
+/* CUDA events on vslam_stream(ctx): record event `slot` (0..3); elapsed ms between two recorded
+ * slots (synchronises on the later one). */
+int vslam_event_record(vslam_ctx* ctx, int slot);
+int vslam_event_elapsed_ms(vslam_ctx* ctx, int slot_a, int slot_b, float* ms);
 /* Register-only POPC throughput microbenchmark: popc.b32 instructions per second (thread
  * level) sustained over all SMs -- the measured denominator of the matching roofline. */
 int vslam_popc_peak(vslam_ctx* ctx, double* popc_per_s);

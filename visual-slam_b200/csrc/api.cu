@@ -103,6 +103,10 @@ void vslam_destroy(vslam_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  for (int i = 0; i < 2; ++i) {
+    if (ctx->batch_plans[i]) vslam_stereo_plan_destroy(ctx->batch_plans[i]);
+    ctx->batch_plans[i] = nullptr;
+  }
   DevBuf* bufs[] = {&ctx->img, &ctx->xy, &ctx->ang, &ctx->desc, &ctx->cnt, &ctx->lam, &ctx->cand, &ctx->candcnt,
                     &ctx->imgmax, &ctx->selws, &ctx->d1, &ctx->d2, &ctx->pairs, &ctx->mcnt, &ctx->rowpart,
                     &ctx->colstat, &ctx->jobs};
@@ -347,6 +351,20 @@ int vslam_best2(vslam_ctx* ctx, const uint32_t* q, int nq, const uint32_t* db, i
 
 float vslam_last_match_ms(vslam_ctx* ctx) { return ctx ? ctx->last_match_ms : 0.f; }
 
+int vslam_event_record(vslam_ctx* ctx, int slot) {
+  if (!ctx || slot < 0 || slot > 3) return VSLAM_E_ARG;
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  VS_CUDA(ctx, cudaEventRecord(ctx->ev[4 + slot], ctx->stream));
+  return VSLAM_OK;
+}
+
+int vslam_event_elapsed_ms(vslam_ctx* ctx, int slot_a, int slot_b, float* ms) {
+  if (!ctx || !ms || slot_a < 0 || slot_a > 3 || slot_b < 0 || slot_b > 3) return VSLAM_E_ARG;
+  VS_CUDA(ctx, cudaEventSynchronize(ctx->ev[4 + slot_b]));
+  VS_CUDA(ctx, cudaEventElapsedTime(ms, ctx->ev[4 + slot_a], ctx->ev[4 + slot_b]));
+  return VSLAM_OK;
+}
+
 int vslam_popc_peak(vslam_ctx* ctx, double* popc_per_s) {
   if (!ctx || !popc_per_s) return VSLAM_E_ARG;
   VS_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -535,7 +553,15 @@ int vslam_stereo_batch(vslam_ctx* ctx, const uint8_t* images, int count, const v
   vslam_stereo_plan* plans[2] = {nullptr, nullptr};
   int rc = VSLAM_OK;
   const int nplans = count > chunk ? 2 : 1;
-  for (int i = 0; i < nplans && !rc; ++i) rc = plan_create_impl(ctx, sp->w, sp->h, chunk, cap, true, &plans[i]);
+  for (int i = 0; i < nplans && !rc; ++i) {
+    vslam_stereo_plan*& cp = ctx->batch_plans[i];
+    if (cp && (cp->w != sp->w || cp->h != sp->h || cp->cap != cap || cp->max_pairs < chunk)) {
+      vslam_stereo_plan_destroy(cp);
+      cp = nullptr;
+    }
+    if (!cp) rc = plan_create_impl(ctx, sp->w, sp->h, chunk, cap, true, &cp);
+    plans[i] = cp;
+  }
   int bad_kp = 0;
   for (int c0 = 0, k = 0; c0 < count && !rc; c0 += chunk, ++k) {
     vslam_stereo_plan* p = plans[k % nplans];
@@ -558,7 +584,6 @@ int vslam_stereo_batch(vslam_ctx* ctx, const uint8_t* images, int count, const v
   if (!rc && n_kp)
     for (size_t i = 0; i < 2 * (size_t)count; ++i)
       if (n_kp[i] < 0) bad_kp = n_kp[i];
-  for (int i = 0; i < nplans; ++i) vslam_stereo_plan_destroy(plans[i]);
   if (!rc && bad_kp) rc = kp_status(ctx, bad_kp);
   return rc;
 }

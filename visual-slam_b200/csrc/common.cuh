@@ -48,6 +48,8 @@ struct vslam_ctx {
   DevBuf cand, candcnt, imgmax, selws;
   DevBuf d1, d2, pairs, mcnt, rowpart, colstat, jobs;
   void* pinned = nullptr;  // small pinned staging block for counts
+  // pipeline plans of vslam_stereo_batch, kept between calls (same geometry -> no reallocation)
+  struct vslam_stereo_plan* batch_plans[2] = {nullptr, nullptr};
 };
 
 #define VS_CUDA(ctx, call)                                                              \

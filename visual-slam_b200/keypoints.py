@@ -33,6 +33,7 @@ ABI_SYMBOLS = [
     "vslam_stereo_plan_destroy", "vslam_stereo_plan_upload", "vslam_stereo_plan_run",
     "vslam_stereo_plan_download", "vslam_stereo_plan_last_ms", "vslam_desc_store_create",
     "vslam_desc_store_destroy", "vslam_match_batch", "vslam_last_match_ms", "vslam_popc_peak",
+    "vslam_event_record", "vslam_event_elapsed_ms",
 ]
 
 VSLAM_OPT_FP_CONTRACT = 1
@@ -104,6 +105,8 @@ def load_library():
     L.vslam_last_match_ms.argtypes = [vp]
     L.vslam_last_match_ms.restype = C.c_float
     L.vslam_popc_peak.argtypes = [vp, C.POINTER(d)]
+    L.vslam_event_record.argtypes = [vp, i]
+    L.vslam_event_elapsed_ms.argtypes = [vp, i, i, C.POINTER(C.c_float)]
     _lib = L
     return L
 
@@ -167,6 +170,26 @@ class Context:
 
     def sync(self):
         self._check(self.lib.vslam_sync(self.h))
+
+    def event_record(self, slot):
+        self._check(self.lib.vslam_event_record(self.h, slot))
+
+    def event_elapsed_ms(self, a, b):
+        ms = C.c_float(0)
+        self._check(self.lib.vslam_event_elapsed_ms(self.h, a, b, C.byref(ms)))
+        return ms.value
+
+    def host_array(self, shape, dtype):
+        """numpy array over pinned host memory (cudaMallocHost); freed with the returned handle's .free()."""
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = self.lib.vslam_host_alloc(max(n, 1))
+        if not p:
+            raise VslamError("vslam_host_alloc(%d) failed" % n)
+        buf = (C.c_uint8 * max(n, 1)).from_address(p)
+        arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+        self._pinned = getattr(self, "_pinned", [])
+        self._pinned.append(p)
+        return arr
 
     def launch_count(self):
         return int(self.lib.vslam_launch_count(self.h))
