@@ -1,0 +1,58 @@
+#!/usr/bin/env python3
+"""Summarise ncu outputs brought back in gpurun_out/ into small text files for profiles/.
+  ncu_summary.py launches <launches.csv>            per-kernel launch count, total time, share
+  ncu_summary.py raw <report.ncu-rep> [metric ...]  selected raw metrics of every captured launch
+"""
+import collections
+import csv
+import subprocess
+import sys
+
+DEFAULT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+           "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+           "smsp__issue_active.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.pct_of_peak_sustained_active",
+           "launch__registers_per_thread", "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem",
+           "smsp__inst_executed.sum", "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active",
+           "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
+           "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
+           "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
+           "sm__pipe_xu_cycles_active.avg.pct_of_peak_sustained_active",
+           "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+           "l1tex__data_bank_conflicts_pipe_lsu.sum", "lts__t_bytes.sum"]
+
+
+def launches(path):
+    rows = list(csv.reader(open(path)))
+    hdr = next(i for i, r in enumerate(rows) if r and r[0] == "ID")
+    H = rows[hdr]
+    ki, vi = H.index("Kernel Name"), H.index("Metric Value")
+    agg = collections.OrderedDict()
+    for r in rows[hdr + 1:]:
+        if len(r) <= vi:
+            continue
+        name = r[ki].split("(")[0].split("::")[-1]
+        a = agg.setdefault(name, [0, 0.0])
+        a[0] += 1
+        a[1] += float(r[vi].replace(",", ""))
+    tot = sum(v[1] for v in agg.values())
+    print("# per-launch gpu__time_duration.sum under ncu (cold-cache, serialised): compare SHARES")
+    for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        print("%-36s launches=%5d total=%10.3f ms mean=%9.3f us share=%5.1f%%" % (k, v[0], v[1] / 1e6, v[1] / v[0] / 1e3, 100 * v[1] / tot))
+
+
+def raw(path, metrics):
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    H, U = rows[0], rows[1]
+    for r in rows[2:]:
+        print("## kernel:", r[H.index("Kernel Name")].split("(")[0], " grid", r[H.index("Grid Size")], " block", r[H.index("Block Size")])
+        for m in metrics:
+            if m in H:
+                print("%-70s %-14s %s" % (m, U[H.index(m)], r[H.index(m)]))
+
+
+if __name__ == "__main__":
+    if sys.argv[1] == "launches":
+        launches(sys.argv[2])
+    else:
+        raw(sys.argv[2], sys.argv[3:] or DEFAULT)

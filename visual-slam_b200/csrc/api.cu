@@ -13,7 +13,9 @@ constexpr double kQuality = 0.01;
 constexpr int kEdgeThreshold = 19;   // keypoints.h:50 EDGE_THRESHOLD
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-inline int dev_pitch(int w) { return (int)align_up((size_t)w, 128); }
+// Device rows are `w` bytes apart when that keeps every row 16-byte aligned (TMA stride rule, 128-bit
+// patch loads): a dense host image then uploads as ONE linear DMA instead of a slow strided 2-D copy.
+inline int dev_pitch(int w) { return (w % 16 == 0) ? w : (int)align_up((size_t)w, 128); }
 inline int cand_capacity(int w, int h) { return (w * h) / 4 + 1024; }
 
 // Image set in ctx scratch + detection workspace for `count` images.
@@ -46,7 +48,9 @@ int upload_images(vslam_ctx* ctx, DevBuf& buf, const uint8_t* host, int count, i
   VS_CUDA(ctx, buf.reserve(ds * count));
   im->base = buf.as<uint8_t>();
   im->w = w; im->h = h; im->pitch = dp; im->stride = ds;
-  if (count > 1 && image_stride == (size_t)pitch * h) {
+  if (pitch == dp && (count == 1 || image_stride == ds)) {
+    VS_CUDA(ctx, cudaMemcpyAsync(buf.p, host, ds * count, cudaMemcpyHostToDevice, stream));
+  } else if (count > 1 && image_stride == (size_t)pitch * h) {
     // images are back to back: one strided copy of count*h rows
     VS_CUDA(ctx, cudaMemcpy2DAsync(buf.p, dp, host, pitch, w, (size_t)h * count, cudaMemcpyHostToDevice, stream));
   } else {
