@@ -1,0 +1,53 @@
+"""The C++ drop-in header (include/visnav/keypoints.h) compiled against stub Pangolin / common_types
+headers and driven like the reference drives it (slam.cpp:1125-1143)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "tests", "cpp", "test_dropin")
+
+
+def _build():
+    cmd = ["g++", "-std=c++14", "-O2", "-I", os.path.join(ROOT, "tests", "cpp", "stubs"), "-I", os.path.join(ROOT, "include"),
+           "-o", EXE, os.path.join(ROOT, "tests", "cpp", "test_dropin.cpp"), "-L", os.path.join(ROOT, "visual-slam_b200", "csrc"),
+           "-lvisnav_b200", "-Wl,-rpath," + os.path.join(ROOT, "visual-slam_b200", "csrc")]
+    subprocess.run(cmd, check=True)
+
+
+def test_dropin_header_compiles_and_fails_loudly_without_gpu():
+    import torch
+    _build()
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    p = subprocess.run([EXE, "/dev/null", "/dev/null", "64", "64"], capture_output=True, text=True)
+    assert p.returncode in (2, 3)      # unreadable input or "no usable sm_100 GPU": never a silent CPU result
+
+
+@pytest.mark.gpu
+def test_dropin_header_matches_oracle(tmp_path, oracle_port):
+    import visnav_b200  # noqa: F401
+    from visnav_b200 import workloads as wl
+    _build()
+    left, right = wl.synth_stereo_pair(11)
+    left.tofile(tmp_path / "l.raw")
+    right.tofile(tmp_path / "r.raw")
+    p = subprocess.run([EXE, str(tmp_path / "l.raw"), str(tmp_path / "r.raw"), "752", "480"], capture_output=True, text=True)
+    assert p.returncode == 0, p.stdout[-500:] + p.stderr[-500:]
+    lines = p.stdout.splitlines()
+    head = lines[0].split()
+    xl, al, dl = oracle_port.detect_describe(left, 1500)
+    xr, ar, dr = oracle_port.detect_describe(right, 1500)
+    want = oracle_port.match(dl, dr, 70, 1.2)
+    assert int(head[1]) == len(xl) and int(head[3]) == len(xr) and int(head[5]) == len(want) and head[7] == "1"
+    got_m = np.array([[int(v) for v in ln.split()[1:]] for ln in lines if ln.startswith("m ")], np.int32)
+    assert np.array_equal(got_m, want)
+    ks = [ln.split() for ln in lines if ln.startswith("k ")]
+    assert np.array_equal(np.array([[float(k[1]), float(k[2])] for k in ks]), xl)
+    assert np.abs(np.array([float(k[3]) for k in ks]) - al).max() <= 1e-5
+    # bitset::to_string prints bit 255 first
+    bits = np.array([[int(c) for c in k[4][::-1]] for k in ks], np.uint8)
+    words = np.packbits(bits.reshape(len(ks), 8, 32), axis=2, bitorder="little").view(np.uint32).reshape(len(ks), 8)
+    assert np.array_equal(words, dl)

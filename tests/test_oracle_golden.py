@@ -1,0 +1,90 @@
+"""The CPU oracle (oracle/visnav_oracle.c) against the committed golden vectors (tests/golden/,
+made by tools/make_golden.py from cv2 and from the reference's own functions) -- this is what
+pins the oracle.  Runs without a GPU."""
+import os
+
+import numpy as np
+import pytest
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _load(name):
+    return np.load(os.path.join(GOLD, name + ".npz"))
+
+
+def _libs(oracle_port, oracle_ref):
+    return [oracle_port] + ([oracle_ref] if oracle_ref is not None else [])
+
+
+@pytest.mark.parametrize("name", ["gftt_320x240", "gftt_161x123", "gftt_752x480"])
+def test_gftt_matches_opencv(oracle_port, name):
+    g = _load(name)
+    img = g["img"]
+    if img.size == 0:
+        from visnav_b200 import workloads as wl
+        img = wl.synth_image(int(g["seed"]), int(g["w"]), int(g["h"]))
+    got = oracle_port.gftt(img, int(g["num_features"]))
+    assert np.array_equal(got, g["corners_unopt"])      # ordered equality, scalar OpenCV
+    assert np.array_equal(got, g["corners_default"])    # and the AVX2 dispatch on these images
+    if "lam_unopt" in g.files:
+        lam = oracle_port.response(img)
+        assert np.array_equal(lam.view(np.uint32), g["lam_unopt"].view(np.uint32))   # bit-exact map
+
+
+def test_detect_applies_border_filter(oracle_port):
+    g = _load("gftt_320x240")
+    xy = oracle_port.detect(g["img"], int(g["num_features"]))
+    c = g["corners_unopt"]
+    keep = (c[:, 0] >= 19) & (c[:, 0] < 320 - 19) & (c[:, 1] >= 19) & (c[:, 1] < 240 - 19)
+    assert np.array_equal(xy, c[keep].astype(np.float64))
+
+
+def test_angles_descriptors_match_reference(oracle_port, oracle_ref):
+    g = _load("stereo_320x240")
+    for lib in _libs(oracle_port, oracle_ref):
+        for side in "lr":
+            img = g["left" if side == "l" else "right"]
+            xy = lib.detect(img, 400)
+            assert np.array_equal(xy, g["xy_" + side])
+            ang = lib.angles(img, xy, True)
+            assert np.array_equal(ang, g["ang_" + side])      # same libm, same integer moments
+            assert np.array_equal(lib.describe(img, xy, ang), g["desc_" + side])
+        assert np.array_equal(lib.describe(g["left"], g["xy_l"], np.zeros(len(g["xy_l"]))), g["desc_l_norot"])
+        assert np.array_equal(lib.angles(g["left"], g["xy_l"], False), np.zeros(len(g["xy_l"])))
+        assert np.array_equal(lib.match(g["desc_l"], g["desc_r"], 70, 1.2), g["matches"])
+
+
+def test_match_ties_golden(oracle_port, oracle_ref):
+    g = _load("match_ties")
+    for lib in _libs(oracle_port, oracle_ref):
+        for key in [k for k in g.files if k.startswith("m_")]:
+            _, thr, ratio = key.split("_")
+            got = lib.match(g["d1"], g["d2"], int(thr), float(ratio.replace("p", ".")))
+            assert np.array_equal(got, g[key]), key
+
+
+def test_match_predicate_properties(oracle_port):
+    """Size-independent properties of the predicate: symmetric under swapping the
+    sets, ascending id1, one-to-one, empty inputs give nothing."""
+    from visnav_b200 import workloads as wl
+    rng = np.random.default_rng(4)
+    d2 = wl.random_descriptors(400, 1)
+    d1 = wl.flip_bits(d2[rng.permutation(400)[:350]], 22, rng)
+    m = oracle_port.match(d1, d2, 70, 1.2)
+    mt = oracle_port.match(d2, d1, 70, 1.2)
+    assert len(m) > 300 and np.all(np.diff(m[:, 0]) > 0)
+    assert len(set(m[:, 1])) == len(m)
+    assert np.array_equal(mt[np.argsort(mt[:, 1])][:, ::-1], m)
+    e = np.zeros((0, 8), np.uint32)
+    assert len(oracle_port.match(e, d2)) == 0 and len(oracle_port.match(d1, e)) == 0
+    b = oracle_port.best2(d1[:5], e)
+    assert np.array_equal(b, np.tile([256, 0, 256], (5, 1)))
+
+
+def test_contraction_modes_differ_only_rarely(oracle_port):
+    g = _load("stereo_320x240")
+    a = oracle_port.describe(g["left"], g["xy_l"], g["ang_l"], contract=True)
+    b = oracle_port.describe(g["left"], g["xy_l"], g["ang_l"], contract=False)
+    assert np.array_equal(a, g["desc_l"])                 # oracle/_ref was built with GCC's default contraction
+    assert (a != b).any(1).mean() < 0.05                  # the two roundings almost never disagree

@@ -1,0 +1,77 @@
+#!/usr/bin/env python3
+"""Generates tests/golden/*.npz -- golden vectors produced by the REFERENCE side, in the build
+container only (needs cv2 and /root/reference; neither exists on the GPU box):
+
+  * cv2 (OpenCV, python wheel): goodFeaturesToTrack / cornerMinEigenVal, with
+    cv2.setUseOptimized(False) (scalar operation order = the oracle's and the CUDA kernel's) and
+    with the default AVX2 dispatch (what a stock visnav build runs).  SURVEY.md section 8c: the
+    python wheel returns the same ordered corners as the vendored OpenCV 4.7.0-dev.
+  * oracle/_ref/libvisnav_ref.so: the reference's own computeAngles / computeDescriptors /
+    matchDescriptors compiled from /root/reference/include/visnav/keypoints.h (oracle/Makefile).
+
+The inputs are seeded synthetic images (visual-slam_b200/workloads.py); they are stored too, so the
+fixtures do not depend on numpy's generator staying bit-stable.
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import cv2  # noqa: E402
+import oracle  # noqa: E402
+import visnav_b200  # noqa: E402,F401
+from visnav_b200 import workloads as wl  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def gftt_cv2(img, n, optimized):
+    cv2.setUseOptimized(optimized)
+    pts = cv2.goodFeaturesToTrack(img, n, 0.01, 8, None, None, 3, False)
+    cv2.setUseOptimized(True)
+    return np.zeros((0, 2), np.float32) if pts is None else pts.reshape(-1, 2).astype(np.float32)
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    ref = oracle.load_ref()
+    assert ref is not None, "build oracle/_ref first (make -C oracle)"
+    # ---- detection: corners (both dispatches) and the response map ----
+    for name, (w, h, seed, nf) in {"gftt_320x240": (320, 240, 5, 300), "gftt_161x123": (161, 123, 9, 0),
+                                  "gftt_752x480": (752, 480, 1234, 1500)}.items():
+        img = wl.synth_image(seed, w, h)
+        rec = dict(img=img if w < 700 else np.zeros((0, 0), np.uint8), seed=seed, w=w, h=h, num_features=nf,
+                   corners_unopt=gftt_cv2(img, nf, False), corners_default=gftt_cv2(img, nf, True))
+        if w < 200:
+            cv2.setUseOptimized(False)
+            rec["lam_unopt"] = cv2.cornerMinEigenVal(img, 3, ksize=3)
+            cv2.setUseOptimized(True)
+        np.savez_compressed(os.path.join(OUT, name + ".npz"), **rec)
+        print(name, len(rec["corners_unopt"]), "corners; default dispatch identical:",
+              np.array_equal(rec["corners_unopt"], rec["corners_default"]))
+    # ---- orientation / description / stereo matching by the reference's own functions ----
+    left, right = wl.synth_stereo_pair(7, 320, 240)
+    xl = ref.detect(left, 400)
+    xr = ref.detect(right, 400)
+    al, ar = ref.angles(left, xl, True), ref.angles(right, xr, True)
+    dl, dr = ref.describe(left, xl, al), ref.describe(right, xr, ar)
+    m = ref.match(dl, dr, 70, 1.2)
+    np.savez_compressed(os.path.join(OUT, "stereo_320x240.npz"), left=left, right=right, xy_l=xl, xy_r=xr, ang_l=al,
+                        ang_r=ar, desc_l=dl, desc_r=dr, matches=m, desc_l_norot=ref.describe(left, xl, np.zeros(len(xl))))
+    print("stereo", len(xl), len(xr), len(m))
+    # ---- matching with heavy ties ----
+    rng = np.random.default_rng(77)
+    base = wl.random_descriptors(24, 3)
+    d1 = wl.flip_bits(base[rng.integers(0, 24, 220)], 5, rng)
+    d2 = wl.flip_bits(base[rng.integers(0, 24, 190)], 5, rng)
+    rec = dict(d1=d1, d2=d2)
+    for thr, ratio in [(70, 1.2), (256, 1.0), (30, 1.0), (300, 0.5)]:
+        rec["m_%d_%s" % (thr, str(ratio).replace(".", "p"))] = ref.match(d1, d2, thr, ratio)
+    np.savez_compressed(os.path.join(OUT, "match_ties.npz"), **rec)
+    print("match_ties", {k: len(v) for k, v in rec.items() if k.startswith("m_")})
+
+
+if __name__ == "__main__":
+    main()
