@@ -107,7 +107,7 @@ void vslam_destroy(vslam_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  for (int i = 0; i < 2; ++i) {
+  for (int i = 0; i < vslam_ctx::kMaxBatchDepth; ++i) {
     if (ctx->batch_plans[i]) vslam_stereo_plan_destroy(ctx->batch_plans[i]);
     ctx->batch_plans[i] = nullptr;
   }
@@ -130,6 +130,8 @@ int vslam_set_option(vslam_ctx* ctx, int option, int value) {
   if (!ctx) return VSLAM_E_ARG;
   if (option == VSLAM_OPT_FP_CONTRACT) ctx->fp_contract = value != 0;
   else if (option == VSLAM_OPT_MATCH_CSA) ctx->match_csa = value != 0;
+  else if (option == VSLAM_OPT_BATCH_CHUNK && value >= 1 && value <= 4096) ctx->batch_chunk = value;
+  else if (option == VSLAM_OPT_BATCH_DEPTH && value >= 1 && value <= vslam_ctx::kMaxBatchDepth) ctx->batch_depth = value;
   else return vs_fail(ctx, VSLAM_E_ARG, "unknown option");
   return VSLAM_OK;
 }
@@ -552,11 +554,14 @@ int vslam_stereo_batch(vslam_ctx* ctx, const uint8_t* images, int count, const v
   if (sp->w < 2 || sp->h < 2 || sp->pitch < sp->w || sp->num_features <= 0 || sp->num_features > cap)
     return vs_fail(ctx, VSLAM_E_ARG, "bad stereo parameters (num_features must be in [1, cap])");
   if (count == 0) return VSLAM_OK;
-  // Two plans on two streams: while chunk k computes, chunk k+1 uploads and chunk k-1 downloads.
-  const int chunk = count < 128 ? count : 128;
-  vslam_stereo_plan* plans[2] = {nullptr, nullptr};
+  // `batch_depth` plans, each on its own stream: while chunk k computes, chunk k+1 uploads and chunk
+  // k-1 downloads.  Stream order serialises a plan's next upload after its own download, so three
+  // plans are needed for the three phases to overlap freely.
+  const int chunk = count < ctx->batch_chunk ? count : ctx->batch_chunk;
+  vslam_stereo_plan* plans[vslam_ctx::kMaxBatchDepth] = {};
   int rc = VSLAM_OK;
-  const int nplans = count > chunk ? 2 : 1;
+  const int nchunks = (count + chunk - 1) / chunk;
+  const int nplans = nchunks < ctx->batch_depth ? nchunks : ctx->batch_depth;
   for (int i = 0; i < nplans && !rc; ++i) {
     vslam_stereo_plan*& cp = ctx->batch_plans[i];
     if (cp && (cp->w != sp->w || cp->h != sp->h || cp->cap != cap || cp->max_pairs < chunk)) {

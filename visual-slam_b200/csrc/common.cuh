@@ -49,7 +49,10 @@ struct vslam_ctx {
   DevBuf d1, d2, pairs, mcnt, rowpart, colstat, jobs;
   void* pinned = nullptr;  // small pinned staging block for counts
   // pipeline plans of vslam_stereo_batch, kept between calls (same geometry -> no reallocation)
-  struct vslam_stereo_plan* batch_plans[2] = {nullptr, nullptr};
+  static constexpr int kMaxBatchDepth = 4;
+  struct vslam_stereo_plan* batch_plans[kMaxBatchDepth] = {nullptr, nullptr, nullptr, nullptr};
+  int batch_chunk = 128;  // stereo pairs per pipeline chunk (VSLAM_OPT_BATCH_CHUNK)
+  int batch_depth = 4;    // chunks in flight: upload / compute / download overlap (VSLAM_OPT_BATCH_DEPTH)
 };
 
 #define VS_CUDA(ctx, call)                                                              \

@@ -38,6 +38,8 @@ ABI_SYMBOLS = [
 
 VSLAM_OPT_FP_CONTRACT = 1
 VSLAM_OPT_MATCH_CSA = 2
+VSLAM_OPT_BATCH_CHUNK = 3
+VSLAM_OPT_BATCH_DEPTH = 4
 
 
 class VslamError(RuntimeError):
