@@ -8,18 +8,27 @@
 // The moments are integers (|.| < 2^23), accumulated in int32; atan2 / sincos / the rotation are
 // fp64 with explicit rounding (__dmul_rn / __fma_rn: no contraction the source does not spell).
 //
-// Design (B200): one warp per keypoint.  The 37 x 37 patch the two functions can touch (reach
-// 18 px, < the 19 px border detectKeypoints leaves) is staged once into shared memory with
-// aligned 128-bit loads (37 rows x 4 x 16 B); moments and the 512 pattern taps then read shared
-// memory.  Lane l produces bits 32k + l, so descriptor word k is one __ballot_sync.
+// Design (B200): one warp owns 32 consecutive keypoints of one image and works in three phases.
+//   1. per keypoint: the 37 x 37 patch both functions can touch (reach 18 px, < the 19 px border
+//      detectKeypoints leaves) is staged into shared memory with aligned 128-bit loads, and the
+//      moments are taken four pixels at a time with DP4A (weights x, and 1 for the row sums that
+//      y multiplies), one (row, 4-column group) item per lane and step;
+//   2. ONCE per 32 keypoints: lane i evaluates atan2 / sincos of keypoint i -- the ~250 fp64
+//      instructions that a warp-per-keypoint layout executes 32 times redundantly;
+//   3. per keypoint: patch staged again (L1/L2 hit), lane l computes bits 32k + l; the lane's
+//      eight pattern rows stay in registers as doubles, coordinates are rounded by ONE fp64 add of
+//      a fixed-point magic constant (C round() semantics proven below), descriptor word k is a ballot.
+// Blocks of one image are consecutive (blockIdx.x = chunk, .y = image), so an image's patches
+// are read from L2 once: the first layout had the image index fastest and re-read DRAM 11 times.
 #include "common.cuh"
 
 namespace {
 
-constexpr int kWarpsPerCta = 8;
+constexpr int kWarpsPerCta = 4;
 constexpr int kPatchRows = 37;   // dy in [-18, 18]
 constexpr int kPatchPitch = 64;  // bytes; 4 aligned 16-byte chunks cover 37 px at any alignment
 constexpr int kReach = 18;
+constexpr int kHalfPatch = 15;   // keypoints.h:49 HALF_PATCH_SIZE
 
 // row i = (xa, ya, xb, yb); plain global memory: lanes read 32 different rows at once
 __device__ const char4 g_pattern[256] = {
@@ -39,35 +48,40 @@ struct DescribeParams {
   int contract;
 };
 
-__global__ void __launch_bounds__(kWarpsPerCta * 32) orient_describe_kernel(const DescribeParams p) {
-  __shared__ __align__(16) unsigned char patch_all[kWarpsPerCta][kPatchRows * kPatchPitch];
-  __shared__ char4 pat[256];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  pat[tid] = g_pattern[tid];
-  __syncthreads();
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b_signed_bytes, int c) {
+  int d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b_signed_bytes), "r"(c));
+  return d;
+}
+__device__ __forceinline__ int dp4a_uu(uint32_t a, uint32_t b, int c) {
+  int d;
+  asm("dp4a.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
 
-  const int img = blockIdx.x;
-  const int kp = blockIdx.y * kWarpsPerCta + warp;
-  const int n = p.n_kp[img];
-  if (kp >= n) return;
-  const size_t slot = (size_t)img * p.cap + kp;
-  const double2 pt = reinterpret_cast<const double2*>(p.xy)[slot];
-  const int cx = (int)pt.x, cy = (int)pt.y;  // keypoints.h:160-161: double -> int truncation
-  const uint8_t* im = p.base + (size_t)img * p.stride;
-  unsigned char* patch = patch_all[warp];
-
-  // ---- stage the patch ------------------------------------------------------------------
+// Starts staging the patch around (cx, cy) into `patch` (cp.async, 16 bytes per item: global -> shared
+// without passing through registers) and commits the group; returns the patch column of the keypoint.
+// The caller waits with patch_wait<N>() before reading.  Two buffers per warp: the next keypoint's
+// patch is in flight while the current one is processed.
+__device__ __forceinline__ int stage_patch(const DescribeParams& p, const uint8_t* im, int cx, int cy,
+                                           unsigned char* patch, int lane) {
   const int x0 = cx - kReach, y0 = cy - kReach;
   const bool interior = x0 >= 0 && y0 >= 0 && cx + kReach < p.w && cy + kReach < p.h;
   int xbase;  // image x of patch byte 0
   if (interior && (p.pitch & 15) == 0 && ((uintptr_t)im & 15) == 0) {
     xbase = x0 & ~15;
-    for (int item = lane; item < kPatchRows * 4; item += 32) {
-      const int row = item >> 2, q = item & 3;
-      const int xs = xbase + q * 16;
-      if (xs <= cx + kReach) {  // chunk holds a needed pixel; it ends at or before `pitch`
-        const uint4 v = __ldg(reinterpret_cast<const uint4*>(im + (size_t)(y0 + row) * p.pitch + xs));
-        *reinterpret_cast<uint4*>(patch + row * kPatchPitch + q * 16) = v;
+    const uint8_t* src = im + (size_t)y0 * p.pitch + xbase;
+    const int q = lane & 3, row0 = lane >> 2;
+    const bool need = xbase + q * 16 <= cx + kReach;  // chunk holds a needed pixel; it ends at or before `pitch`
+    if (need) {
+      const uint32_t dst = static_cast<uint32_t>(__cvta_generic_to_shared(patch + row0 * kPatchPitch + q * 16));
+      src += (size_t)row0 * p.pitch + q * 16;
+#pragma unroll
+      for (int it = 0; it < 5; ++it) {
+        if (row0 + 8 * it < kPatchRows)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + it * 8 * kPatchPitch),
+                       "l"(src + (size_t)it * 8 * p.pitch)
+                       : "memory");
       }
     }
   } else {
@@ -80,68 +94,175 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) orient_describe_kernel(cons
       patch[row * kPatchPitch + col] = im[(size_t)yy * p.pitch + xx];
     }
   }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  return cx - xbase;
+}
+template <int kPending>
+__device__ __forceinline__ void patch_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory");
   __syncwarp();
-  const int off = cx - xbase;  // patch column of the keypoint
-#define PATCH(dx, dy) patch[((dy) + kReach) * kPatchPitch + (dx) + off]
+}
 
-  // ---- orientation -----------------------------------------------------------------------
+// (int)round(v) for |v| < 2^10 from ONE fp64 add, plus a tie detector.
+//   A = low word of (v + kRoundMagic), kRoundMagic = 1.5 * 2^32 + 0.5: the add rounds v + 0.5 to a
+//   multiple of 2^-20 (nearest-even), so A = RNE((v + 0.5) * 2^20) as a two's-complement integer and
+//   A >> 20 = floor(v + 0.5 +- 2^-21).  That equals C round(v) (halfway cases away from zero) unless
+//   v lies within 2^-21 of a halfway point -- exactly the case (A & 0xFFFFF) == 0, which the caller
+//   screens for and recomputes with round() itself.  (For negative halfway points floor(v + 0.5)
+//   differs from round(v); they are screened the same way.)
+constexpr double kRoundMagic = 6442450944.5;
+__device__ __forceinline__ int round_fix20(double v) { return __double2loint(__dadd_rn(v, kRoundMagic)); }
+
+// Rotates the two test points of one pattern row by the keypoint angle (keypoints.h:206-214).
+template <bool kContract>
+__device__ __forceinline__ void rotate_pair(double c, double s, char4 q, double& xar, double& yar, double& xbr,
+                                            double& ybr) {
+  const double xa = q.x, ya = q.y, xb = q.z, yb = q.w;
+  if (kContract) {
+    // x' = fma(c, x, -(s*y)); y' = fma(s, x, c*y): GCC's contraction of the reference expressions
+    xar = __fma_rn(c, xa, -__dmul_rn(s, ya));
+    yar = __fma_rn(s, xa, __dmul_rn(c, ya));
+    xbr = __fma_rn(c, xb, -__dmul_rn(s, yb));
+    ybr = __fma_rn(s, xb, __dmul_rn(c, yb));
+  } else {
+    xar = __dsub_rn(__dmul_rn(c, xa), __dmul_rn(s, ya));
+    yar = __dadd_rn(__dmul_rn(s, xa), __dmul_rn(c, ya));
+    xbr = __dsub_rn(__dmul_rn(c, xb), __dmul_rn(s, yb));
+    ybr = __dadd_rn(__dmul_rn(s, xb), __dmul_rn(c, yb));
+  }
+}
+
+template <bool kContract>
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 8) orient_describe_kernel(const DescribeParams p) {
+  __shared__ __align__(16) unsigned char patch_all[kWarpsPerCta][2][kPatchRows * kPatchPitch];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int img = blockIdx.y;
+  const int kp0 = (blockIdx.x * kWarpsPerCta + warp) * 32;
+  const int n = p.n_kp[img];
+  const int nk = min(32, n - kp0);
+  if (nk <= 0) return;
+  const size_t slot0 = (size_t)img * p.cap + kp0;
+  const uint8_t* im = p.base + (size_t)img * p.stride;
+  unsigned char* const patch0 = patch_all[warp][0];
+  unsigned char* const patch1 = patch_all[warp][1];
+
+  int cx = 0, cy = 0;
+  if (lane < nk) {
+    const double2 pt = reinterpret_cast<const double2*>(p.xy)[slot0 + lane];
+    cx = (int)pt.x;  // keypoints.h:160-161: double -> int truncation
+    cy = (int)pt.y;
+  }
+
+  // ---- phase 1: moments (keypoints.h:171-183) -------------------------------------------------
   double angle = 0.0;
   if (p.mode_angles == 1) {
-    int m10 = 0, m01 = 0;
-    const int dx = lane - 15;  // lanes 0..30 <-> dx -15..15
-    if (lane < 31) {
-      const int lim = 225 - dx * dx;
-#pragma unroll 1
-      for (int dy = -15; dy <= 15; ++dy) {
-        if (dy * dy <= lim) {
-          const int v = PATCH(dx, dy);
-          m10 += dx * v;
-          m01 += dy * v;
+    // lane = (row group, 4-column group): rows rsub + 4*it, columns dx = 4g - 16 + j
+    const int g = lane & 7, rsub = lane >> 3;
+    uint32_t ones[8], wx[8];
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int row = rsub + 4 * it, dy = row - kHalfPatch;
+      uint32_t o = 0, wv = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int dx = 4 * g - 16 + j;
+        const bool in = row <= 2 * kHalfPatch && dx >= -kHalfPatch && dx * dx + dy * dy <= kHalfPatch * kHalfPatch;
+        if (in) {
+          o |= 1u << (8 * j);
+          wv |= (uint32_t)(dx & 0xFF) << (8 * j);
         }
       }
+      ones[it] = o;
+      wx[it] = wv;
     }
+    int my_m10 = 0, my_m01 = 0;
+    int off_next = stage_patch(p, im, __shfl_sync(0xFFFFFFFFu, cx, 0), __shfl_sync(0xFFFFFFFFu, cy, 0), patch0, lane);
+    for (int i = 0; i < nk; ++i) {
+      unsigned char* patch = (i & 1) ? patch1 : patch0;
+      const int off = off_next;
+      if (i + 1 < nk) {
+        off_next = stage_patch(p, im, __shfl_sync(0xFFFFFFFFu, cx, i + 1), __shfl_sync(0xFFFFFFFFu, cy, i + 1),
+                               (i & 1) ? patch0 : patch1, lane);
+        patch_wait<1>();
+      } else {
+        patch_wait<0>();
+      }
+      const int sb = off - 16;  // patch byte of column dx = -16
+      const uint32_t* wrow = reinterpret_cast<const uint32_t*>(patch + (rsub + 3) * kPatchPitch) + (sb >> 2) + g;
+      const int shift = (sb & 3) * 8;
+      int m10 = 0, m01 = 0;
 #pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-      m10 += __shfl_xor_sync(0xFFFFFFFFu, m10, s);
-      m01 += __shfl_xor_sync(0xFFFFFFFFu, m01, s);
+      for (int it = 0; it < 8; ++it) {
+        const uint32_t lo = wrow[it * 4 * (kPatchPitch / 4)], hi = wrow[it * 4 * (kPatchPitch / 4) + 1];
+        const uint32_t pix = __funnelshift_r(lo, hi, shift);
+        m10 = dp4a_us(pix, wx[it], m10);
+        m01 += (rsub + 4 * it - kHalfPatch) * dp4a_uu(pix, ones[it], 0);
+      }
+      m10 = __reduce_add_sync(0xFFFFFFFFu, m10);
+      m01 = __reduce_add_sync(0xFFFFFFFFu, m01);
+      if (lane == i) {
+        my_m10 = m10;
+        my_m01 = m01;
+      }
+      __syncwarp();  // every lane is done with this buffer before it is refilled
     }
-    angle = atan2((double)m01, (double)m10);
-    if (lane == 0) p.angles[slot] = angle;
+    // ---- phase 2: one atan2 per lane = per keypoint ----
+    angle = atan2((double)my_m01, (double)my_m10);
   } else if (p.mode_angles == 2) {
-    angle = p.angles[slot];
-  } else if (lane == 0) {
-    p.angles[slot] = 0.0;
+    if (lane < nk) angle = p.angles[slot0 + lane];
   }
+  if (p.mode_angles != 2 && lane < nk) p.angles[slot0 + lane] = angle;
   if (!p.desc) return;
+  double c, s;
+  sincos(angle, &s, &c);
 
-  // ---- rBRIEF ------------------------------------------------------------------------------
-  const double c = cos(angle), s = sin(angle);
-  uint32_t my_word = 0;
+  // ---- phase 3: rBRIEF (keypoints.h:205-217) ----------------------------------------------------
+  // this lane's pattern rows 32k + lane stay packed (8 registers); the int8 -> fp64 conversions run on
+  // the otherwise idle conversion unit
+  char4 pat[8];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const char4 q = pat[k * 32 + lane];
-    const double xa = q.x, ya = q.y, xb = q.z, yb = q.w;
-    double xar, yar, xbr, ybr;
-    if (p.contract) {
-      // x' = fma(c, x, -(s*y)); y' = fma(s, x, c*y): GCC's contraction of keypoints.h:206-214
-      xar = __fma_rn(c, xa, -__dmul_rn(s, ya));
-      yar = __fma_rn(s, xa, __dmul_rn(c, ya));
-      xbr = __fma_rn(c, xb, -__dmul_rn(s, yb));
-      ybr = __fma_rn(s, xb, __dmul_rn(c, yb));
+  for (int k = 0; k < 8; ++k) pat[k] = g_pattern[k * 32 + lane];
+  int off_next = stage_patch(p, im, __shfl_sync(0xFFFFFFFFu, cx, 0), __shfl_sync(0xFFFFFFFFu, cy, 0), patch0, lane);
+  for (int i = 0; i < nk; ++i) {
+    const double ci = __shfl_sync(0xFFFFFFFFu, c, i), si = __shfl_sync(0xFFFFFFFFu, s, i);
+    unsigned char* patch = (i & 1) ? patch1 : patch0;
+    const int off = off_next;
+    if (i + 1 < nk) {
+      off_next = stage_patch(p, im, __shfl_sync(0xFFFFFFFFu, cx, i + 1), __shfl_sync(0xFFFFFFFFu, cy, i + 1),
+                             (i & 1) ? patch0 : patch1, lane);
+      patch_wait<1>();
     } else {
-      xar = __dsub_rn(__dmul_rn(c, xa), __dmul_rn(s, ya));
-      yar = __dadd_rn(__dmul_rn(s, xa), __dmul_rn(c, ya));
-      xbr = __dsub_rn(__dmul_rn(c, xb), __dmul_rn(s, yb));
-      ybr = __dadd_rn(__dmul_rn(s, xb), __dmul_rn(c, yb));
+      patch_wait<0>();
     }
-    const int xai = (int)round(xar), yai = (int)round(yar);
-    const int xbi = (int)round(xbr), ybi = (int)round(ybr);
-    const int va = PATCH(xai, yai), vb = PATCH(xbi, ybi);
-    const uint32_t word = __ballot_sync(0xFFFFFFFFu, va < vb);
-    if (lane == k) my_word = word;
+    const unsigned char* centre = patch + kReach * kPatchPitch + off;
+    uint32_t my_word = 0;
+    int fmin = 1;  // smallest fixed-point fraction seen: 0 <=> some coordinate needs the exact round()
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      double xar, yar, xbr, ybr;
+      rotate_pair<kContract>(ci, si, pat[k], xar, yar, xbr, ybr);
+      const int axa = round_fix20(xar), aya = round_fix20(yar), axb = round_fix20(xbr), ayb = round_fix20(ybr);
+      const int xai = axa >> 20, yai = aya >> 20, xbi = axb >> 20, ybi = ayb >> 20;
+      fmin = min(fmin, min(min(axa - (xai << 20), aya - (yai << 20)), min(axb - (xbi << 20), ayb - (ybi << 20))));
+      const int va = centre[yai * kPatchPitch + xai], vb = centre[ybi * kPatchPitch + xbi];
+      const uint32_t word = __ballot_sync(0xFFFFFFFFu, va < vb);
+      if (lane == k) my_word = word;
+    }
+    if (__any_sync(0xFFFFFFFFu, fmin == 0)) {
+      // a coordinate within 2^-21 of a halfway point (practically never): redo the keypoint with round()
+#pragma unroll 1
+      for (int k = 0; k < 8; ++k) {
+        double xar, yar, xbr, ybr;
+        rotate_pair<kContract>(ci, si, pat[k], xar, yar, xbr, ybr);
+        const int xai = (int)round(xar), yai = (int)round(yar), xbi = (int)round(xbr), ybi = (int)round(ybr);
+        const int va = centre[yai * kPatchPitch + xai], vb = centre[ybi * kPatchPitch + xbi];
+        const uint32_t word = __ballot_sync(0xFFFFFFFFu, va < vb);
+        if (lane == k) my_word = word;
+      }
+    }
+    if (lane < 8) p.desc[(slot0 + i) * 8 + lane] = my_word;
+    __syncwarp();  // every lane is done with this buffer before it is refilled
   }
-  if (lane < 8) p.desc[slot * 8 + lane] = my_word;
-#undef PATCH
 }
 
 }  // namespace
@@ -154,8 +275,11 @@ int launch_orient_describe(vslam_ctx* ctx, const DevImages& im, int count, const
   p.base = im.base; p.w = im.w; p.h = im.h; p.pitch = im.pitch; p.stride = im.stride;
   p.xy = xy; p.n_kp = n_kp; p.cap = cap; p.mode_angles = mode_angles;
   p.angles = angles; p.desc = desc; p.contract = ctx->fp_contract;
-  dim3 grid(count, (cap + kWarpsPerCta - 1) / kWarpsPerCta);
-  orient_describe_kernel<<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(p);
+  const int per_cta = kWarpsPerCta * 32;
+  if (count > 65535) return vs_fail(ctx, VSLAM_E_LIMIT, "more than 65535 images in one describe launch");
+  dim3 grid((cap + per_cta - 1) / per_cta, count);
+  if (p.contract) orient_describe_kernel<true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(p);
+  else orient_describe_kernel<false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(p);
   ctx->launches++;
   VS_CUDA(ctx, cudaGetLastError());
   return VSLAM_OK;
