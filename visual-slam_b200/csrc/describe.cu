@@ -53,41 +53,40 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b_signed_bytes, int 
   asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b_signed_bytes), "r"(c));
   return d;
 }
-__device__ __forceinline__ int dp4a_uu(uint32_t a, uint32_t b, int c) {
-  int d;
-  asm("dp4a.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-  return d;
-}
 
-// Starts staging the patch around (cx, cy) into `patch` (cp.async, 16 bytes per item: global -> shared
-// without passing through registers) and commits the group; returns the patch column of the keypoint.
-// The caller waits with patch_wait<N>() before reading.  Two buffers per warp: the next keypoint's
+// Per-lane constants of the patch copy: lane = (row0, 16-byte chunk q); 5 rows per lane, 8 apart.
+struct StageLane {
+  const uint8_t* src;   // image base + row0 * pitch + q * 16
+  uint32_t dst[2];      // shared address of (row0, q) in the two patch buffers of the warp
+  size_t pitch8;        // 8 image rows in bytes
+  int q;
+  bool row4;            // the lane's fifth row (row0 + 32) exists
+};
+
+// Starts staging one keypoint's patch (cp.async, 16 bytes per item: global -> shared without passing
+// through registers) and commits the group; the caller waits with patch_wait<N>() before reading.
+// kp_off / kp_meta are the keypoint's precomputed byte offset of patch (row 0, byte 0) in the image
+// and its (patch column of the keypoint | interior << 8).  Two buffers per warp: the next keypoint's
 // patch is in flight while the current one is processed.
-__device__ __forceinline__ int stage_patch(const DescribeParams& p, const uint8_t* im, int cx, int cy,
-                                           unsigned char* patch, int lane) {
-  const int x0 = cx - kReach, y0 = cy - kReach;
-  const bool interior = x0 >= 0 && y0 >= 0 && cx + kReach < p.w && cy + kReach < p.h;
-  int xbase;  // image x of patch byte 0
-  if (interior && (p.pitch & 15) == 0 && ((uintptr_t)im & 15) == 0) {
-    xbase = x0 & ~15;
-    const uint8_t* src = im + (size_t)y0 * p.pitch + xbase;
-    const int q = lane & 3, row0 = lane >> 2;
-    const bool need = xbase + q * 16 <= cx + kReach;  // chunk holds a needed pixel; it ends at or before `pitch`
-    if (need) {
-      const uint32_t dst = static_cast<uint32_t>(__cvta_generic_to_shared(patch + row0 * kPatchPitch + q * 16));
-      src += (size_t)row0 * p.pitch + q * 16;
+__device__ __forceinline__ void stage_patch(const DescribeParams& p, const uint8_t* im, const StageLane& L, int buf,
+                                            int kp_off, int kp_meta, int cx, int cy, unsigned char* patch,
+                                            int lane) {
+  if (kp_meta & 256) {
+    if (L.q * 16 <= (kp_meta & 255) + kReach) {  // chunk holds a needed pixel; it ends at or before `pitch`
+      const uint8_t* src = L.src + kp_off;
+      const uint32_t dst = L.dst[buf];
 #pragma unroll
       for (int it = 0; it < 5; ++it) {
-        if (row0 + 8 * it < kPatchRows)
+        if (it < 4 || L.row4)
           asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + it * 8 * kPatchPitch),
-                       "l"(src + (size_t)it * 8 * p.pitch)
+                       "l"(src + it * L.pitch8)
                        : "memory");
       }
     }
   } else {
     // Border keypoints (never produced by detectKeypoints): the reference reads out of bounds
     // here; like the oracle we replicate the edge pixel so the result is defined.
-    xbase = x0;
+    const int x0 = cx - kReach, y0 = cy - kReach;
     for (int item = lane; item < kPatchRows * kPatchRows; item += 32) {
       const int row = item / kPatchRows, col = item - row * kPatchRows;
       const int yy = min(max(y0 + row, 0), p.h - 1), xx = min(max(x0 + col, 0), p.w - 1);
@@ -95,7 +94,6 @@ __device__ __forceinline__ int stage_patch(const DescribeParams& p, const uint8_
     }
   }
   asm volatile("cp.async.commit_group;" ::: "memory");
-  return cx - xbase;
 }
 template <int kPending>
 __device__ __forceinline__ void patch_wait() {
@@ -153,12 +151,37 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 8) orient_describe_kernel(c
     cy = (int)pt.y;
   }
 
+  // patch geometry of this lane's keypoint: byte offset of patch (row 0, byte 0), patch column of the
+  // keypoint (18..33 when the patch starts on a 16-byte boundary, 18 on the border path), interior flag
+  int kp_off, kp_meta;
+  {
+    const int x0 = cx - kReach, y0 = cy - kReach;
+    const bool interior = x0 >= 0 && y0 >= 0 && cx + kReach < p.w && cy + kReach < p.h && (p.pitch & 15) == 0 &&
+                          ((uintptr_t)im & 15) == 0;
+    const int xbase = interior ? (x0 & ~15) : x0;
+    kp_off = y0 * p.pitch + xbase;  // < 2^30 (check_image)
+    kp_meta = (cx - xbase) | (interior ? 256 : 0);
+  }
+  StageLane L;
+  {
+    const int q = lane & 3, row0 = lane >> 2;
+    L.q = q;
+    L.row4 = row0 + 32 < kPatchRows;
+    L.src = im + (size_t)row0 * p.pitch + q * 16;
+    L.pitch8 = (size_t)8 * p.pitch;
+    L.dst[0] = static_cast<uint32_t>(__cvta_generic_to_shared(patch0 + row0 * kPatchPitch + q * 16));
+    L.dst[1] = static_cast<uint32_t>(__cvta_generic_to_shared(patch1 + row0 * kPatchPitch + q * 16));
+  }
+#define STAGE(i_, buf_)                                                                                   \
+  stage_patch(p, im, L, (buf_), __shfl_sync(0xFFFFFFFFu, kp_off, (i_)), __shfl_sync(0xFFFFFFFFu, kp_meta, (i_)), \
+              __shfl_sync(0xFFFFFFFFu, cx, (i_)), __shfl_sync(0xFFFFFFFFu, cy, (i_)), (buf_) ? patch1 : patch0, lane)
+
   // ---- phase 1: moments (keypoints.h:171-183) -------------------------------------------------
   double angle = 0.0;
   if (p.mode_angles == 1) {
     // lane = (row group, 4-column group): rows rsub + 4*it, columns dx = 4g - 16 + j
     const int g = lane & 7, rsub = lane >> 3;
-    uint32_t ones[8], wx[8];
+    uint32_t wy[8], wx[8];
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
       const int row = rsub + 4 * it, dy = row - kHalfPatch;
@@ -168,21 +191,20 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 8) orient_describe_kernel(c
         const int dx = 4 * g - 16 + j;
         const bool in = row <= 2 * kHalfPatch && dx >= -kHalfPatch && dx * dx + dy * dy <= kHalfPatch * kHalfPatch;
         if (in) {
-          o |= 1u << (8 * j);
+          o |= (uint32_t)(dy & 0xFF) << (8 * j);
           wv |= (uint32_t)(dx & 0xFF) << (8 * j);
         }
       }
-      ones[it] = o;
+      wy[it] = o;
       wx[it] = wv;
     }
     int my_m10 = 0, my_m01 = 0;
-    int off_next = stage_patch(p, im, __shfl_sync(0xFFFFFFFFu, cx, 0), __shfl_sync(0xFFFFFFFFu, cy, 0), patch0, lane);
+    STAGE(0, 0);
     for (int i = 0; i < nk; ++i) {
-      unsigned char* patch = (i & 1) ? patch1 : patch0;
-      const int off = off_next;
+      const unsigned char* patch = (i & 1) ? patch1 : patch0;
+      const int off = __shfl_sync(0xFFFFFFFFu, kp_meta, i) & 255;
       if (i + 1 < nk) {
-        off_next = stage_patch(p, im, __shfl_sync(0xFFFFFFFFu, cx, i + 1), __shfl_sync(0xFFFFFFFFu, cy, i + 1),
-                               (i & 1) ? patch0 : patch1, lane);
+        STAGE(i + 1, (i + 1) & 1);
         patch_wait<1>();
       } else {
         patch_wait<0>();
@@ -196,7 +218,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 8) orient_describe_kernel(c
         const uint32_t lo = wrow[it * 4 * (kPatchPitch / 4)], hi = wrow[it * 4 * (kPatchPitch / 4) + 1];
         const uint32_t pix = __funnelshift_r(lo, hi, shift);
         m10 = dp4a_us(pix, wx[it], m10);
-        m01 += (rsub + 4 * it - kHalfPatch) * dp4a_uu(pix, ones[it], 0);
+        m01 = dp4a_us(pix, wy[it], m01);
       }
       m10 = __reduce_add_sync(0xFFFFFFFFu, m10);
       m01 = __reduce_add_sync(0xFFFFFFFFu, m01);
@@ -222,14 +244,13 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 8) orient_describe_kernel(c
   char4 pat[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) pat[k] = g_pattern[k * 32 + lane];
-  int off_next = stage_patch(p, im, __shfl_sync(0xFFFFFFFFu, cx, 0), __shfl_sync(0xFFFFFFFFu, cy, 0), patch0, lane);
+  STAGE(0, 0);
   for (int i = 0; i < nk; ++i) {
     const double ci = __shfl_sync(0xFFFFFFFFu, c, i), si = __shfl_sync(0xFFFFFFFFu, s, i);
-    unsigned char* patch = (i & 1) ? patch1 : patch0;
-    const int off = off_next;
+    const unsigned char* patch = (i & 1) ? patch1 : patch0;
+    const int off = __shfl_sync(0xFFFFFFFFu, kp_meta, i) & 255;
     if (i + 1 < nk) {
-      off_next = stage_patch(p, im, __shfl_sync(0xFFFFFFFFu, cx, i + 1), __shfl_sync(0xFFFFFFFFu, cy, i + 1),
-                             (i & 1) ? patch0 : patch1, lane);
+      STAGE(i + 1, (i + 1) & 1);
       patch_wait<1>();
     } else {
       patch_wait<0>();
@@ -263,6 +284,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 8) orient_describe_kernel(c
     if (lane < 8) p.desc[(slot0 + i) * 8 + lane] = my_word;
     __syncwarp();  // every lane is done with this buffer before it is refilled
   }
+#undef STAGE
 }
 
 }  // namespace
