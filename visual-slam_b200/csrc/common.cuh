@@ -82,7 +82,7 @@ struct DevImages {
 // ---- launchers (each file's kernels stay private to it) ----
 // detect.cu
 struct DetectWorkspace {
-  uint64_t* cand;      // [count][cand_cap] keys (float bits << 32 | pixel index)
+  uint64_t* cand;      // [count][cand_cap] keys (float bits << 32 | y << 16 | x)
   uint32_t* cand_cnt;  // [count]
   uint32_t* img_max;   // [count] ordered-int encoding of the max response
   int cand_cap;
