@@ -299,7 +299,10 @@ static int match_common(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32
   VS_CUDA(ctx, cudaMemcpyAsync(ctx->d2.p, d2, (size_t)n2 * 32, cudaMemcpyHostToDevice, ctx->stream));
   VS_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
   int rc;
-  if (!best2_out && match_fits_fused(n1, n2)) {
+  // A single call is latency-bound: the fused kernel would run it on ONE SM (0.6 ms at 1300 x 1300).
+  // Beyond a few thousand distances per SM the column-split path (all SMs, three short launches) wins.
+  const bool small = (long long)n1 * n2 <= 256LL * 256LL;
+  if (!best2_out && small && match_fits_fused(n1, n2)) {
     VS_CUDA(ctx, ctx->jobs.reserve(sizeof(MatchJob)));
     MatchJob job;
     job.d1 = ctx->d1.as<uint32_t>(); job.d2 = ctx->d2.as<uint32_t>();

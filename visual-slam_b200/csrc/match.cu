@@ -102,6 +102,34 @@ __device__ __forceinline__ uint32_t hamming256(const uint32_t (&a)[8], const uin
   }
 }
 
+// One shared-memory stage of columns against the first kNr row groups of a warp.
+template <bool kCsa, int kNr>
+__device__ __forceinline__ void scan_chunk(const uint32_t (&a)[kR][8], uint32_t (&m1)[kR], uint32_t (&m2)[kR],
+                                           const uint32_t (&rid)[kR], const uint4* bs, int nc, uint32_t jbase,
+                                           uint2* part, int lane) {
+  for (int c = 0; c < nc; ++c) {
+    const uint4 b0 = bs[2 * c], b1 = bs[2 * c + 1];
+    uint32_t c1 = 0xFFFFFFFFu, c2 = 0xFFFFFFFFu;
+    const uint32_t j = jbase + c;
+#pragma unroll
+    for (int r = 0; r < kNr; ++r) {
+      const uint32_t d = hamming256<kCsa>(a[r], b0, b1);
+      const uint32_t kr = (d << kShift) + j;
+      const uint32_t t = max(m1[r], kr);
+      m1[r] = min(m1[r], kr);
+      m2[r] = min(m2[r], t);
+      const uint32_t kc = (d << kShift) + rid[r];
+      const uint32_t u = max(c1, kc);
+      c1 = min(c1, kc);
+      c2 = min(c2, u);
+    }
+    // fold the 32 lanes: smallest key, then the smallest of (owner's second, others' first)
+    const uint32_t g1 = __reduce_min_sync(0xFFFFFFFFu, c1);
+    const uint32_t g2 = __reduce_min_sync(0xFFFFFFFFu, c1 == g1 ? c2 : c1);
+    if (lane == 0) part[c] = make_uint2(g1, g2);
+  }
+}
+
 struct ScanSmem {
   uint4* bs;        // [kStages][kChunk][2]
   uint2* part;      // [2][kWarps][kChunk]
@@ -162,28 +190,16 @@ __device__ void scan_rows_cols(const uint4* __restrict__ A, int n1, const uint4*
       const uint32_t jbase = chunk * kChunk;
       uint2* part = sm.part + ((it & 1) * kWarps + warp) * kChunk;
       if (nr > 0) {
-        for (int c = 0; c < nc; ++c) {
-          const uint4 b0 = bs[2 * c], b1 = bs[2 * c + 1];
-          uint32_t c1 = 0xFFFFFFFFu, c2 = 0xFFFFFFFFu;
-          const uint32_t j = jbase + c;
-#pragma unroll
-          for (int r = 0; r < kR; ++r) {
-            if (r < nr) {
-              const uint32_t d = hamming256<kCsa>(a[r], b0, b1);
-              const uint32_t kr = (d << kShift) + j;
-              const uint32_t t = max(m1[r], kr);
-              m1[r] = min(m1[r], kr);
-              m2[r] = min(m2[r], t);
-              const uint32_t kc = (d << kShift) + rid[r];
-              const uint32_t u = max(c1, kc);
-              c1 = min(c1, kc);
-              c2 = min(c2, u);
-            }
-          }
-          // fold the 32 lanes: smallest key, then the smallest of (owner's second, others' first)
-          const uint32_t g1 = __reduce_min_sync(0xFFFFFFFFu, c1);
-          const uint32_t g2 = __reduce_min_sync(0xFFFFFFFFu, c1 == g1 ? c2 : c1);
-          if (lane == 0) part[c] = make_uint2(g1, g2);
+        // the row-group count is warp-uniform: dispatch once per stage to a loop whose row dimension is a
+        // compile-time constant (a guard inside the loop costs a branch per distance and keeps the
+        // compiler from interleaving the independent rows)
+        switch (nr) {
+          case 1: scan_chunk<kCsa, 1>(a, m1, m2, rid, bs, nc, jbase, part, lane); break;
+          case 2: scan_chunk<kCsa, 2>(a, m1, m2, rid, bs, nc, jbase, part, lane); break;
+          case 3: scan_chunk<kCsa, 3>(a, m1, m2, rid, bs, nc, jbase, part, lane); break;
+          case 4: scan_chunk<kCsa, 4>(a, m1, m2, rid, bs, nc, jbase, part, lane); break;
+          case 5: scan_chunk<kCsa, 5>(a, m1, m2, rid, bs, nc, jbase, part, lane); break;
+          default: scan_chunk<kCsa, kR>(a, m1, m2, rid, bs, nc, jbase, part, lane); break;
         }
       } else if (lane == 0) {
         for (int c = 0; c < nc; ++c) part[c] = make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
