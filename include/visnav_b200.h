@@ -95,6 +95,17 @@ int vslam_match(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_t* d2, 
  * queries (BASELINE config 4) use this together with vslam_match. */
 int vslam_best2(vslam_ctx* ctx, const uint32_t* q, int nq, const uint32_t* db, int ndb,
                 int32_t* out3);
+/* visnav::find_matches_landmarks (vo_utils.h:83-167): keypoints of the current frame against the
+ * projected map landmarks.  kp_xy [n_kp][2] / kp_desc [n_kp][8]: kdl.corners / kdl.corner_descriptors;
+ * proj_xy [n_proj][2]: projected_points (their order decides ties exactly as std::partial_sort does in
+ * the reference); landmark j owns the observation descriptors obs_desc[obs_offsets[j] ..
+ * obs_offsets[j+1]) (the host side gathers feature_corners.at(fcid).corner_descriptors[f_id] over
+ * landmarks.at(projected_track_ids[j]).all_obs).  pairs[cap][2] = (feature id, index j into
+ * proj_xy) in ascending feature id; the caller maps j to projected_track_ids[j]. */
+int vslam_match_landmarks(vslam_ctx* ctx, const double* kp_xy, const uint32_t* kp_desc, int n_kp,
+                          const double* proj_xy, int n_proj, const int32_t* obs_offsets,
+                          const uint32_t* obs_desc, double match_max_dist_2d, int threshold,
+                          double dist_2_best, int32_t* pairs, int cap, int* n);
 /* Min-eigenvalue response map (the float image cv::goodFeaturesToTrack thresholds,
  * OCV featureselect.cpp:411) -- exported for parity tests.  lam: h x w floats, dense. */
 int vslam_response(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch, float* lam);

@@ -155,6 +155,47 @@ class Oracle:
         return out
 
 
+def _lm_args(kp_xy, kp_desc, proj_xy, obs_offsets, obs_desc):
+    kp_xy = np.ascontiguousarray(kp_xy, np.float64).reshape(-1, 2)
+    kp_desc = np.ascontiguousarray(kp_desc, np.uint32).reshape(-1, 8)
+    proj_xy = np.ascontiguousarray(proj_xy, np.float64).reshape(-1, 2)
+    obs_offsets = np.ascontiguousarray(obs_offsets, np.int32)
+    obs_desc = np.ascontiguousarray(obs_desc, np.uint32).reshape(-1, 8)
+    assert len(kp_xy) == len(kp_desc) and len(obs_offsets) == len(proj_xy) + 1
+    return kp_xy, kp_desc, proj_xy, obs_offsets, obs_desc
+
+
+_LM_ARGTYPES = [_f64p, _u32p, C.c_int, _f64p, C.c_int, _i32p, _u32p, C.c_double, C.c_int, C.c_double, _i32p, C.c_int]
+
+
+def _match_landmarks(fn, kp_xy, kp_desc, proj_xy, obs_offsets, obs_desc, max_dist_2d, threshold, ratio):
+    kp_xy, kp_desc, proj_xy, obs_offsets, obs_desc = _lm_args(kp_xy, kp_desc, proj_xy, obs_offsets, obs_desc)
+    cap = max(1, len(kp_xy))
+    pairs = np.empty((cap, 2), np.int32)
+    fn.restype = C.c_int
+    fn.argtypes = _LM_ARGTYPES
+    n = fn(_p(kp_xy, _f64p), _p(kp_desc, _u32p), len(kp_xy), _p(proj_xy, _f64p), len(proj_xy),
+           _p(obs_offsets, _i32p), _p(obs_desc, _u32p), float(max_dist_2d), int(threshold), float(ratio),
+           _p(pairs, _i32p), cap)
+    assert 0 <= n <= cap, n
+    return pairs[:n].copy()
+
+
+def match_landmarks_port(kp_xy, kp_desc, proj_xy, obs_offsets, obs_desc, max_dist_2d=20.0, threshold=70, ratio=1.2):
+    """C restatement of find_matches_landmarks (vo_utils.h:83-167): [(feature id, projected index)]."""
+    return _match_landmarks(load_oracle().lib.vso_match_landmarks, kp_xy, kp_desc, proj_xy, obs_offsets, obs_desc,
+                            max_dist_2d, threshold, ratio)
+
+
+def match_landmarks_ref(kp_xy, kp_desc, proj_xy, obs_offsets, obs_desc, max_dist_2d=20.0, threshold=70, ratio=1.2):
+    """The reference's own find_matches_landmarks (oracle/_ref/libvisnav_ref_lm.so), or None if not built."""
+    path = os.path.join(_HERE, "_ref", "libvisnav_ref_lm.so")
+    if not os.path.exists(path):
+        return None
+    return _match_landmarks(C.CDLL(path).ref_match_landmarks, kp_xy, kp_desc, proj_xy, obs_offsets, obs_desc,
+                            max_dist_2d, threshold, ratio)
+
+
 def load_oracle():
     path = os.path.join(_HERE, "liboracle.so")
     if not os.path.exists(path):

@@ -394,6 +394,52 @@ void vso_best2(const uint32_t* q, int nq, const uint32_t* db, int ndb, int32_t* 
     scan_best2(q + (size_t)i * 8, db, ndb, &out3[3 * i], &out3[3 * i + 1], &out3[3 * i + 2]);
 }
 
+/* ---- landmark matching ---------------------------------------------------------------------
+ * visnav::find_matches_landmarks (include/visnav/vo_utils.h:83-167).  kp_xy/kp_desc: the frame's
+ * keypoints; proj_xy: projected landmark positions in the caller's order; landmark j owns the
+ * observation descriptors obs_desc[obs_off[j] .. obs_off[j+1]).  pairs = (feature id, j).
+ *
+ * The reference orders the in-radius candidates with std::partial_sort(first, first + 2, last,
+ * by distance) (:132-137), which is not stable.  The two-element heap below restates libstdc++'s
+ * algorithm (bits/stl_algo.h __heap_select / __sort_heap, bits/stl_heap.h __make_heap, __pop_heap,
+ * __adjust_heap, __push_heap) for middle = first + 2, so equally good candidates are named in the
+ * same order as the reference does (pinned against the reference build in oracle/_ref). */
+int vso_match_landmarks(const double* kp_xy, const uint32_t* kp_desc, int n_kp, const double* proj_xy,
+                        int n_proj, const int32_t* obs_off, const uint32_t* obs_desc,
+                        double match_max_dist_2d, int threshold, double dist_2_best, int32_t* pairs,
+                        int cap) {
+  int m = 0;
+  for (int i = 0; i < n_kp; i++) {
+    int n = 0, id0 = 0, d0 = 0, id1 = 0, d1 = 0; /* heap: (id0,d0) on top, (id1,d1) below */
+    for (int j = 0; j < n_proj; j++) {
+      const double dx = kp_xy[2 * i] - proj_xy[2 * j], dy = kp_xy[2 * i + 1] - proj_xy[2 * j + 1];
+      const double dist = sqrt(dx * dx + dy * dy); /* Eigen norm(), :108 (built with -ffp-contract=off) */
+      if (!(dist < match_max_dist_2d)) continue;
+      int best = 256; /* :113 */
+      for (int o = obs_off[j]; o < obs_off[j + 1]; o++) {
+        const int d = hamming256(obs_desc + (size_t)o * 8, kp_desc + (size_t)i * 8);
+        if (d < best) best = d;
+      }
+      if (n == 0) { id1 = j; d1 = best; }
+      else if (n == 1) { /* make_heap: the later element goes on top unless it is strictly smaller */
+        if (best < d1) { id0 = id1; d0 = d1; id1 = j; d1 = best; }
+        else { id0 = j; d0 = best; }
+      } else if (best < d0) { /* __heap_select: pop the top, sift the newcomer */
+        if (d1 < best) { id0 = j; d0 = best; }
+        else { id0 = id1; d0 = d1; id1 = j; d1 = best; }
+      }
+      n++;
+    }
+    if (n == 0) continue;
+    if (d1 >= threshold) continue;                                    /* :142 */
+    const int second = n >= 2 ? d0 : 256;                             /* :146, :154 */
+    if ((double)second < (double)d1 * dist_2_best) continue;
+    if (m < cap) { pairs[2 * m] = i; pairs[2 * m + 1] = id1; }
+    m++;
+  }
+  return m;
+}
+
 /* detect + angles + describe for one image (keypoints.h:223-229). */
 int vso_detect_describe(const uint8_t* img, int w, int h, int pitch, int num_features,
                         int rotate, int contract, double* xy, double* angles,

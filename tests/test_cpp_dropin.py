@@ -51,3 +51,36 @@ def test_dropin_header_matches_oracle(tmp_path, oracle_port):
     bits = np.array([[int(c) for c in k[4][::-1]] for k in ks], np.uint8)
     words = np.packbits(bits.reshape(len(ks), 8, 32), axis=2, bitorder="little").view(np.uint32).reshape(len(ks), 8)
     assert np.array_equal(words, dl)
+
+
+EXE_LM = os.path.join(ROOT, "tests", "cpp", "test_dropin_landmarks")
+
+
+def _build_lm():
+    cmd = ["g++", "-std=c++14", "-O2", "-I", os.path.join(ROOT, "tests", "cpp", "stubs"), "-I", os.path.join(ROOT, "include"),
+           "-o", EXE_LM, os.path.join(ROOT, "tests", "cpp", "test_dropin_landmarks.cpp"), "-L",
+           os.path.join(ROOT, "visual-slam_b200", "csrc"), "-lvisnav_b200",
+           "-Wl,-rpath," + os.path.join(ROOT, "visual-slam_b200", "csrc")]
+    subprocess.run(cmd, check=True)
+
+
+def test_landmark_dropin_compiles_and_fails_loudly_without_gpu():
+    import torch
+    _build_lm()
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    p = subprocess.run([EXE_LM], capture_output=True, text=True)
+    assert p.returncode == 3 and "no usable sm_100 GPU" in p.stdout
+
+
+@pytest.mark.gpu
+def test_landmark_dropin_header():
+    """find_matches_landmarks_b200 on std containers shaped like the reference's: every second keypoint
+    has one landmark 2.5 px away with 3 flipped bits -> 20 matches (feature 2k, track 500 + 2k)."""
+    _build_lm()
+    p = subprocess.run([EXE_LM], capture_output=True, text=True)
+    assert p.returncode == 0, p.stdout[-500:] + p.stderr[-500:]
+    lines = p.stdout.splitlines()
+    assert lines[0] == "matches 20"
+    got = [tuple(int(v) for v in ln.split()[1:]) for ln in lines[1:]]
+    assert got == [(j, 500 + j) for j in range(0, 40, 2)]

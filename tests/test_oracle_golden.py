@@ -88,3 +88,42 @@ def test_contraction_modes_differ_only_rarely(oracle_port):
     b = oracle_port.describe(g["left"], g["xy_l"], g["ang_l"], contract=False)
     assert np.array_equal(a, g["desc_l"])                 # oracle/_ref was built with GCC's default contraction
     assert (a != b).any(1).mean() < 0.05                  # the two roundings almost never disagree
+
+
+def _lm_params(key):
+    _, r, thr, ratio = key.split("_")
+    return float(r.replace("p", ".")), int(thr), float(ratio.replace("p", "."))
+
+
+def test_landmark_matching_vs_reference_fixture():
+    """vso_match_landmarks (incl. its restatement of libstdc++'s partial_sort tie order) against the
+    outputs of the reference's own find_matches_landmarks (vo_utils.h:83-167)."""
+    import oracle.oracle as oo
+    g = _load("landmarks_220x200")
+    sc = (g["kp_xy"], g["kp_desc"], g["proj_xy"], g["obs_offsets"], g["obs_desc"])
+    keys = [k for k in g.files if k.startswith("m_")]
+    assert len(keys) == 4
+    tie_cases = 0
+    for k in keys:
+        r, thr, ratio = _lm_params(k)
+        got = oo.match_landmarks_port(*sc, r, thr, ratio)
+        assert np.array_equal(got, g[k]), k
+        live = oo.match_landmarks_ref(*sc, r, thr, ratio)
+        if live is not None:
+            assert np.array_equal(live, g[k]), k
+        tie_cases += len(g[k])
+    assert tie_cases > 100
+
+
+def test_landmark_matching_edge_cases():
+    import oracle.oracle as oo
+    from visnav_b200 import workloads as wl
+    sc = wl.landmark_scene(n_kp=50, n_landmarks=40, seed=3)
+    e2, e8 = np.zeros((0, 2)), np.zeros((0, 8), np.uint32)
+    assert len(oo.match_landmarks_port(e2, e8, sc[2], sc[3], sc[4])) == 0          # no keypoints
+    assert len(oo.match_landmarks_port(sc[0], sc[1], e2, np.zeros(1, np.int32), e8)) == 0   # no landmarks
+    # landmarks without observations keep the initial 256 and can never pass a threshold <= 256
+    off0 = np.zeros(len(sc[2]) + 1, np.int32)
+    assert len(oo.match_landmarks_port(sc[0], sc[1], sc[2], off0, e8, 20.0, 256, 1.0)) == 0
+    # radius 0: nothing is inside the gate
+    assert len(oo.match_landmarks_port(*sc, 0.0, 70, 1.2)) == 0

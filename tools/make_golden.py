@@ -8,6 +8,8 @@ container only (needs cv2 and /root/reference; neither exists on the GPU box):
     python wheel returns the same ordered corners as the vendored OpenCV 4.7.0-dev.
   * oracle/_ref/libvisnav_ref.so: the reference's own computeAngles / computeDescriptors /
     matchDescriptors compiled from /root/reference/include/visnav/keypoints.h (oracle/Makefile).
+  * oracle/_ref/libvisnav_ref_lm.so: the reference's own find_matches_landmarks
+    (/root/reference/include/visnav/vo_utils.h:83-167, with its vendored Eigen).
 
 The inputs are seeded synthetic images (visual-slam_b200/workloads.py); they are stored too, so the
 fixtures do not depend on numpy's generator staying bit-stable.
@@ -73,5 +75,22 @@ def main():
     print("match_ties", {k: len(v) for k, v in rec.items() if k.startswith("m_")})
 
 
+def landmarks():
+    """find_matches_landmarks by the reference's own function (oracle/_ref/libvisnav_ref_lm.so)."""
+    import oracle.oracle as oo
+    sc = wl.landmark_scene(n_kp=220, n_landmarks=200, seed=11)
+    rec = dict(kp_xy=sc[0], kp_desc=sc[1], proj_xy=sc[2], obs_offsets=sc[3], obs_desc=sc[4])
+    for r, thr, ratio in [(20.0, 70, 1.2), (35.0, 256, 1.0), (12.5, 40, 1.5), (20.0, 70, 0.9)]:
+        m = oo.match_landmarks_ref(*sc, r, thr, ratio)
+        assert m is not None, "build oracle/_ref first (make -C oracle)"
+        rec["m_%s_%d_%s" % (str(r).replace(".", "p"), thr, str(ratio).replace(".", "p"))] = m
+    np.savez_compressed(os.path.join(OUT, "landmarks_220x200.npz"), **rec)
+    print("landmarks", {k: len(v) for k, v in rec.items() if k.startswith("m_")})
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "landmarks":
+        landmarks()
+    else:
+        main()
+        landmarks()

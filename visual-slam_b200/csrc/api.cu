@@ -113,7 +113,7 @@ void vslam_destroy(vslam_ctx* ctx) {
   }
   DevBuf* bufs[] = {&ctx->img, &ctx->xy, &ctx->ang, &ctx->desc, &ctx->cnt, &ctx->lam, &ctx->cand, &ctx->candcnt,
                     &ctx->imgmax, &ctx->selws, &ctx->d1, &ctx->d2, &ctx->pairs, &ctx->mcnt, &ctx->rowpart,
-                    &ctx->colstat, &ctx->jobs};
+                    &ctx->colstat, &ctx->jobs, &ctx->lm};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 8; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -344,6 +344,60 @@ int vslam_match(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_t* d2, 
   *n = 0;
   if (n1 == 0 || n2 == 0) return VSLAM_OK;  // keypoints.h:327 clear(); nothing can pass
   return match_common(ctx, d1, n1, d2, n2, threshold, dist_2_best, pairs, cap, n, nullptr);
+}
+
+int vslam_match_landmarks(vslam_ctx* ctx, const double* kp_xy, const uint32_t* kp_desc, int n_kp,
+                          const double* proj_xy, int n_proj, const int32_t* obs_offsets, const uint32_t* obs_desc,
+                          double match_max_dist_2d, int threshold, double dist_2_best, int32_t* pairs, int cap,
+                          int* n) {
+  if (!ctx) return VSLAM_E_ARG;
+  if (!n || n_kp < 0 || n_proj < 0 || cap < 0 || (n_kp > 0 && (!kp_xy || !kp_desc)) ||
+      (n_proj > 0 && (!proj_xy || !obs_offsets)) || (cap > 0 && !pairs))
+    return vs_fail(ctx, VSLAM_E_ARG, "bad landmark-match arguments");
+  *n = 0;
+  if (n_kp == 0 || n_proj == 0) return VSLAM_OK;  // vo_utils.h:92 clear(); no candidate can exist
+  const int total_obs = obs_offsets[n_proj];
+  if (obs_offsets[0] != 0 || total_obs < 0 || (total_obs > 0 && !obs_desc))
+    return vs_fail(ctx, VSLAM_E_ARG, "bad observation offsets");
+  for (int j = 0; j < n_proj; ++j)
+    if (obs_offsets[j + 1] < obs_offsets[j]) return vs_fail(ctx, VSLAM_E_ARG, "observation offsets must ascend");
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  // one staging buffer: [kp_xy | proj_xy | kp_desc | obs_desc | obs_offsets | result | pairs | count]
+  auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+  const int dcap = cap > 0 ? cap : 1;
+  const size_t o_kpxy = 0, o_proj = o_kpxy + up((size_t)n_kp * 16), o_kpd = o_proj + up((size_t)n_proj * 16),
+               o_obsd = o_kpd + up((size_t)n_kp * 32), o_off = o_obsd + up((size_t)total_obs * 32 + 32),
+               o_res = o_off + up((size_t)(n_proj + 1) * 4), o_pairs = o_res + up((size_t)n_kp * 4),
+               o_cnt = o_pairs + up((size_t)dcap * 8), total = o_cnt + 256;
+  VS_CUDA(ctx, ctx->lm.reserve(total));
+  uint8_t* base = ctx->lm.as<uint8_t>();
+  cudaStream_t st = ctx->stream;
+  VS_CUDA(ctx, cudaMemcpyAsync(base + o_kpxy, kp_xy, (size_t)n_kp * 16, cudaMemcpyHostToDevice, st));
+  VS_CUDA(ctx, cudaMemcpyAsync(base + o_proj, proj_xy, (size_t)n_proj * 16, cudaMemcpyHostToDevice, st));
+  VS_CUDA(ctx, cudaMemcpyAsync(base + o_kpd, kp_desc, (size_t)n_kp * 32, cudaMemcpyHostToDevice, st));
+  if (total_obs > 0)
+    VS_CUDA(ctx, cudaMemcpyAsync(base + o_obsd, obs_desc, (size_t)total_obs * 32, cudaMemcpyHostToDevice, st));
+  VS_CUDA(ctx, cudaMemcpyAsync(base + o_off, obs_offsets, (size_t)(n_proj + 1) * 4, cudaMemcpyHostToDevice, st));
+  VS_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
+  int rc = launch_match_landmarks(ctx, reinterpret_cast<const double*>(base + o_kpxy),
+                                  reinterpret_cast<const uint32_t*>(base + o_kpd), n_kp,
+                                  reinterpret_cast<const double*>(base + o_proj), n_proj,
+                                  reinterpret_cast<const int32_t*>(base + o_off),
+                                  reinterpret_cast<const uint32_t*>(base + o_obsd), match_max_dist_2d, threshold,
+                                  dist_2_best, reinterpret_cast<int32_t*>(base + o_res),
+                                  reinterpret_cast<int32_t*>(base + o_pairs), reinterpret_cast<int32_t*>(base + o_cnt),
+                                  dcap);
+  if (rc) return rc;
+  VS_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));
+  int32_t* hn = static_cast<int32_t*>(ctx->pinned);
+  VS_CUDA(ctx, cudaMemcpyAsync(hn, base + o_cnt, 4, cudaMemcpyDeviceToHost, st));
+  VS_CUDA(ctx, cudaStreamSynchronize(st));
+  *n = *hn;
+  const int m = *n < cap ? *n : cap;
+  if (m > 0) VS_CUDA(ctx, cudaMemcpy(pairs, base + o_pairs, (size_t)m * 8, cudaMemcpyDeviceToHost));
+  VS_CUDA(ctx, cudaEventElapsedTime(&ctx->last_match_ms, ctx->ev[0], ctx->ev[1]));
+  if (*n > cap) return vs_fail(ctx, VSLAM_E_CAPACITY, "more landmark matches than the output capacity");
+  return VSLAM_OK;
 }
 
 int vslam_best2(vslam_ctx* ctx, const uint32_t* q, int nq, const uint32_t* db, int ndb, int32_t* out3) {

@@ -47,6 +47,7 @@ struct vslam_ctx {
   DevBuf img, xy, ang, desc, cnt, lam;
   DevBuf cand, candcnt, imgmax, selws;
   DevBuf d1, d2, pairs, mcnt, rowpart, colstat, jobs;
+  DevBuf lm;  // vslam_match_landmarks staging
   void* pinned = nullptr;  // small pinned staging block for counts
   // pipeline plans of vslam_stereo_batch, kept between calls (same geometry -> no reallocation)
   static constexpr int kMaxBatchDepth = 4;
@@ -120,3 +121,8 @@ int launch_build_store_jobs(vslam_ctx* ctx, const int32_t* jobs_i2, int n_jobs, 
                             const int64_t* offsets, const int32_t* counts, int n_sets, int32_t* pairs,
                             int32_t* out_counts, int cap, MatchJob* out);
 int launch_popc_peak(vslam_ctx* ctx, double* popc_per_s);
+// landmarks.cu
+int launch_match_landmarks(vslam_ctx* ctx, const double* kp_xy, const uint32_t* kp_desc, int n_kp,
+                           const double* proj_xy, int n_proj, const int32_t* obs_off, const uint32_t* obs_desc,
+                           double max_dist_2d, int threshold, double ratio, int32_t* result, int32_t* pairs,
+                           int32_t* count, int cap);

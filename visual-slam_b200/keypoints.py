@@ -29,6 +29,7 @@ ABI_SYMBOLS = [
     "vslam_create", "vslam_destroy", "vslam_last_error", "vslam_set_option", "vslam_stream", "vslam_sync",
     "vslam_launch_count", "vslam_host_alloc", "vslam_host_free", "vslam_detect", "vslam_angles",
     "vslam_describe", "vslam_detect_describe", "vslam_match", "vslam_best2", "vslam_response",
+    "vslam_match_landmarks",
     "vslam_detect_describe_batch", "vslam_stereo_batch", "vslam_stereo_plan_create",
     "vslam_stereo_plan_destroy", "vslam_stereo_plan_upload", "vslam_stereo_plan_run",
     "vslam_stereo_plan_download", "vslam_stereo_plan_last_ms", "vslam_desc_store_create",
@@ -90,6 +91,7 @@ def load_library():
     L.vslam_detect_describe.argtypes = [vp, vp, i, i, i, i, i, vp, vp, vp, i, C.POINTER(i)]
     L.vslam_match.argtypes = [vp, vp, i, vp, i, i, d, vp, i, C.POINTER(i)]
     L.vslam_best2.argtypes = [vp, vp, i, vp, i, vp]
+    L.vslam_match_landmarks.argtypes = [vp, vp, vp, i, vp, i, vp, vp, d, i, d, vp, i, C.POINTER(i)]
     L.vslam_response.argtypes = [vp, vp, i, i, i, vp]
     L.vslam_detect_describe_batch.argtypes = [vp, vp, i, i, i, i, sz, i, i, vp, vp, vp, vp, i]
     L.vslam_stereo_batch.argtypes = [vp, vp, i, C.POINTER(StereoParams), vp, vp, vp, vp, vp, vp, i]
@@ -249,6 +251,24 @@ class Context:
         n = C.c_int(0)
         self._check(self.lib.vslam_match(self.h, _ptr(d1), len(d1), _ptr(d2), len(d2), int(threshold),
                                          float(dist_2_best), _ptr(pairs), cap, C.byref(n)))
+        return pairs[:n.value].copy()
+
+    def match_landmarks(self, kp_xy, kp_desc, proj_xy, obs_offsets, obs_desc, match_max_dist_2d=20.0, threshold=70,
+                        dist_2_best=1.2, cap=None):
+        """find_matches_landmarks (vo_utils.h:83-167): returns [(feature id, projected index)] as int32 [m, 2]."""
+        kp_xy = np.ascontiguousarray(kp_xy, np.float64).reshape(-1, 2)
+        kp_desc = np.ascontiguousarray(kp_desc, np.uint32).reshape(-1, 8)
+        proj_xy = np.ascontiguousarray(proj_xy, np.float64).reshape(-1, 2)
+        obs_offsets = np.ascontiguousarray(obs_offsets, np.int32)
+        obs_desc = np.ascontiguousarray(obs_desc, np.uint32).reshape(-1, 8)
+        assert len(kp_xy) == len(kp_desc) and len(obs_offsets) == len(proj_xy) + 1
+        cap = len(kp_xy) if cap is None else cap
+        pairs = np.empty((max(cap, 1), 2), np.int32)
+        n = C.c_int(0)
+        self._check(self.lib.vslam_match_landmarks(self.h, _ptr(kp_xy), _ptr(kp_desc), len(kp_xy), _ptr(proj_xy),
+                                                   len(proj_xy), _ptr(obs_offsets), _ptr(obs_desc),
+                                                   C.c_double(match_max_dist_2d), int(threshold),
+                                                   C.c_double(dist_2_best), _ptr(pairs), cap, C.byref(n)))
         return pairs[:n.value].copy()
 
     def best2(self, q, db):
