@@ -118,6 +118,18 @@ int vslam_detect_describe_batch(vslam_ctx* ctx, const uint8_t* images, int count
                                 int pitch, size_t image_stride, int num_features, int rotate,
                                 double* xy, double* angles, uint32_t* desc, int32_t* n_kp, int cap);
 
+/* ---- multi-scale extension (BASELINE config 5; no reference behaviour) ------ */
+/* Factor-2 pyramid, level k+1 (x, y) = (a + b + c + d + 2) >> 2 over the 2x2 block of level k, level k
+ * being (w >> k) x (h >> k); detectKeypointsAndDescriptors semantics per level with num_features[k]
+ * (coordinates are in the level's own pixels).  Per image, level k's outputs occupy the slab entries
+ * [sum(num_features[0..k)), +n_kp[image][k]): xy [count][cap][2], angles [count][cap],
+ * desc [count][cap][8], n_kp [count][n_levels]; cap >= sum(num_features). */
+#define VSLAM_MAX_PYRAMID_LEVELS 8
+int vslam_pyramid_detect_describe_batch(vslam_ctx* ctx, const uint8_t* images, int count, int w, int h,
+                                        int pitch, size_t image_stride, int n_levels,
+                                        const int* num_features, int rotate, double* xy, double* angles,
+                                        uint32_t* desc, int32_t* n_kp, int cap);
+
 /* ---- batched stereo front end: detect+describe both images, then matchDescriptors -------- */
 /* slam.cpp:1125-1143 for `count` independent stereo pairs.  images: [count][2] images (left,
  * right) `image_stride` bytes apart.  Per image outputs as above with 2*count images; per pair:

@@ -113,7 +113,7 @@ void vslam_destroy(vslam_ctx* ctx) {
   }
   DevBuf* bufs[] = {&ctx->img, &ctx->xy, &ctx->ang, &ctx->desc, &ctx->cnt, &ctx->lam, &ctx->cand, &ctx->candcnt,
                     &ctx->imgmax, &ctx->selws, &ctx->d1, &ctx->d2, &ctx->pairs, &ctx->mcnt, &ctx->rowpart,
-                    &ctx->colstat, &ctx->jobs, &ctx->lm};
+                    &ctx->colstat, &ctx->jobs, &ctx->lm, &ctx->pyr};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 8; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -692,6 +692,81 @@ int vslam_detect_describe_batch(vslam_ctx* ctx, const uint8_t* images, int count
     VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     for (int i = 0; i < nc; ++i)
       if ((rc = kp_status(ctx, n_kp[c0 + i]))) return rc;
+  }
+  return VSLAM_OK;
+}
+
+int vslam_pyramid_detect_describe_batch(vslam_ctx* ctx, const uint8_t* images, int count, int w, int h, int pitch,
+                                        size_t image_stride, int n_levels, const int* num_features, int rotate,
+                                        double* xy, double* angles, uint32_t* desc, int32_t* n_kp, int cap) {
+  int rc = check_image(ctx, images, w, h, pitch);
+  if (rc) return rc;
+  if (count < 0 || n_levels < 1 || n_levels > VSLAM_MAX_PYRAMID_LEVELS || !num_features || cap <= 0 || !xy ||
+      !angles || !desc || !n_kp)
+    return vs_fail(ctx, VSLAM_E_ARG, "bad pyramid arguments");
+  long long total_feat = 0;
+  for (int k = 0; k < n_levels; ++k) {
+    if (num_features[k] <= 0) return vs_fail(ctx, VSLAM_E_ARG, "num_features[k] must be positive");
+    total_feat += num_features[k];
+  }
+  if (total_feat > cap) return vs_fail(ctx, VSLAM_E_ARG, "cap must hold the sum of num_features");
+  if (count == 0) return VSLAM_OK;
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  // level geometry: level k is (w >> k) x (h >> k)
+  int lw[VSLAM_MAX_PYRAMID_LEVELS], lh[VSLAM_MAX_PYRAMID_LEVELS], lp[VSLAM_MAX_PYRAMID_LEVELS];
+  size_t loff[VSLAM_MAX_PYRAMID_LEVELS + 1];
+  const int chunk = count < 64 ? count : 64;
+  loff[1] = 0;
+  for (int k = 0; k < n_levels; ++k) {
+    lw[k] = w >> k; lh[k] = h >> k; lp[k] = lw[k] > 0 ? dev_pitch(lw[k]) : 16;
+    if (k >= 1) loff[k + 1] = loff[k] + align_up((size_t)lp[k] * (lh[k] > 0 ? lh[k] : 1) * chunk, 256);
+  }
+  if (n_levels > 1) VS_CUDA(ctx, ctx->pyr.reserve(loff[n_levels] + 256));
+  const size_t cp = cap;
+  for (int c0 = 0; c0 < count; c0 += chunk) {
+    const int nc = count - c0 < chunk ? count - c0 : chunk;
+    DevImages lv[VSLAM_MAX_PYRAMID_LEVELS];
+    rc = upload_images(ctx, ctx->img, images + image_stride * (size_t)c0, nc, w, h, pitch, image_stride, &lv[0], ctx->stream);
+    if (rc) return rc;
+    VS_CUDA(ctx, ctx->xy.reserve((size_t)nc * cp * 16));
+    VS_CUDA(ctx, ctx->ang.reserve((size_t)nc * cp * 8));
+    VS_CUDA(ctx, ctx->desc.reserve((size_t)nc * cp * 32));
+    VS_CUDA(ctx, ctx->cnt.reserve((size_t)nc * n_levels * 4));
+    size_t feat_off = 0;
+    for (int k = 0; k < n_levels; ++k) {
+      if (k >= 1) {
+        lv[k].base = ctx->pyr.as<uint8_t>() + loff[k];
+        lv[k].w = lw[k]; lv[k].h = lh[k]; lv[k].pitch = lp[k]; lv[k].stride = (size_t)lp[k] * (lh[k] > 0 ? lh[k] : 1);
+        rc = launch_pyr_down(ctx, lv[k - 1], lv[k], nc);
+        if (rc) return rc;
+      }
+      int32_t* cnt_k = ctx->cnt.as<int32_t>() + (size_t)k * nc;  // level-major on the device
+      if (lw[k] < 2 * kEdgeThreshold + 1 || lh[k] < 2 * kEdgeThreshold + 1) {
+        VS_CUDA(ctx, cudaMemsetAsync(cnt_k, 0, (size_t)nc * 4, ctx->stream));  // nothing survives the 19 px border
+      } else {
+        DetectWorkspace ws;
+        rc = prepare_detect_ws(ctx, lw[k], lh[k], nc, ctx->cand, ctx->candcnt, ctx->imgmax, ctx->selws, &ws);
+        if (rc) return rc;
+        // the level's outputs start feat_off entries into each image's slab (stride cap)
+        double* xy_k = ctx->xy.as<double>() + feat_off * 2;
+        rc = launch_response(ctx, lv[k], nc, ws, nullptr);
+        if (!rc) rc = launch_select(ctx, lv[k], nc, ws, num_features[k], kQuality, kMinDistance, kEdgeThreshold, xy_k, cnt_k, cap);
+        if (!rc) rc = launch_orient_describe(ctx, lv[k], nc, xy_k, cnt_k, cap, rotate ? 1 : 0,
+                                             ctx->ang.as<double>() + feat_off, ctx->desc.as<uint32_t>() + feat_off * 8);
+        if (rc) return rc;
+      }
+      feat_off += num_features[k];
+    }
+    VS_CUDA(ctx, cudaMemcpyAsync(xy + (size_t)c0 * cp * 2, ctx->xy.p, (size_t)nc * cp * 16, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaMemcpyAsync(angles + (size_t)c0 * cp, ctx->ang.p, (size_t)nc * cp * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaMemcpyAsync(desc + (size_t)c0 * cp * 8, ctx->desc.p, (size_t)nc * cp * 32, cudaMemcpyDeviceToHost, ctx->stream));
+    // n_kp is [count][n_levels] on the host: one strided copy per level
+    for (int k = 0; k < n_levels; ++k)
+      VS_CUDA(ctx, cudaMemcpy2DAsync(n_kp + (size_t)c0 * n_levels + k, (size_t)n_levels * 4,
+                                     ctx->cnt.as<int32_t>() + (size_t)k * nc, 4, 4, nc, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < nc * n_levels; ++i)
+      if ((rc = kp_status(ctx, n_kp[(size_t)c0 * n_levels + i]))) return rc;
   }
   return VSLAM_OK;
 }

@@ -48,6 +48,7 @@ struct vslam_ctx {
   DevBuf cand, candcnt, imgmax, selws;
   DevBuf d1, d2, pairs, mcnt, rowpart, colstat, jobs;
   DevBuf lm;  // vslam_match_landmarks staging
+  DevBuf pyr;  // vslam_pyramid_detect_describe_batch: levels 1.. of the chunk in flight
   void* pinned = nullptr;  // small pinned staging block for counts
   // pipeline plans of vslam_stereo_batch, kept between calls (same geometry -> no reallocation)
   static constexpr int kMaxBatchDepth = 4;
@@ -121,6 +122,8 @@ int launch_build_store_jobs(vslam_ctx* ctx, const int32_t* jobs_i2, int n_jobs, 
                             const int64_t* offsets, const int32_t* counts, int n_sets, int32_t* pairs,
                             int32_t* out_counts, int cap, MatchJob* out);
 int launch_popc_peak(vslam_ctx* ctx, double* popc_per_s);
+// pyramid.cu: dst level = 2x2 rounded mean of src (dst.w = src.w / 2, dst.h = src.h / 2)
+int launch_pyr_down(vslam_ctx* ctx, const DevImages& src, const DevImages& dst, int count);
 // landmarks.cu
 int launch_match_landmarks(vslam_ctx* ctx, const double* kp_xy, const uint32_t* kp_desc, int n_kp,
                            const double* proj_xy, int n_proj, const int32_t* obs_off, const uint32_t* obs_desc,

@@ -29,7 +29,7 @@ ABI_SYMBOLS = [
     "vslam_create", "vslam_destroy", "vslam_last_error", "vslam_set_option", "vslam_stream", "vslam_sync",
     "vslam_launch_count", "vslam_host_alloc", "vslam_host_free", "vslam_detect", "vslam_angles",
     "vslam_describe", "vslam_detect_describe", "vslam_match", "vslam_best2", "vslam_response",
-    "vslam_match_landmarks",
+    "vslam_match_landmarks", "vslam_pyramid_detect_describe_batch",
     "vslam_detect_describe_batch", "vslam_stereo_batch", "vslam_stereo_plan_create",
     "vslam_stereo_plan_destroy", "vslam_stereo_plan_upload", "vslam_stereo_plan_run",
     "vslam_stereo_plan_download", "vslam_stereo_plan_last_ms", "vslam_desc_store_create",
@@ -94,6 +94,7 @@ def load_library():
     L.vslam_match_landmarks.argtypes = [vp, vp, vp, i, vp, i, vp, vp, d, i, d, vp, i, C.POINTER(i)]
     L.vslam_response.argtypes = [vp, vp, i, i, i, vp]
     L.vslam_detect_describe_batch.argtypes = [vp, vp, i, i, i, i, sz, i, i, vp, vp, vp, vp, i]
+    L.vslam_pyramid_detect_describe_batch.argtypes = [vp, vp, i, i, i, i, sz, i, vp, i, vp, vp, vp, vp, i]
     L.vslam_stereo_batch.argtypes = [vp, vp, i, C.POINTER(StereoParams), vp, vp, vp, vp, vp, vp, i]
     L.vslam_stereo_plan_create.argtypes = [vp, i, i, i, i, C.POINTER(vp)]
     L.vslam_stereo_plan_destroy.argtypes = [vp]
@@ -298,6 +299,23 @@ class Context:
         self._check(self.lib.vslam_detect_describe_batch(self.h, _ptr(images), count, w, h, w, w * h, int(num_features),
                                                          int(bool(rotate)), _ptr(xy), _ptr(ang), _ptr(desc), _ptr(nkp), cap))
         return xy, ang, desc, nkp
+
+    def pyramid_detect_describe_batch(self, images, num_features, rotate=True):
+        """Multi-scale extension (config 5): num_features = per-level caps.  Returns per image and level
+        lists via (xy, angles, desc, n_kp[count][levels], level offsets)."""
+        images = np.ascontiguousarray(images, np.uint8)
+        count, h, w = images.shape
+        nf = np.ascontiguousarray(num_features, np.int32)
+        cap = int(nf.sum())
+        xy = np.empty((count, cap, 2), np.float64)
+        ang = np.empty((count, cap), np.float64)
+        desc = np.empty((count, cap, 8), np.uint32)
+        nkp = np.empty((count, len(nf)), np.int32)
+        self._check(self.lib.vslam_pyramid_detect_describe_batch(self.h, _ptr(images), count, w, h, w, w * h, len(nf),
+                                                                 _ptr(nf), int(bool(rotate)), _ptr(xy), _ptr(ang),
+                                                                 _ptr(desc), _ptr(nkp), cap))
+        off = np.concatenate([[0], np.cumsum(nf)[:-1]]).astype(np.int64)
+        return xy, ang, desc, nkp, off
 
     def stereo_batch(self, images, num_features=1500, rotate=True, threshold=70, dist_2_best=1.2, cap=None,
                      out=None):
