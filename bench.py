@@ -32,6 +32,10 @@ UNIT = "stereo pairs/s"
 # algorithmic bytes per image of the dominant kernel (response): the u8 image read once + the
 # 1500 x 8 B corner list it ultimately yields
 RESP_BYTES_PER_IMAGE = W_IMG * H_IMG + NUM_FEATURES * 8
+# DRAM traffic of the response kernel per image, from the ncu --set full capture of the same kernel
+# (profiles/r1d_response_raw.txt: dram__bytes_read.sum 185.04 MB + dram__bytes_write.sum 14.32 MB for
+# 512 images): the image is read once (1.00x its size), the rest is the candidate list.
+RESP_DRAM_BYTES_PER_IMAGE = (185.042944e6 + 14.323456e6) / 512
 
 
 def parse():
@@ -266,14 +270,16 @@ def run_ours(args):
         "stage_ms": {"response": stage_ms[1], "select": stage_ms[2], "describe": stage_ms[3], "match": stage_ms[4]},
         "roofline": {"kernel": "response_kernel (Sobel+cov+box+min-eig+local-max, TMA tiles)", "bound": "hbm",
                      "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "ms_per_launch": resp_ms, "algorithmic_bytes_per_launch": RESP_BYTES_PER_IMAGE * 2 * n_pairs},
+                     "traffic": RESP_DRAM_BYTES_PER_IMAGE * 2 * n_pairs,
+                     "traffic_source": "ncu --set full, profiles/r1d_response_raw.txt (per image x images per launch)",
+                     "ms_per_launch": resp_ms, "algorithmic_bytes_per_launch": RESP_BYTES_PER_IMAGE * 2 * n_pairs},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
         "gpu_launches": int(launches), "clocks": clocks,
         "results": {"mean_keypoints": float(res["n_kp"].mean()), "mean_matches": float(res["n_matches"].mean())},
     }
     if not args.no_cpu_baseline and world == 1:
         cores = os.cpu_count() or 1
-        sample = min(2 * cores, n_distinct)
+        sample = min(16 * cores, n_distinct)      # ~15-25 s of CPU work (73 ms per pair and core)
         v, done, kind = cpu_pairs_per_s(distinct[:sample], cores, budget_s=20.0)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
                                 "sample": "%d of the same synthetic pairs on %d host threads (reference functions from "

@@ -60,5 +60,55 @@ print("stereo", out["stereo"], flush=True)
 t0 = time.perf_counter(); ctx.stereo_batch(imgs); t1 = time.perf_counter()
 out["stereo_e2e_pageable_pairs_per_s"] = npairs / (t1 - t0)
 print("e2e pageable", out["stereo_e2e_pageable_pairs_per_s"])
+
+# config 3 in full: 500 keyframes x 1500, all 124 750 unordered pairs (counts only come back)
+if os.environ.get("PROBE_C3_FULL", "1") == "1":
+    kf = wl.keyframe_descriptors(500, 1500, 25)
+    store = DescStore(ctx, kf)
+    jobs = wl.keyframe_pair_jobs(500)
+    t0 = time.perf_counter()
+    _, counts = ctx.match_batch(store, jobs, 70, 1.2, want_matches=False)
+    wall = time.perf_counter() - t0
+    ms = ctx.last_match_ms()
+    dist = len(jobs) * 1500.0 * 1500.0
+    out["c3_full"] = dict(jobs=len(jobs), kernel_ms=ms, wall_s=wall, dist_per_s=dist / (ms * 1e-3),
+                          popc_equiv_per_s=8 * dist / (ms * 1e-3), frac_of_popc_peak=8 * dist / (ms * 1e-3) / out["popc_per_s"],
+                          mean_matches=float(counts.mean()), min_matches=int(counts.min()))
+    print("c3 full", out["c3_full"], flush=True)
+    store.close()
+
+# config 5: 1920x1080, 4000 features -- single-scale stereo plan and the 4-level pyramid extension
+n5 = int(os.environ.get("PROBE_C5_PAIRS", "32"))
+base5 = wl.synth_stereo_batch(min(n5, 8), 1920, 1080)
+imgs5 = np.concatenate([base5] * ((n5 + len(base5) - 1) // len(base5)))[:n5]
+plan5 = StereoPlan(ctx, 1920, 1080, n5, 4000)
+plan5.upload(imgs5)
+for rep in range(3):
+    plan5.run(n5, 4000)
+    ms5 = plan5.last_ms()
+r5 = plan5.download(n5)
+out["c5_single_scale"] = dict(pairs=n5, ms_total=ms5[0], ms_response=ms5[1], ms_select=ms5[2], ms_describe=ms5[3],
+                              ms_match=ms5[4], pairs_per_s=n5 / (ms5[0] * 1e-3), mean_kp=float(r5["n_kp"].mean()),
+                              mean_matches=float(r5["n_matches"].mean()))
+print("c5 single-scale", out["c5_single_scale"], flush=True)
+plan5.close()
+flat = np.ascontiguousarray(imgs5.reshape(-1, 1080, 1920))
+caps = [3012, 753, 188, 47]
+ctx.pyramid_detect_describe_batch(flat[:4], caps)
+t0 = time.perf_counter()
+res = ctx.pyramid_detect_describe_batch(flat, caps)
+dt = time.perf_counter() - t0
+out["c5_pyramid_e2e"] = dict(images=len(flat), wall_s=dt, images_per_s=len(flat) / dt,
+                             mean_kp_per_level=[float(v) for v in res[3].mean(axis=0)])
+print("c5 pyramid (pageable host arrays, H2D + D2H included)", out["c5_pyramid_e2e"], flush=True)
+
+# find_matches_landmarks: one frame against the projected map (slam.cpp:1159)
+sc = wl.landmark_scene(n_kp=1313, n_landmarks=2000, seed=1)
+t = []
+for rep in range(20):
+    t0 = time.perf_counter(); m = ctx.match_landmarks(*sc); t.append(time.perf_counter() - t0)
+out["landmarks"] = dict(n_kp=1313, n_landmarks=2000, call_ms=1e3 * float(np.median(t)), kernel_ms=ctx.last_match_ms(),
+                        matches=len(m))
+print("landmarks", out["landmarks"], flush=True)
 os.makedirs("gpurun_out", exist_ok=True)
 json.dump(out, open("gpurun_out/probe.json", "w"), indent=1)
