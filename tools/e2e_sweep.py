@@ -17,7 +17,7 @@ for k in range(0, n_pairs, 64):
 out = dict(xy=ctx.host_array((n_pairs * 2, cap, 2), np.float64), angles=ctx.host_array((n_pairs * 2, cap), np.float64),
            desc=ctx.host_array((n_pairs * 2, cap, 8), np.uint32), n_kp=ctx.host_array((n_pairs * 2,), np.int32),
            matches=ctx.host_array((n_pairs, cap, 2), np.int32), n_matches=ctx.host_array((n_pairs,), np.int32))
-for depth, chunk in [(2, 128), (3, 128), (4, 128), (3, 64), (4, 64), (3, 256), (4, 32), (1, 128)]:
+for depth, chunk in [(4, 128), (4, 64), (4, 96), (4, 192), (4, 256)]:
     ctx.set_option(VSLAM_OPT_BATCH_CHUNK, chunk)
     ctx.set_option(VSLAM_OPT_BATCH_DEPTH, depth)
     ctx.stereo_batch(imgs, 1500, True, 70, 1.2, cap, out=out)

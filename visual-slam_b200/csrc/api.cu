@@ -617,7 +617,27 @@ int vslam_stereo_batch(vslam_ctx* ctx, const uint8_t* images, int count, const v
   const int chunk = count < ctx->batch_chunk ? count : ctx->batch_chunk;
   vslam_stereo_plan* plans[vslam_ctx::kMaxBatchDepth] = {};
   int rc = VSLAM_OK;
-  const int nchunks = (count + chunk - 1) / chunk;
+  // Chunk schedule: the pipeline's fill (first upload) and drain (last compute + download) are not
+  // overlapped, so the first and last chunks are short (chunk/4, chunk/2) when the batch is long enough.
+  std::vector<int> sizes;
+  {
+    const int q = chunk / 4, hlf = chunk / 2;
+    if (q >= 8 && count >= 2 * (q + hlf) + chunk) {
+      int mid = count - 2 * (q + hlf);
+      sizes.push_back(q);
+      sizes.push_back(hlf);
+      while (mid > 0) {
+        const int c = mid < chunk ? mid : chunk;
+        sizes.push_back(c);
+        mid -= c;
+      }
+      sizes.push_back(hlf);
+      sizes.push_back(q);
+    } else {
+      for (int left = count; left > 0; left -= chunk) sizes.push_back(left < chunk ? left : chunk);
+    }
+  }
+  const int nchunks = (int)sizes.size();
   const int nplans = nchunks < ctx->batch_depth ? nchunks : ctx->batch_depth;
   for (int i = 0; i < nplans && !rc; ++i) {
     vslam_stereo_plan*& cp = ctx->batch_plans[i];
@@ -629,9 +649,9 @@ int vslam_stereo_batch(vslam_ctx* ctx, const uint8_t* images, int count, const v
     plans[i] = cp;
   }
   int bad_kp = 0;
-  for (int c0 = 0, k = 0; c0 < count && !rc; c0 += chunk, ++k) {
+  for (int c0 = 0, k = 0; k < nchunks && !rc; c0 += sizes[k], ++k) {
     vslam_stereo_plan* p = plans[k % nplans];
-    const int nc = count - c0 < chunk ? count - c0 : chunk;
+    const int nc = sizes[k];
     // stream order on p->stream serialises this chunk after the plan's previous download
     rc = vslam_stereo_plan_upload(p, images + sp->image_stride * 2 * (size_t)c0, nc, sp->pitch, sp->image_stride);
     if (!rc) rc = vslam_stereo_plan_run(p, nc, sp->num_features, sp->rotate_features, sp->match_threshold, sp->match_dist_2_best);
