@@ -78,7 +78,7 @@ if os.environ.get("PROBE_C3_FULL", "1") == "1":
     store.close()
 
 # config 5: 1920x1080, 4000 features -- single-scale stereo plan and the 4-level pyramid extension
-n5 = int(os.environ.get("PROBE_C5_PAIRS", "32"))
+n5 = int(os.environ.get("PROBE_C5_PAIRS", "296"))
 base5 = wl.synth_stereo_batch(min(n5, 8), 1920, 1080)
 imgs5 = np.concatenate([base5] * ((n5 + len(base5) - 1) // len(base5)))[:n5]
 plan5 = StereoPlan(ctx, 1920, 1080, n5, 4000)
