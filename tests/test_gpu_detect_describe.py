@@ -38,6 +38,21 @@ def test_detect_ordered_equal(ctx, oracle_port, w, h, nf):
     assert got.shape == want.shape and np.array_equal(got, want)
 
 
+def test_detect_strongest_subset_paths(ctx, oracle_port):
+    """1080p images have ~24 k candidates above the threshold: the select kernel decides on the strongest
+    8192 in shared memory when they yield num_features corners (4000) and must fall back to the complete
+    set on the global workspace when they do not (9000)."""
+    img = _image(1920, 1080, 77)
+    for nf in (4000, 9000):
+        got = ctx.detect(img, nf)
+        want = oracle_port.detect(img, nf)
+        assert got.shape == want.shape and np.array_equal(got, want), nf
+    rng = np.random.default_rng(8)
+    noise = rng.integers(0, 256, (600, 800), dtype=np.uint8)   # very dense candidates, many equal responses
+    for nf in (300, 3000, 6000):
+        assert np.array_equal(ctx.detect(noise, nf), oracle_port.detect(noise, nf)), nf
+
+
 def test_detect_special_images(ctx, oracle_port):
     flat = np.full((120, 160), 77, np.uint8)              # constant: no response anywhere
     assert len(ctx.detect(flat, 100)) == 0 == len(oracle_port.detect(flat, 100))
