@@ -107,6 +107,7 @@ template <bool kCsa, int kNr>
 __device__ __forceinline__ void scan_chunk(const uint32_t (&a)[kR][8], uint32_t (&m1)[kR], uint32_t (&m2)[kR],
                                            const uint32_t (&rid)[kR], const uint4* bs, int nc, uint32_t jbase,
                                            uint2* part, int lane) {
+#pragma unroll 2
   for (int c = 0; c < nc; ++c) {
     const uint4 b0 = bs[2 * c], b1 = bs[2 * c + 1];
     uint32_t c1 = 0xFFFFFFFFu, c2 = 0xFFFFFFFFu;
