@@ -1,5 +1,6 @@
 // common.cuh -- context, workspace and error plumbing shared by the kernels' host launchers.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -92,6 +93,8 @@ struct DetectWorkspace {
   size_t sel_ws_stride;
 };
 size_t detect_sel_ws_bytes(int w, int h, int cand_cap, int cell);
+// 3-D TMA tensor map {w, h, count} over an image set with a box of box_w x box_h x 1 bytes
+int make_image_tmap(vslam_ctx* ctx, const DevImages& im, int count, int box_w, int box_h, CUtensorMap* tmap);
 int launch_response(vslam_ctx* ctx, const DevImages& im, int count, const DetectWorkspace& ws,
                     float* lam_out /*optional, [count][h][w]*/);
 int launch_select(vslam_ctx* ctx, const DevImages& im, int count, const DetectWorkspace& ws,

@@ -57,7 +57,7 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b_signed_bytes, int 
 // Per-lane constants of the patch copy: lane = (row0, 16-byte chunk q); 5 rows per lane, 8 apart.
 struct StageLane {
   const uint8_t* src;   // image base + row0 * pitch + q * 16
-  uint32_t dst[2];      // shared address of (row0, q) in the two patch buffers of the warp
+  uint32_t dst0;        // shared address of (row0, q) in patch buffer 0 of the warp (buffer 1: + patch bytes)
   size_t pitch8;        // 8 image rows in bytes
   int q;
   bool row4;            // the lane's fifth row (row0 + 32) exists
@@ -74,7 +74,7 @@ __device__ __forceinline__ void stage_patch(const DescribeParams& p, const uint8
   if (kp_meta & 256) {
     if (L.q * 16 <= (kp_meta & 255) + kReach) {  // chunk holds a needed pixel; it ends at or before `pitch`
       const uint8_t* src = L.src + kp_off;
-      const uint32_t dst = L.dst[buf];
+      const uint32_t dst = L.dst0 + buf * (kPatchRows * kPatchPitch);
 #pragma unroll
       for (int it = 0; it < 5; ++it) {
         if (it < 4 || L.row4)
@@ -169,8 +169,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 8) orient_describe_kernel(c
     L.row4 = row0 + 32 < kPatchRows;
     L.src = im + (size_t)row0 * p.pitch + q * 16;
     L.pitch8 = (size_t)8 * p.pitch;
-    L.dst[0] = static_cast<uint32_t>(__cvta_generic_to_shared(patch0 + row0 * kPatchPitch + q * 16));
-    L.dst[1] = static_cast<uint32_t>(__cvta_generic_to_shared(patch1 + row0 * kPatchPitch + q * 16));
+    L.dst0 = static_cast<uint32_t>(__cvta_generic_to_shared(patch0 + row0 * kPatchPitch + q * 16));
   }
 #define STAGE(i_, buf_)                                                                                   \
   stage_patch(p, im, L, (buf_), __shfl_sync(0xFFFFFFFFu, kp_off, (i_)), __shfl_sync(0xFFFFFFFFu, kp_meta, (i_)), \
