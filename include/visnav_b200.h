@@ -158,8 +158,8 @@ int vslam_stereo_plan_run(vslam_stereo_plan* plan, int count, int num_features, 
                           int match_threshold, double match_dist_2_best);
 int vslam_stereo_plan_download(vslam_stereo_plan* plan, int count, double* xy, double* angles,
                                uint32_t* desc, int32_t* n_kp, int32_t* matches, int32_t* n_matches);
-/* time of the last run() on the device, CUDA events on the ctx stream: total and per stage
- * (response, select, describe, match); ms[5]. */
+/* time of the last run() on the device, CUDA events on the ctx stream: total (including the optional
+ * epipolar stage) and per stage (response, select, describe, match); ms[5]. */
 int vslam_stereo_plan_last_ms(vslam_stereo_plan* plan, float* ms);
 
 /* ---- batched matching against a device-resident descriptor store ----------------------- */
@@ -176,6 +176,55 @@ int vslam_match_batch(vslam_ctx* ctx, const vslam_desc_store* s, const int32_t* 
                       int cap);
 /* device time of the last vslam_match_batch / vslam_match / vslam_best2 kernels (ms) */
 float vslam_last_match_ms(vslam_ctx* ctx);
+
+/* ---- geometry that follows matching ------------------------------------------ */
+/* The four camera models of include/visnav/camera_models.h, all with the reference's 8-double parameter vector
+ * (fx fy cx cy + model parameters, AbstractCamera::getParam(); width/height = AbstractCamera::width()/height()):
+ *   pinhole :47-124    eucm :126-216 (alpha, beta)    ds :218-309 (xi, alpha)    kb4 :311-443 (k1..k4) */
+#define VSLAM_CAM_PINHOLE 0
+#define VSLAM_CAM_EUCM 1
+#define VSLAM_CAM_DS 2
+#define VSLAM_CAM_KB4 3
+typedef struct {
+  int model; /* VSLAM_CAM_* */
+  int width, height;
+  int reserved;
+  double param[8];
+} vslam_camera;
+/* AbstractCamera::project / unproject for n points: xyz [n][3], uv [n][2] (doubles). */
+int vslam_cam_project(vslam_ctx* ctx, const vslam_camera* cam, const double* xyz, int n, double* uv);
+int vslam_cam_unproject(vslam_ctx* ctx, const vslam_camera* cam, const double* uv, int n, double* xyz);
+/* visnav::findInliersEssential (matching_utils.h:63-88): for every match (id1, id2) unproject
+ * kd1.corners[id1] / kd2.corners[id2] and keep the match iff !(|p0^T E p1| > epipolar_error_threshold), in
+ * input order.  E: 3x3 row-major (computeEssential, matching_utils.h:55-61, stays on the host: one 3x3 product).
+ * inliers [cap][2]; *n_inliers may exceed cap (then VSLAM_E_CAPACITY).  err_out (nullable): p0^T E p1 per match. */
+int vslam_find_inliers_essential(vslam_ctx* ctx, const double* xy1, int n1, const double* xy2, int n2,
+                                 const vslam_camera* cam1, const vslam_camera* cam2, const double* E,
+                                 double epipolar_error_threshold, const int32_t* matches, int n_matches,
+                                 int32_t* inliers, int cap, int* n_inliers, double* err_out);
+/* visnav::project_landmarks (vo_utils.h:48-81): p_c = current_pose.inverse() * p for n landmark positions
+ * xyz [n][3]; kept iff !(p_c.z < cam_z_threshold) and the projection lies in [0, width] x [0, height].
+ * pose_w_c = Sophus::SE3d::data() of current_pose: qx qy qz qw tx ty tz.  Outputs in ascending landmark index
+ * (the reference iterates an unordered_map; no caller depends on its order): proj_xy [cap][2], proj_idx [cap]
+ * = index into xyz (the host maps it to the TrackId). */
+int vslam_project_landmarks(vslam_ctx* ctx, const double* pose_w_c, const vslam_camera* cam, const double* xyz,
+                            int n, double cam_z_threshold, double* proj_xy, int32_t* proj_idx, int cap, int* n_out);
+/* Stereo front end with the inlier filter fused behind the matcher (slam.cpp:1141-1143: matchDescriptors, then
+ * findInliersEssential on the same pair): inliers [count][cap][2], n_inliers [count] in addition to the
+ * outputs of vslam_stereo_batch; corners and matches never leave the device in between. */
+typedef struct {
+  vslam_camera cam1, cam2;
+  double E[9]; /* row-major */
+  double epipolar_error_threshold;
+} vslam_epipolar;
+int vslam_stereo_batch_epipolar(vslam_ctx* ctx, const uint8_t* images, int count, const vslam_stereo_params* p,
+                                const vslam_epipolar* ep, double* xy, double* angles, uint32_t* desc,
+                                int32_t* n_kp, int32_t* matches, int32_t* n_matches, int32_t* inliers,
+                                int32_t* n_inliers, int cap);
+/* plan form: ep == NULL switches the stage off again */
+int vslam_stereo_plan_set_epipolar(vslam_stereo_plan* plan, const vslam_epipolar* ep);
+int vslam_stereo_plan_download_inliers(vslam_stereo_plan* plan, int count, int32_t* inliers, int32_t* n_inliers);
+int vslam_stereo_plan_last_epipolar_ms(vslam_stereo_plan* plan, float* ms);
 
 /* ---- measurement helpers --------------------------------------------------------------- */
 /* CUDA events on vslam_stream(ctx): record event `slot` (0..3); elapsed ms between two recorded

@@ -196,6 +196,100 @@ def match_landmarks_ref(kp_xy, kp_desc, proj_xy, obs_offsets, obs_desc, max_dist
                             max_dist_2d, threshold, ratio)
 
 
+# --- geometry after matching: camera models, findInliersEssential, project_landmarks ------
+CAM_MODELS = {"pinhole": 0, "eucm": 1, "ds": 2, "kb4": 3}
+
+
+class Geometry:
+    """kind == "port": oracle/visnav_oracle_geo.c.  kind == "reference": the reference's own camera_models.h,
+    matching_utils.h:63-88 and vo_utils.h:48-81 (oracle/_ref/libvisnav_ref_geo.so)."""
+
+    def __init__(self, lib, kind):
+        self.lib, self.kind = lib, kind
+        pre = "vso_" if kind == "port" else "ref_"
+        self._project = getattr(lib, pre + "cam_project")
+        self._project.restype = None
+        self._project.argtypes = [C.c_int, _f64p, _f64p, C.c_int, _f64p]
+        self._unproject = getattr(lib, pre + "cam_unproject")
+        self._unproject.restype = None
+        self._unproject.argtypes = [C.c_int, _f64p, _f64p, C.c_int, _f64p]
+        self._inl = getattr(lib, pre + "find_inliers_essential")
+        self._inl.restype = C.c_int
+        self._inl.argtypes = [_f64p, C.c_int, _f64p, C.c_int, C.c_int, _f64p, C.c_int, _f64p, _f64p, C.c_double,
+                              _i32p, C.c_int, _i32p, _f64p]
+        self._pl = getattr(lib, pre + "project_landmarks")
+        self._pl.restype = C.c_int
+        self._pl.argtypes = [_f64p, C.c_int, _f64p, C.c_int, C.c_int, _f64p, C.c_int, C.c_double, _f64p, _i32p]
+        if kind == "reference":
+            lib.ref_compute_essential.restype = None
+            lib.ref_compute_essential.argtypes = [_f64p, _f64p]
+
+    @staticmethod
+    def _cam(model, param):
+        model = CAM_MODELS[model] if isinstance(model, str) else int(model)
+        param = np.ascontiguousarray(param, np.float64)
+        assert param.shape == (8,)
+        return model, param
+
+    def project(self, model, param, xyz):
+        model, param = self._cam(model, param)
+        xyz = np.ascontiguousarray(xyz, np.float64).reshape(-1, 3)
+        uv = np.empty((len(xyz), 2), np.float64)
+        self._project(model, _p(param, _f64p), _p(xyz, _f64p), len(xyz), _p(uv, _f64p))
+        return uv
+
+    def unproject(self, model, param, uv):
+        model, param = self._cam(model, param)
+        uv = np.ascontiguousarray(uv, np.float64).reshape(-1, 2)
+        xyz = np.empty((len(uv), 3), np.float64)
+        self._unproject(model, _p(param, _f64p), _p(uv, _f64p), len(uv), _p(xyz, _f64p))
+        return xyz
+
+    def compute_essential(self, pose_0_1):
+        """matching_utils.h:55-61 (reference library only): E = skew(t/|t|) R, row-major 3x3."""
+        pose = np.ascontiguousarray(pose_0_1, np.float64)
+        E = np.empty((3, 3), np.float64)
+        self.lib.ref_compute_essential(_p(pose, _f64p), _p(E, _f64p))
+        return E
+
+    def find_inliers_essential(self, xy1, xy2, cam1, cam2, E, thr, matches):
+        """-> (inliers [m][2] int32, err [n_matches] = p0^T E p1)."""
+        xy1 = np.ascontiguousarray(xy1, np.float64).reshape(-1, 2)
+        xy2 = np.ascontiguousarray(xy2, np.float64).reshape(-1, 2)
+        m1, p1 = self._cam(*cam1)
+        m2, p2 = self._cam(*cam2)
+        E = np.ascontiguousarray(E, np.float64).reshape(3, 3)
+        matches = np.ascontiguousarray(matches, np.int32).reshape(-1, 2)
+        inl = np.empty((max(1, len(matches)), 2), np.int32)
+        err = np.empty(max(1, len(matches)), np.float64)
+        n = self._inl(_p(xy1, _f64p), len(xy1), _p(xy2, _f64p), len(xy2), m1, _p(p1, _f64p), m2, _p(p2, _f64p),
+                      _p(E, _f64p), float(thr), _p(matches, _i32p), len(matches), _p(inl, _i32p), _p(err, _f64p))
+        return inl[:n].copy(), err[:len(matches)].copy()
+
+    def project_landmarks(self, pose_w_c, cam, width, height, xyz, cam_z_threshold):
+        """-> (projected_points [m][2], landmark indices [m]) in ascending landmark index."""
+        pose = np.ascontiguousarray(pose_w_c, np.float64)
+        assert pose.shape == (7,)
+        model, param = self._cam(*cam)
+        xyz = np.ascontiguousarray(xyz, np.float64).reshape(-1, 3)
+        xy = np.empty((max(1, len(xyz)), 2), np.float64)
+        idx = np.empty(max(1, len(xyz)), np.int32)
+        n = self._pl(_p(pose, _f64p), model, _p(param, _f64p), int(width), int(height), _p(xyz, _f64p), len(xyz),
+                     float(cam_z_threshold), _p(xy, _f64p), _p(idx, _i32p))
+        return xy[:n].copy(), idx[:n].copy()
+
+
+def load_geometry():
+    return Geometry(load_oracle().lib, "port")
+
+
+def load_geometry_ref():
+    path = os.path.join(_HERE, "_ref", "libvisnav_ref_geo.so")
+    if not os.path.exists(path):
+        return None
+    return Geometry(C.CDLL(path), "reference")
+
+
 def load_oracle():
     path = os.path.join(_HERE, "liboracle.so")
     if not os.path.exists(path):

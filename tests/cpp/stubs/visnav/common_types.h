@@ -7,6 +7,7 @@ namespace visnav {
 struct Vec2d {
   double v[2];
   double operator[](int i) const { return v[i]; }
+  double& operator[](int i) { return v[i]; }
 };
 struct KeypointsData {
   std::vector<Vec2d> corners;

@@ -84,3 +84,42 @@ def test_landmark_dropin_header():
     assert lines[0] == "matches 20"
     got = [tuple(int(v) for v in ln.split()[1:]) for ln in lines[1:]]
     assert got == [(j, 500 + j) for j in range(0, 40, 2)]
+
+
+EXE_GEO = os.path.join(ROOT, "tests", "cpp", "test_dropin_geometry")
+
+
+def _build_geo():
+    cmd = ["g++", "-std=c++14", "-O2", "-I", os.path.join(ROOT, "tests", "cpp", "stubs"), "-I", os.path.join(ROOT, "include"),
+           "-o", EXE_GEO, os.path.join(ROOT, "tests", "cpp", "test_dropin_geometry.cpp"), "-L",
+           os.path.join(ROOT, "visual-slam_b200", "csrc"), "-lvisnav_b200",
+           "-Wl,-rpath," + os.path.join(ROOT, "visual-slam_b200", "csrc")]
+    subprocess.run(cmd, check=True)
+
+
+def test_geometry_dropin_compiles_and_fails_loudly_without_gpu():
+    import torch
+    _build_geo()
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    p = subprocess.run([EXE_GEO], capture_output=True, text=True)
+    assert p.returncode == 3 and "no usable sm_100 GPU" in p.stdout
+
+
+@pytest.mark.gpu
+def test_geometry_dropin_header():
+    """findInliersEssential_b200 / project_landmarks_b200 on a pinhole rig with a pure x baseline: partners in the
+    same row are inliers, every third (10 rows off) is not; landmarks behind the camera or outside the image
+    are dropped and the rest project to fx*x/z+cx, fy*y/z+cy."""
+    _build_geo()
+    p = subprocess.run([EXE_GEO], capture_output=True, text=True)
+    assert p.returncode == 0, p.stdout[-500:] + p.stderr[-500:]
+    lines = p.stdout.splitlines()
+    assert lines[0] == "inliers 20"
+    assert [tuple(int(v) for v in ln.split()[1:]) for ln in lines if ln.startswith("i ")] == \
+        [(i, i) for i in range(30) if i % 3 != 2]
+    proj = [ln.split() for ln in lines if ln.startswith("p ")]
+    want = [(700 + j, 400 * (-3.0 + 0.5 * j) / (2.0 + j) + 376, 400 * (0.1 * j) / (2.0 + j) + 240) for j in range(2, 12)]
+    want = [w for w in want if 0 <= w[1] <= 752 and 0 <= w[2] <= 480]
+    assert [int(r[0]) for r in proj] == [w[0] for w in want]
+    assert np.abs(np.array([[float(r[1]), float(r[2])] for r in proj]) - np.array([w[1:] for w in want])).max() < 1e-8

@@ -10,6 +10,8 @@ container only (needs cv2 and /root/reference; neither exists on the GPU box):
     matchDescriptors compiled from /root/reference/include/visnav/keypoints.h (oracle/Makefile).
   * oracle/_ref/libvisnav_ref_lm.so: the reference's own find_matches_landmarks
     (/root/reference/include/visnav/vo_utils.h:83-167, with its vendored Eigen).
+  * oracle/_ref/libvisnav_ref_geo.so: the reference's own camera models (camera_models.h),
+    findInliersEssential (matching_utils.h:63-88) and project_landmarks (vo_utils.h:48-81).
 
 The inputs are seeded synthetic images (visual-slam_b200/workloads.py); they are stored too, so the
 fixtures do not depend on numpy's generator staying bit-stable.
@@ -88,9 +90,42 @@ def landmarks():
     print("landmarks", {k: len(v) for k, v in rec.items() if k.startswith("m_")})
 
 
+def geometry():
+    """Camera models, findInliersEssential and project_landmarks by the reference's own code
+    (oracle/_ref/libvisnav_ref_geo.so: camera_models.h, matching_utils.h:50-88, vo_utils.h:48-81)."""
+    import oracle.oracle as oo
+    ref = oo.load_geometry_ref()
+    assert ref is not None, "build oracle/_ref first (make -C oracle)"
+    rng = np.random.default_rng(21)
+    rec = {}
+    for m, P in wl.CAMERAS.items():
+        xyz = rng.normal(size=(160, 3)) * [3, 2, 3] + [0, 0, 5]
+        xyz[0] = [0, 0, 2.0]                                   # on the optical axis (kb4 r == 0 branch)
+        uv = rng.uniform([0, 0], [752, 480], size=(160, 2))
+        uv[0] = P[2:4]                                         # principal point (kb4 ru == 0 branch)
+        xy1, xy2, mt, pose, _ = wl.epipolar_scene(m, 300, seed=3)
+        E = ref.compute_essential(pose)
+        lp, lx = wl.landmark_cloud(600, 5)
+        rec.update({m + "_param": np.array(P, np.float64), m + "_xyz": xyz, m + "_uv": uv,
+                    m + "_project": ref.project(m, P, xyz), m + "_unproject": ref.unproject(m, P, uv),
+                    m + "_xy1": xy1, m + "_xy2": xy2, m + "_matches": mt, m + "_pose01": pose, m + "_E": E,
+                    m + "_lm_pose": lp, m + "_lm_xyz": lx})
+        for thr in (5e-3, 1e-3):
+            inl, err = ref.find_inliers_essential(xy1, xy2, (m, P), (m, P), E, thr, mt)
+            rec[m + "_inliers_%g" % thr] = inl
+            rec[m + "_err"] = err
+        pxy, pidx = ref.project_landmarks(lp, (m, P), 752, 480, lx, 0.1)
+        rec[m + "_proj_xy"], rec[m + "_proj_idx"] = pxy, pidx
+        print("geometry", m, {k: len(v) for k, v in rec.items() if k.startswith(m + "_inliers")}, len(pidx))
+    np.savez_compressed(os.path.join(OUT, "geometry.npz"), **rec)
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "landmarks":
         landmarks()
+    elif len(sys.argv) > 1 and sys.argv[1] == "geometry":
+        geometry()
     else:
         main()
         landmarks()
+        geometry()

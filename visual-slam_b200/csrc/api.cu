@@ -113,7 +113,7 @@ void vslam_destroy(vslam_ctx* ctx) {
   }
   DevBuf* bufs[] = {&ctx->img, &ctx->xy, &ctx->ang, &ctx->desc, &ctx->cnt, &ctx->lam, &ctx->cand, &ctx->candcnt,
                     &ctx->imgmax, &ctx->selws, &ctx->d1, &ctx->d2, &ctx->pairs, &ctx->mcnt, &ctx->rowpart,
-                    &ctx->colstat, &ctx->jobs, &ctx->lm, &ctx->pyr};
+                    &ctx->colstat, &ctx->jobs, &ctx->lm, &ctx->pyr, &ctx->geo};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 8; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -444,10 +444,12 @@ struct vslam_stereo_plan {
   DevImages im{};
   DevBuf images, xy, ang, desc, nkp, matches, nmatch, jobs;
   DevBuf cand, candcnt, imgmax, selws;
+  DevBuf inliers, ninl, epiws;  // optional fused findInliersEssential stage (vslam_stereo_plan_set_epipolar)
+  bool epi_on = false;
+  vslam_epipolar epi{};
   DetectWorkspace ws{};
-  cudaEvent_t ev[5] = {};
+  cudaEvent_t ev[6] = {};
   cudaStream_t stream = nullptr;  // null: ctx stream
-  float ms[5] = {};
   bool timed = false;
 };
 
@@ -458,9 +460,10 @@ void vslam_stereo_plan_destroy(vslam_stereo_plan* plan) {
   cudaSetDevice(plan->ctx->device);
   cudaDeviceSynchronize();
   DevBuf* bufs[] = {&plan->images, &plan->xy, &plan->ang, &plan->desc, &plan->nkp, &plan->matches, &plan->nmatch,
-                    &plan->jobs, &plan->cand, &plan->candcnt, &plan->imgmax, &plan->selws};
+                    &plan->jobs, &plan->cand, &plan->candcnt, &plan->imgmax, &plan->selws, &plan->inliers,
+                    &plan->ninl, &plan->epiws};
   for (DevBuf* b : bufs) b->release();
-  for (int i = 0; i < 5; ++i)
+  for (int i = 0; i < 6; ++i)
     if (plan->ev[i]) cudaEventDestroy(plan->ev[i]);
   if (plan->stream) cudaStreamDestroy(plan->stream);
   delete plan;
@@ -500,7 +503,7 @@ static int plan_create_impl(vslam_ctx* ctx, int w, int h, int max_pairs, int cap
   PLAN_CUDA(p->jobs.reserve((size_t)max_pairs * sizeof(MatchJob)));
   rc = prepare_detect_ws(ctx, w, h, nimg, p->cand, p->candcnt, p->imgmax, p->selws, &p->ws);
   if (rc) return fail(rc);
-  for (int i = 0; i < 5; ++i) PLAN_CUDA(cudaEventCreate(&p->ev[i]));
+  for (int i = 0; i < 6; ++i) PLAN_CUDA(cudaEventCreate(&p->ev[i]));
   if (own_stream) PLAN_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
   // the stereo jobs only depend on the plan's buffers: build them once
   std::vector<MatchJob> jobs(max_pairs);
@@ -569,6 +572,16 @@ int vslam_stereo_plan_run(vslam_stereo_plan* plan, int count, int num_features, 
     rc = launch_match_jobs(ctx, plan->jobs.as<MatchJob>(), count, plan->cap, plan->cap, match_threshold,
                            match_dist_2_best, plan->cap);
   cudaEventRecord(plan->ev[4], ctx->stream);
+  if (!rc && plan->epi_on) {
+    // matching_utils.h:63-88 on the matcher's device output: left corners of pair k are image 2k, right 2k+1
+    rc = launch_essential_jobs(ctx, &plan->epi.cam1, &plan->epi.cam2, plan->epi.E, plan->epi.epipolar_error_threshold,
+                               plan->xy.as<double>(), plan->xy.as<double>() + (size_t)plan->cap * 2,
+                               (size_t)plan->cap * 4, plan->matches.as<int32_t>(), (size_t)plan->cap,
+                               plan->nmatch.as<int32_t>(), plan->cap, count, plan->epiws.as<uint8_t>(),
+                               plan->inliers.as<int32_t>(), (size_t)plan->cap, plan->cap, plan->ninl.as<int32_t>(),
+                               nullptr);
+  }
+  cudaEventRecord(plan->ev[5], ctx->stream);
   plan->timed = true;
   ctx->stream = saved;
   return rc;
@@ -596,16 +609,59 @@ int vslam_stereo_plan_last_ms(vslam_stereo_plan* plan, float* ms) {
   if (!plan || !ms) return VSLAM_E_ARG;
   vslam_ctx* ctx = plan->ctx;
   if (!plan->timed) return vs_fail(ctx, VSLAM_E_ARG, "plan has not run");
-  VS_CUDA(ctx, cudaEventSynchronize(plan->ev[4]));
-  VS_CUDA(ctx, cudaEventElapsedTime(&ms[0], plan->ev[0], plan->ev[4]));
+  VS_CUDA(ctx, cudaEventSynchronize(plan->ev[5]));
+  VS_CUDA(ctx, cudaEventElapsedTime(&ms[0], plan->ev[0], plan->ev[5]));
   for (int i = 0; i < 4; ++i) VS_CUDA(ctx, cudaEventElapsedTime(&ms[1 + i], plan->ev[i], plan->ev[i + 1]));
+  return VSLAM_OK;
+}
+
+int vslam_stereo_plan_set_epipolar(vslam_stereo_plan* plan, const vslam_epipolar* ep) {
+  if (!plan) return VSLAM_E_ARG;
+  vslam_ctx* ctx = plan->ctx;
+  if (!ep) {
+    plan->epi_on = false;
+    return VSLAM_OK;
+  }
+  for (const vslam_camera* c : {&ep->cam1, &ep->cam2})
+    if (c->model < VSLAM_CAM_PINHOLE || c->model > VSLAM_CAM_KB4) return vs_fail(ctx, VSLAM_E_ARG, "bad camera model");
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  VS_CUDA(ctx, plan->inliers.reserve((size_t)plan->max_pairs * plan->cap * 8));
+  VS_CUDA(ctx, plan->ninl.reserve((size_t)plan->max_pairs * 4));
+  VS_CUDA(ctx, plan->epiws.reserve(essential_ws_bytes(plan->cap, plan->max_pairs)));  // sized for max_pairs jobs: run(count <= max_pairs) uses a prefix
+  plan->epi = *ep;
+  plan->epi_on = true;
+  return VSLAM_OK;
+}
+
+int vslam_stereo_plan_download_inliers(vslam_stereo_plan* plan, int count, int32_t* inliers, int32_t* n_inliers) {
+  if (!plan) return VSLAM_E_ARG;
+  vslam_ctx* ctx = plan->ctx;
+  if (count < 0 || count > plan->max_pairs) return vs_fail(ctx, VSLAM_E_ARG, "bad pair count");
+  if (!plan->epi_on) return vs_fail(ctx, VSLAM_E_ARG, "the plan has no epipolar stage (vslam_stereo_plan_set_epipolar)");
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t s = plan_stream(plan);
+  if (inliers) VS_CUDA(ctx, cudaMemcpyAsync(inliers, plan->inliers.p, (size_t)count * plan->cap * 8, cudaMemcpyDeviceToHost, s));
+  if (n_inliers) VS_CUDA(ctx, cudaMemcpyAsync(n_inliers, plan->ninl.p, (size_t)count * 4, cudaMemcpyDeviceToHost, s));
+  VS_CUDA(ctx, cudaStreamSynchronize(s));
+  return VSLAM_OK;
+}
+
+int vslam_stereo_plan_last_epipolar_ms(vslam_stereo_plan* plan, float* ms) {
+  if (!plan || !ms) return VSLAM_E_ARG;
+  vslam_ctx* ctx = plan->ctx;
+  if (!plan->timed) return vs_fail(ctx, VSLAM_E_ARG, "plan has not run");
+  VS_CUDA(ctx, cudaEventSynchronize(plan->ev[5]));
+  VS_CUDA(ctx, cudaEventElapsedTime(ms, plan->ev[4], plan->ev[5]));
   return VSLAM_OK;
 }
 
 // ---- batched front ends on host buffers -------------------------------------------------------------
 
-int vslam_stereo_batch(vslam_ctx* ctx, const uint8_t* images, int count, const vslam_stereo_params* sp, double* xy,
-                       double* angles, uint32_t* desc, int32_t* n_kp, int32_t* matches, int32_t* n_matches, int cap) {
+}  // extern "C"
+
+static int stereo_batch_impl(vslam_ctx* ctx, const uint8_t* images, int count, const vslam_stereo_params* sp,
+                             const vslam_epipolar* ep, double* xy, double* angles, uint32_t* desc, int32_t* n_kp,
+                             int32_t* matches, int32_t* n_matches, int32_t* inliers, int32_t* n_inliers, int cap) {
   if (!ctx) return VSLAM_E_ARG;
   if (!images || !sp || count < 0 || cap <= 0) return vs_fail(ctx, VSLAM_E_ARG, "bad batch arguments");
   if (sp->w < 2 || sp->h < 2 || sp->pitch < sp->w || sp->num_features <= 0 || sp->num_features > cap)
@@ -646,6 +702,7 @@ int vslam_stereo_batch(vslam_ctx* ctx, const uint8_t* images, int count, const v
       cp = nullptr;
     }
     if (!cp) rc = plan_create_impl(ctx, sp->w, sp->h, chunk, cap, true, &cp);
+    if (!rc) rc = vslam_stereo_plan_set_epipolar(cp, ep);
     plans[i] = cp;
   }
   int bad_kp = 0;
@@ -664,6 +721,8 @@ int vslam_stereo_batch(vslam_ctx* ctx, const uint8_t* images, int count, const v
     if (n_kp) VS_CUDA(ctx, cudaMemcpyAsync(n_kp + i0, p->nkp.p, ni * 4, cudaMemcpyDeviceToHost, s));
     if (matches) VS_CUDA(ctx, cudaMemcpyAsync(matches + (size_t)c0 * cp * 2, p->matches.p, (size_t)nc * cp * 8, cudaMemcpyDeviceToHost, s));
     if (n_matches) VS_CUDA(ctx, cudaMemcpyAsync(n_matches + c0, p->nmatch.p, (size_t)nc * 4, cudaMemcpyDeviceToHost, s));
+    if (ep && inliers) VS_CUDA(ctx, cudaMemcpyAsync(inliers + (size_t)c0 * cp * 2, p->inliers.p, (size_t)nc * cp * 8, cudaMemcpyDeviceToHost, s));
+    if (ep && n_inliers) VS_CUDA(ctx, cudaMemcpyAsync(n_inliers + c0, p->ninl.p, (size_t)nc * 4, cudaMemcpyDeviceToHost, s));
   }
   for (int i = 0; i < nplans; ++i)
     if (plans[i]) cudaStreamSynchronize(plans[i]->stream);
@@ -672,6 +731,22 @@ int vslam_stereo_batch(vslam_ctx* ctx, const uint8_t* images, int count, const v
       if (n_kp[i] < 0) bad_kp = n_kp[i];
   if (!rc && bad_kp) rc = kp_status(ctx, bad_kp);
   return rc;
+}
+
+extern "C" {
+
+int vslam_stereo_batch(vslam_ctx* ctx, const uint8_t* images, int count, const vslam_stereo_params* sp, double* xy,
+                       double* angles, uint32_t* desc, int32_t* n_kp, int32_t* matches, int32_t* n_matches, int cap) {
+  return stereo_batch_impl(ctx, images, count, sp, nullptr, xy, angles, desc, n_kp, matches, n_matches, nullptr,
+                           nullptr, cap);
+}
+
+int vslam_stereo_batch_epipolar(vslam_ctx* ctx, const uint8_t* images, int count, const vslam_stereo_params* sp,
+                                const vslam_epipolar* ep, double* xy, double* angles, uint32_t* desc, int32_t* n_kp,
+                                int32_t* matches, int32_t* n_matches, int32_t* inliers, int32_t* n_inliers, int cap) {
+  if (ctx && !ep) return vs_fail(ctx, VSLAM_E_ARG, "epipolar parameters missing");
+  return stereo_batch_impl(ctx, images, count, sp, ep, xy, angles, desc, n_kp, matches, n_matches, inliers, n_inliers,
+                           cap);
 }
 
 int vslam_detect_describe_batch(vslam_ctx* ctx, const uint8_t* images, int count, int w, int h, int pitch,

@@ -49,6 +49,7 @@ struct vslam_ctx {
   DevBuf cand, candcnt, imgmax, selws;
   DevBuf d1, d2, pairs, mcnt, rowpart, colstat, jobs;
   DevBuf lm;  // vslam_match_landmarks staging
+  DevBuf geo;  // geometry.cu staging (camera models, essential inliers, landmark projection)
   DevBuf pyr;  // vslam_pyramid_detect_describe_batch: levels 1.. of the chunk in flight
   void* pinned = nullptr;  // small pinned staging block for counts
   // pipeline plans of vslam_stereo_batch, kept between calls (same geometry -> no reallocation)
@@ -132,3 +133,12 @@ int launch_match_landmarks(vslam_ctx* ctx, const double* kp_xy, const uint32_t* 
                            const double* proj_xy, int n_proj, const int32_t* obs_off, const uint32_t* obs_desc,
                            double max_dist_2d, int threshold, double ratio, int32_t* result, int32_t* pairs,
                            int32_t* count, int cap);
+// geometry.cu: findInliersEssential for n_jobs independent match lists that are already on the device
+// (xy1/xy2: corner slabs, job k at + k*xy_job_stride doubles; matches: job k at + k*match_job_stride pairs;
+// n_matches_dev: per-job counts on the device, or nullptr -> n_matches_max for every job).
+size_t essential_ws_bytes(int n_matches_max, int n_jobs);  // keep flags + block counts
+int launch_essential_jobs(vslam_ctx* ctx, const vslam_camera* cam1, const vslam_camera* cam2, const double* E,
+                          double thr, const double* xy1, const double* xy2, size_t xy_job_stride,
+                          const int32_t* matches, size_t match_job_stride, const int32_t* n_matches_dev,
+                          int n_matches_max, int n_jobs, uint8_t* ws /*essential_ws_bytes()*/, int32_t* inliers,
+                          size_t inlier_job_stride, int cap, int32_t* n_inliers, double* err_out);

@@ -35,6 +35,9 @@ ABI_SYMBOLS = [
     "vslam_stereo_plan_download", "vslam_stereo_plan_last_ms", "vslam_desc_store_create",
     "vslam_desc_store_destroy", "vslam_match_batch", "vslam_last_match_ms", "vslam_popc_peak",
     "vslam_event_record", "vslam_event_elapsed_ms",
+    "vslam_cam_project", "vslam_cam_unproject", "vslam_find_inliers_essential", "vslam_project_landmarks",
+    "vslam_stereo_batch_epipolar", "vslam_stereo_plan_set_epipolar", "vslam_stereo_plan_download_inliers",
+    "vslam_stereo_plan_last_epipolar_ms",
 ]
 
 VSLAM_OPT_FP_CONTRACT = 1
@@ -51,6 +54,34 @@ class StereoParams(C.Structure):
     _fields_ = [("w", C.c_int), ("h", C.c_int), ("pitch", C.c_int), ("image_stride", C.c_size_t),
                 ("num_features", C.c_int), ("rotate_features", C.c_int), ("match_threshold", C.c_int),
                 ("match_dist_2_best", C.c_double)]
+
+
+CAM_MODELS = {"pinhole": 0, "eucm": 1, "ds": 2, "kb4": 3}  # camera_models.h getName() -> VSLAM_CAM_*
+
+
+class Camera(C.Structure):
+    """vslam_camera: one of the reference's camera models (camera_models.h) with its 8-double parameter vector."""
+    _fields_ = [("model", C.c_int), ("width", C.c_int), ("height", C.c_int), ("reserved", C.c_int),
+                ("param", C.c_double * 8)]
+
+    @classmethod
+    def from_data(cls, name, param, width=0, height=0):
+        """AbstractCamera::from_data (camera_models.h:475-498) + width()/height()."""
+        if name not in CAM_MODELS:
+            raise VslamError("Camera model %s is not implemented." % name)
+        param = [float(v) for v in param]
+        if len(param) != 8:
+            raise VslamError("camera parameter vector must have 8 entries")
+        return cls(CAM_MODELS[name], int(width), int(height), 0, (C.c_double * 8)(*param))
+
+
+class Epipolar(C.Structure):
+    _fields_ = [("cam1", Camera), ("cam2", Camera), ("E", C.c_double * 9), ("epipolar_error_threshold", C.c_double)]
+
+    @classmethod
+    def make(cls, cam1, cam2, E, thr):
+        E = np.ascontiguousarray(E, np.float64).reshape(9)
+        return cls(cam1, cam2, (C.c_double * 9)(*E.tolist()), float(thr))
 
 
 def lib_path():
@@ -112,6 +143,16 @@ def load_library():
     L.vslam_popc_peak.argtypes = [vp, C.POINTER(d)]
     L.vslam_event_record.argtypes = [vp, i]
     L.vslam_event_elapsed_ms.argtypes = [vp, i, i, C.POINTER(C.c_float)]
+    cam = C.POINTER(Camera)
+    L.vslam_cam_project.argtypes = [vp, cam, vp, i, vp]
+    L.vslam_cam_unproject.argtypes = [vp, cam, vp, i, vp]
+    L.vslam_find_inliers_essential.argtypes = [vp, vp, i, vp, i, cam, cam, vp, d, vp, i, vp, i, C.POINTER(i), vp]
+    L.vslam_project_landmarks.argtypes = [vp, vp, cam, vp, i, d, vp, vp, i, C.POINTER(i)]
+    L.vslam_stereo_batch_epipolar.argtypes = [vp, vp, i, C.POINTER(StereoParams), C.POINTER(Epipolar), vp, vp, vp, vp,
+                                              vp, vp, vp, vp, i]
+    L.vslam_stereo_plan_set_epipolar.argtypes = [vp, C.POINTER(Epipolar)]
+    L.vslam_stereo_plan_download_inliers.argtypes = [vp, i, vp, vp]
+    L.vslam_stereo_plan_last_epipolar_ms.argtypes = [vp, C.POINTER(C.c_float)]
     _lib = L
     return L
 
@@ -272,6 +313,50 @@ class Context:
                                                    C.c_double(dist_2_best), _ptr(pairs), cap, C.byref(n)))
         return pairs[:n.value].copy()
 
+    # --- geometry after matching (camera_models.h, matching_utils.h:63-88, vo_utils.h:48-81) ---
+    def cam_project(self, cam, xyz):
+        xyz = np.ascontiguousarray(xyz, np.float64).reshape(-1, 3)
+        uv = np.empty((len(xyz), 2), np.float64)
+        self._check(self.lib.vslam_cam_project(self.h, C.byref(cam), _ptr(xyz), len(xyz), _ptr(uv)))
+        return uv
+
+    def cam_unproject(self, cam, uv):
+        uv = np.ascontiguousarray(uv, np.float64).reshape(-1, 2)
+        xyz = np.empty((len(uv), 3), np.float64)
+        self._check(self.lib.vslam_cam_unproject(self.h, C.byref(cam), _ptr(uv), len(uv), _ptr(xyz)))
+        return xyz
+
+    def find_inliers_essential(self, xy1, xy2, cam1, cam2, E, thr, matches, want_err=False, cap=None):
+        """findInliersEssential: -> inliers [m][2] (and p0^T E p1 per match when want_err)."""
+        xy1 = np.ascontiguousarray(xy1, np.float64).reshape(-1, 2)
+        xy2 = np.ascontiguousarray(xy2, np.float64).reshape(-1, 2)
+        matches = np.ascontiguousarray(matches, np.int32).reshape(-1, 2)
+        E = np.ascontiguousarray(E, np.float64).reshape(9)
+        cap = len(matches) if cap is None else cap
+        inl = np.empty((max(cap, 1), 2), np.int32)
+        err = np.empty(max(len(matches), 1), np.float64) if want_err else None
+        n = C.c_int(0)
+        self._check(self.lib.vslam_find_inliers_essential(self.h, _ptr(xy1), len(xy1), _ptr(xy2), len(xy2),
+                                                          C.byref(cam1), C.byref(cam2), _ptr(E), float(thr),
+                                                          _ptr(matches), len(matches), _ptr(inl), cap, C.byref(n),
+                                                          _ptr(err)))
+        inl = inl[:n.value].copy()
+        return (inl, err[:len(matches)]) if want_err else inl
+
+    def project_landmarks(self, pose_w_c, cam, xyz, cam_z_threshold, cap=None):
+        """project_landmarks: -> (projected_points [m][2], landmark indices [m])."""
+        pose = np.ascontiguousarray(pose_w_c, np.float64)
+        if pose.shape != (7,):
+            raise VslamError("pose must be Sophus::SE3d::data(): qx qy qz qw tx ty tz")
+        xyz = np.ascontiguousarray(xyz, np.float64).reshape(-1, 3)
+        cap = len(xyz) if cap is None else cap
+        xy = np.empty((max(cap, 1), 2), np.float64)
+        idx = np.empty(max(cap, 1), np.int32)
+        n = C.c_int(0)
+        self._check(self.lib.vslam_project_landmarks(self.h, _ptr(pose), C.byref(cam), _ptr(xyz), len(xyz),
+                                                     float(cam_z_threshold), _ptr(xy), _ptr(idx), cap, C.byref(n)))
+        return xy[:n.value].copy(), idx[:n.value].copy()
+
     def best2(self, q, db):
         q = np.ascontiguousarray(q, np.uint32).reshape(-1, 8)
         db = np.ascontiguousarray(db, np.uint32).reshape(-1, 8)
@@ -318,9 +403,10 @@ class Context:
         return xy, ang, desc, nkp, off
 
     def stereo_batch(self, images, num_features=1500, rotate=True, threshold=70, dist_2_best=1.2, cap=None,
-                     out=None):
+                     out=None, epipolar=None):
         """images: [count, 2, h, w] uint8 (C-contiguous; pinned memory makes the copies asynchronous).
-        Returns dict(xy, angles, desc, n_kp, matches, n_matches) of fixed-stride slabs."""
+        Returns dict(xy, angles, desc, n_kp, matches, n_matches) of fixed-stride slabs; with `epipolar`
+        (an Epipolar) also inliers / n_inliers (findInliersEssential fused behind the matcher)."""
         images = np.asarray(images)
         if images.dtype != np.uint8 or images.ndim != 4 or images.shape[1] != 2 or not images.flags.c_contiguous:
             raise VslamError("images must be a C-contiguous [count, 2, h, w] uint8 array")
@@ -331,6 +417,14 @@ class Context:
                        desc=np.empty((count * 2, cap, 8), np.uint32), n_kp=np.empty(count * 2, np.int32),
                        matches=np.empty((count, cap, 2), np.int32), n_matches=np.empty(count, np.int32))
         p = StereoParams(w, h, w, w * h, int(num_features), int(bool(rotate)), int(threshold), float(dist_2_best))
+        if epipolar is not None:
+            out.setdefault("inliers", np.empty((count, cap, 2), np.int32))
+            out.setdefault("n_inliers", np.empty(count, np.int32))
+            self._check(self.lib.vslam_stereo_batch_epipolar(
+                self.h, _ptr(images), count, C.byref(p), C.byref(epipolar), _ptr(out.get("xy")), _ptr(out.get("angles")),
+                _ptr(out.get("desc")), _ptr(out.get("n_kp")), _ptr(out.get("matches")), _ptr(out.get("n_matches")),
+                _ptr(out["inliers"]), _ptr(out["n_inliers"]), cap))
+            return out
         self._check(self.lib.vslam_stereo_batch(self.h, _ptr(images), count, C.byref(p), _ptr(out.get("xy")),
                                                 _ptr(out.get("angles")), _ptr(out.get("desc")), _ptr(out.get("n_kp")),
                                                 _ptr(out.get("matches")), _ptr(out.get("n_matches")), cap))
@@ -406,6 +500,21 @@ class StereoPlan:
                                                                 _ptr(out["n_matches"])))
         return out
 
+    def set_epipolar(self, epipolar):
+        """Fuse findInliersEssential behind the matcher (None switches it off)."""
+        self.ctx._check(self.ctx.lib.vslam_stereo_plan_set_epipolar(self.p, C.byref(epipolar) if epipolar is not None else None))
+
+    def download_inliers(self, count):
+        inl = np.empty((count, self.cap, 2), np.int32)
+        n = np.empty(count, np.int32)
+        self.ctx._check(self.ctx.lib.vslam_stereo_plan_download_inliers(self.p, count, _ptr(inl), _ptr(n)))
+        return inl, n
+
+    def last_epipolar_ms(self):
+        ms = C.c_float(0)
+        self.ctx._check(self.ctx.lib.vslam_stereo_plan_last_epipolar_ms(self.p, C.byref(ms)))
+        return ms.value
+
     def last_ms(self):
         ms = (C.c_float * 5)()
         self.ctx._check(self.ctx.lib.vslam_stereo_plan_last_ms(self.p, ms))
@@ -463,3 +572,24 @@ def matchDescriptors(corner_descriptors_1, corner_descriptors_2, matches, thresh
     del matches[:]
     pairs = default_context().match(corner_descriptors_1, corner_descriptors_2, threshold, dist_2_best)
     matches.extend((int(a), int(b)) for a, b in pairs)
+
+
+def findInliersEssential(kd1, kd2, cam1, cam2, E, epipolar_error_threshold, md):
+    """matching_utils.h:63-88: md.inliers.clear(), then the matches whose |p0^T E p1| is not above the threshold.
+    kd1/kd2: KeypointsData; cam1/cam2: Camera; md: object with .matches / .inliers lists of (id1, id2)."""
+    del md.inliers[:]
+    inl = default_context().find_inliers_essential(kd1.corners, kd2.corners, cam1, cam2, E, epipolar_error_threshold,
+                                                   np.asarray(md.matches, np.int32).reshape(-1, 2))
+    md.inliers.extend((int(a), int(b)) for a, b in inl)
+
+
+def project_landmarks(current_pose, cam, landmarks, cam_z_threshold, projected_points, projected_track_ids):
+    """vo_utils.h:48-81.  current_pose: 7 doubles (Sophus::SE3d::data()); landmarks: dict TrackId -> 3-vector
+    (Landmark::p).  Clears and fills projected_points / projected_track_ids (in the dict's iteration order)."""
+    del projected_points[:]
+    del projected_track_ids[:]
+    ids = list(landmarks.keys())
+    xyz = np.array([landmarks[k] for k in ids], np.float64).reshape(-1, 3)
+    xy, idx = default_context().project_landmarks(current_pose, cam, xyz, cam_z_threshold)
+    projected_points.extend(xy[k].copy() for k in range(len(xy)))
+    projected_track_ids.extend(ids[k] for k in idx)
