@@ -118,7 +118,7 @@ def test_geometry_dropin_header():
     assert lines[0] == "inliers 20"
     assert [tuple(int(v) for v in ln.split()[1:]) for ln in lines if ln.startswith("i ")] == \
         [(i, i) for i in range(30) if i % 3 != 2]
-    proj = [ln.split() for ln in lines if ln.startswith("p ")]
+    proj = [ln.split()[1:] for ln in lines if ln.startswith("p ")]
     want = [(700 + j, 400 * (-3.0 + 0.5 * j) / (2.0 + j) + 376, 400 * (0.1 * j) / (2.0 + j) + 240) for j in range(2, 12)]
     want = [w for w in want if 0 <= w[1] <= 752 and 0 <= w[2] <= 480]
     assert [int(r[0]) for r in proj] == [w[0] for w in want]

@@ -110,5 +110,29 @@ for rep in range(20):
 out["landmarks"] = dict(n_kp=1313, n_landmarks=2000, call_ms=1e3 * float(np.median(t)), kernel_ms=ctx.last_match_ms(),
                         matches=len(m))
 print("landmarks", out["landmarks"], flush=True)
+
+# geometry after matching: single calls with host buffers, and the inlier filter fused into the plan
+from visnav_b200.keypoints import Camera, Epipolar
+P = wl.CAMERAS["ds"]
+cam = Camera.from_data("ds", P, 752, 480)
+xy1, xy2, mt, pose01, E = wl.epipolar_scene("ds", 1300, seed=2)
+t = []
+for rep in range(20):
+    t0 = time.perf_counter(); inl = ctx.find_inliers_essential(xy1, xy2, cam, cam, E, 5e-3, mt); t.append(time.perf_counter() - t0)
+out["inliers_essential"] = dict(matches=len(mt), inliers=len(inl), call_ms=1e3 * float(np.median(t)))
+pose_w, pts = wl.landmark_cloud(20000, 1)
+pts = np.tile(pts, (5, 1))
+t = []
+for rep in range(20):
+    t0 = time.perf_counter(); pxy, pidx = ctx.project_landmarks(pose_w, cam, pts, 0.1); t.append(time.perf_counter() - t0)
+out["project_landmarks"] = dict(landmarks=len(pts), projected=len(pidx), call_ms=1e3 * float(np.median(t)))
+plan.set_epipolar(Epipolar.make(cam, cam, wl.stereo_geometry(0)[1], 0.02))
+for rep in range(3):
+    plan.run(npairs)
+inl, ninl = plan.download_inliers(npairs)
+out["stereo_fused_epipolar"] = dict(pairs=npairs, epipolar_ms=plan.last_epipolar_ms(), total_ms=plan.last_ms()[0],
+                                    mean_inliers=float(ninl.mean()))
+plan.set_epipolar(None)
+print("geometry", out["inliers_essential"], out["project_landmarks"], out["stereo_fused_epipolar"], flush=True)
 os.makedirs("gpurun_out", exist_ok=True)
 json.dump(out, open("gpurun_out/probe.json", "w"), indent=1)
