@@ -44,3 +44,25 @@ def test_match_ties_vs_reference(ctx):
     for key in [k for k in g.files if k.startswith("m_")]:
         _, thr, ratio = key.split("_")
         assert np.array_equal(ctx.match(g["d1"], g["d2"], int(thr), float(ratio.replace("p", "."))), g[key]), key
+
+
+def test_real_euroc_pair_vs_opencv_and_reference(ctx):
+    """A real EuRoC stereo pair (bundled with the reference, data/euroc_V1): corners == cv2.goodFeaturesToTrack
+    (+ the reference's 19-px filter), angles <= 1e-5 rad, descriptors and stereo matches bit-exact vs the
+    reference's own functions -- slam.cpp:1125-1143 end to end, single calls and the batched call."""
+    g = _load("euroc_pair")
+    descs = {}
+    for side in ("l", "r"):
+        img = g["img_" + side]
+        c = g["corners_unopt_" + side]
+        keep = (c[:, 0] >= 19) & (c[:, 0] < 752 - 19) & (c[:, 1] >= 19) & (c[:, 1] < 480 - 19)
+        xy, ang, desc = ctx.detect_describe(img, 1500, True)
+        assert np.array_equal(xy, c[keep].astype(np.float64)) and np.array_equal(xy, g["xy_" + side])
+        assert np.abs(ang - g["ang_" + side]).max() <= 1e-5
+        assert np.array_equal(desc, g["desc_" + side])
+        descs[side] = desc
+    assert np.array_equal(ctx.match(descs["l"], descs["r"], 70, 1.2), g["matches"])
+    out = ctx.stereo_batch(np.ascontiguousarray(np.stack([g["img_l"], g["img_r"]])[None]), 1500, True, 70, 1.2)
+    m = int(out["n_matches"][0])
+    assert np.array_equal(out["matches"][0, :m], g["matches"])
+    assert np.array_equal(out["desc"][0, :out["n_kp"][0]], g["desc_l"])

@@ -127,3 +127,22 @@ def test_landmark_matching_edge_cases():
     assert len(oo.match_landmarks_port(sc[0], sc[1], sc[2], off0, e8, 20.0, 256, 1.0)) == 0
     # radius 0: nothing is inside the gate
     assert len(oo.match_landmarks_port(*sc, 0.0, 70, 1.2)) == 0
+
+
+def test_real_euroc_pair(oracle_port, oracle_ref):
+    """Restated gftt == cv2 on a REAL image pair (scalar and default AVX2 dispatch agree there), and the
+    restated angles / descriptors / matcher == the reference's own functions' committed outputs."""
+    g = np.load(os.path.join(GOLD, "euroc_pair.npz"))
+    descs = {}
+    for side in ("l", "r"):
+        img = g["img_" + side]
+        assert np.array_equal(oracle_port.gftt(img, 1500), g["corners_unopt_" + side])
+        assert np.array_equal(g["corners_unopt_" + side], g["corners_default_" + side])
+        xy, ang, desc = oracle_port.detect_describe(img, 1500)
+        assert np.array_equal(xy, g["xy_" + side])
+        assert np.abs(ang - g["ang_" + side]).max() <= 1e-12
+        assert np.array_equal(desc, g["desc_" + side])
+        descs[side] = desc
+    assert np.array_equal(oracle_port.match(descs["l"], descs["r"], 70, 1.2), g["matches"])
+    if oracle_ref is not None:
+        assert np.array_equal(oracle_ref.match(descs["l"], descs["r"], 70, 1.2), g["matches"])

@@ -120,12 +120,45 @@ def geometry():
     np.savez_compressed(os.path.join(OUT, "geometry.npz"), **rec)
 
 
+def euroc():
+    """One REAL EuRoC stereo pair bundled with the reference (data/euroc_V1, 752x480): decoded here with cv2
+    (the decoded bytes are stored, so the fixture does not depend on a JPEG decoder), corners by cv2's
+    goodFeaturesToTrack (scalar and default dispatch), angles / descriptors / stereo matches by the reference's
+    own functions -- the call sequence of slam.cpp:1125-1143 with num_features = 1500."""
+    ref = oracle.load_ref()
+    assert ref is not None
+    d = "/root/reference/data/euroc_V1"
+    stem = "1403715273262142976"
+    rec = {}
+    kd = {}
+    for side, cam in (("l", 0), ("r", 1)):
+        img = cv2.imread(os.path.join(d, "%s_%d.jpg" % (stem, cam)), cv2.IMREAD_GRAYSCALE)
+        assert img is not None and img.shape == (480, 752)
+        c0, c1 = gftt_cv2(img, 1500, False), gftt_cv2(img, 1500, True)
+        xy = ref.detect(img, 1500)
+        keep = (c0[:, 0] >= 19) & (c0[:, 0] < 752 - 19) & (c0[:, 1] >= 19) & (c0[:, 1] < 480 - 19)
+        assert np.array_equal(xy, c0[keep].astype(np.float64)), "restated gftt differs from cv2 on a real image"
+        ang = ref.angles(img, xy, True)
+        desc = ref.describe(img, xy, ang)
+        kd[side] = desc
+        rec.update({"img_" + side: img, "corners_unopt_" + side: c0, "corners_default_" + side: c1, "xy_" + side: xy,
+                    "ang_" + side: ang, "desc_" + side: desc})
+    rec["matches"] = ref.match(kd["l"], kd["r"], 70, 1.2)
+    np.savez_compressed(os.path.join(OUT, "euroc_pair.npz"), **rec)
+    print("euroc", len(rec["xy_l"]), len(rec["xy_r"]), len(rec["matches"]), "default dispatch identical:",
+          np.array_equal(rec["corners_unopt_l"], rec["corners_default_l"]),
+          np.array_equal(rec["corners_unopt_r"], rec["corners_default_r"]))
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "landmarks":
         landmarks()
     elif len(sys.argv) > 1 and sys.argv[1] == "geometry":
         geometry()
+    elif len(sys.argv) > 1 and sys.argv[1] == "euroc":
+        euroc()
     else:
         main()
         landmarks()
         geometry()
+        euroc()
