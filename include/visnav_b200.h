@@ -106,6 +106,17 @@ int vslam_match_landmarks(vslam_ctx* ctx, const double* kp_xy, const uint32_t* k
                           const double* proj_xy, int n_proj, const int32_t* obs_offsets,
                           const uint32_t* obs_desc, double match_max_dist_2d, int threshold,
                           double dist_2_best, int32_t* pairs, int cap, int* n);
+/* matchDescriptors with desc2 SHARDED over GPUs (BASELINE config 4: one query set against a large map; SURVEY
+ * 8e).  Every GPU holds all of d1 and one contiguous shard of desc2 starting at global row index_offset.
+ * vslam_match_shard writes part4 [n1][4] int32 = (best distance, GLOBAL index of the lowest-index best row of this
+ * shard, second best, mutual-check flag of that row) -- 16 bytes per query, the only data that has to be
+ * gathered.  vslam_match_merge_shards merges n_parts such parts ([n_parts][n1][4], any order) with the
+ * associative operator of the scan (lowest global index wins ties) and applies threshold / ratio / mutual check:
+ * the result equals vslam_match(d1, all of desc2). */
+int vslam_match_shard(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_t* d2_shard, int n2_shard,
+                      int index_offset, int threshold, double dist_2_best, int32_t* part4);
+int vslam_match_merge_shards(vslam_ctx* ctx, const int32_t* parts4, int n_parts, int n1, int threshold,
+                             double dist_2_best, int32_t* pairs, int cap, int* n);
 /* Min-eigenvalue response map (the float image cv::goodFeaturesToTrack thresholds,
  * OCV featureselect.cpp:411) -- exported for parity tests.  lam: h x w floats, dense. */
 int vslam_response(vslam_ctx* ctx, const uint8_t* img, int w, int h, int pitch, float* lam);

@@ -290,6 +290,43 @@ def load_geometry_ref():
     return Geometry(C.CDLL(path), "reference")
 
 
+# --- DB-sharded matchDescriptors (config 4 across GPUs): CPU statement of the part / merge pair -------------
+def _passes(m1, m2, threshold, ratio):
+    """keypoints.h:355-357: best1 < threshold and not (best2 < best1 * dist_2_best) (int * double)."""
+    return (m1 < threshold) & ~(m2.astype(np.float64) < m1.astype(np.float64) * ratio)
+
+
+def match_shard_part(o, d1, d2_shard, index_offset, threshold=70, ratio=1.2):
+    """[n1][4] int32 (m1, global a1, m2, mutual flag) of one desc2 shard, from the restated scan
+    (keypoints.h:331-354 for the rows, :278-313 isPQiffQP for the flag)."""
+    d1 = np.ascontiguousarray(d1, np.uint32).reshape(-1, 8)
+    d2 = np.ascontiguousarray(d2_shard, np.uint32).reshape(-1, 8)
+    part = np.empty((len(d1), 4), np.int32)
+    if len(d2) == 0:
+        part[:] = [256, index_offset, 256, 0]
+        return part
+    rows = o.best2(d1, d2)
+    cols = o.best2(d2, d1)
+    c = cols[rows[:, 1]]
+    flag = _passes(c[:, 0], c[:, 2], threshold, ratio) & (c[:, 1] == np.arange(len(d1)))
+    part[:, 0], part[:, 1], part[:, 2], part[:, 3] = rows[:, 0], rows[:, 1] + index_offset, rows[:, 2], flag
+    return part
+
+
+def merge_shard_parts(parts, threshold=70, ratio=1.2):
+    """Associative merge of the row triples (lowest global index wins ties), then threshold / ratio / mutual flag."""
+    parts = np.asarray(parts, np.int32)
+    best = parts[0].copy()
+    for v in parts[1:]:
+        m2 = np.minimum(np.minimum(best[:, 2], v[:, 2]), np.maximum(best[:, 0], v[:, 0]))
+        take = (v[:, 0] < best[:, 0]) | ((v[:, 0] == best[:, 0]) & (v[:, 1] < best[:, 1]))
+        best[take] = v[take]
+        best[:, 2] = m2
+    ok = _passes(best[:, 0], best[:, 2], threshold, ratio) & (best[:, 3] != 0)
+    idx = np.nonzero(ok)[0]
+    return np.stack([idx, best[idx, 1]], 1).astype(np.int32)
+
+
 def load_oracle():
     path = os.path.join(_HERE, "liboracle.so")
     if not os.path.exists(path):

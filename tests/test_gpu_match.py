@@ -109,3 +109,41 @@ def test_match_batch_store(ctx, oracle_port):
         want = oracle_port.match(kf_list[i], kf_list[j], 70, 1.2)
         assert c == len(want) and np.array_equal(m[:c], want), (i, j)
     store.close()
+
+
+@pytest.mark.parametrize("n_shards", [1, 2, 3, 8])
+def test_match_db_sharded_equals_unsharded(ctx, oracle_port, n_shards):
+    """Config 4 with desc2 split into shards (one per GPU in production; here one after the other on one GPU):
+    vslam_match_shard + vslam_match_merge_shards == vslam_match on the whole DB == the oracle; equal best
+    distances in different shards resolve to the lowest global index; an empty shard is harmless."""
+    import oracle.oracle as oo
+    from visnav_b200 import sharding, workloads as wl
+    rng = np.random.default_rng(n_shards)
+    db = wl.random_descriptors(20011, 8)
+    q = wl.flip_bits(db[rng.integers(0, len(db), 700)], 22, rng)
+    db[15000:15050] = db[3000:3050]
+    for thr, ratio in [(70, 1.2), (256, 1.0)]:
+        parts, cpu_parts = [], []
+        for r in range(n_shards):
+            lo, hi = sharding.shard_range(len(db), r, n_shards)
+            parts.append(ctx.match_shard(q, db[lo:hi], lo, thr, ratio))
+            cpu_parts.append(oo.match_shard_part(oracle_port, q, db[lo:hi], lo, thr, ratio))
+        assert np.array_equal(np.stack(parts), np.stack(cpu_parts))
+        parts.append(ctx.match_shard(q, db[:0], len(db), thr, ratio))      # empty shard
+        want = oracle_port.match(q, db, thr, ratio)
+        assert np.array_equal(ctx.match_merge_shards(np.stack(parts), thr, ratio), want)
+        assert np.array_equal(ctx.match_merge_shards(np.stack(parts[::-1]), thr, ratio), want)
+        assert np.array_equal(ctx.match(q, db, thr, ratio), want)
+
+
+def test_match_db_sharded_config4_full_size(ctx):
+    """BASELINE config 4 in full (1500 x 200 000) over 8 shards: every planted query finds its DB row."""
+    from visnav_b200 import sharding, workloads as wl
+    q, db = wl.reloc_query()
+    parts = []
+    for r in range(8):
+        lo, hi = sharding.shard_range(len(db), r, 8)
+        parts.append(ctx.match_shard(q, db[lo:hi], lo))
+    got = ctx.match_merge_shards(np.stack(parts))
+    assert np.array_equal(got, ctx.match(q, db))
+    assert np.array_equal(got, np.stack([np.arange(1500), 133 * np.arange(1500)], 1))

@@ -412,6 +412,62 @@ int vslam_best2(vslam_ctx* ctx, const uint32_t* q, int nq, const uint32_t* db, i
   return match_common(ctx, q, nq, db, ndb, 0, 0.0, nullptr, 0, &dummy, out3);
 }
 
+int vslam_match_shard(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_t* d2_shard, int n2_shard,
+                      int index_offset, int threshold, double dist_2_best, int32_t* part4) {
+  if (!ctx) return VSLAM_E_ARG;
+  if (n1 < 0 || n2_shard < 0 || index_offset < 0 || (n1 > 0 && (!d1 || !part4)) || (n2_shard > 0 && !d2_shard))
+    return vs_fail(ctx, VSLAM_E_ARG, "bad shard arguments");
+  if (n1 == 0) return VSLAM_OK;
+  if (n2_shard == 0) {  // an empty shard contributes the scan's initial values and can never win the mutual check
+    for (int i = 0; i < n1; ++i) {
+      part4[4 * i] = 256; part4[4 * i + 1] = index_offset; part4[4 * i + 2] = 256; part4[4 * i + 3] = 0;
+    }
+    return VSLAM_OK;
+  }
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  VS_CUDA(ctx, ctx->d1.reserve((size_t)n1 * 32));
+  VS_CUDA(ctx, ctx->d2.reserve((size_t)n2_shard * 32));
+  VS_CUDA(ctx, ctx->pairs.reserve((size_t)n1 * 16));
+  VS_CUDA(ctx, cudaMemcpyAsync(ctx->d1.p, d1, (size_t)n1 * 32, cudaMemcpyHostToDevice, ctx->stream));
+  VS_CUDA(ctx, cudaMemcpyAsync(ctx->d2.p, d2_shard, (size_t)n2_shard * 32, cudaMemcpyHostToDevice, ctx->stream));
+  VS_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+  int rc = launch_match_shard(ctx, ctx->d1.as<uint32_t>(), n1, ctx->d2.as<uint32_t>(), n2_shard, index_offset, threshold,
+                              dist_2_best, ctx->pairs.as<int32_t>());
+  if (rc) return rc;
+  VS_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+  VS_CUDA(ctx, cudaMemcpyAsync(part4, ctx->pairs.p, (size_t)n1 * 16, cudaMemcpyDeviceToHost, ctx->stream));
+  VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  VS_CUDA(ctx, cudaEventElapsedTime(&ctx->last_match_ms, ctx->ev[0], ctx->ev[1]));
+  return VSLAM_OK;
+}
+
+int vslam_match_merge_shards(vslam_ctx* ctx, const int32_t* parts4, int n_parts, int n1, int threshold,
+                             double dist_2_best, int32_t* pairs, int cap, int* n) {
+  if (!ctx) return VSLAM_E_ARG;
+  if (!n || n_parts < 0 || n1 < 0 || cap < 0 || (n_parts > 0 && n1 > 0 && !parts4) || (cap > 0 && !pairs))
+    return vs_fail(ctx, VSLAM_E_ARG, "bad merge arguments");
+  *n = 0;
+  if (n_parts == 0 || n1 == 0) return VSLAM_OK;
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int dcap = cap > 0 ? cap : 1;
+  const size_t pbytes = (size_t)n_parts * n1 * 16;
+  VS_CUDA(ctx, ctx->rowpart.reserve(pbytes));
+  VS_CUDA(ctx, ctx->pairs.reserve((size_t)dcap * 8));
+  VS_CUDA(ctx, ctx->mcnt.reserve(256));
+  VS_CUDA(ctx, cudaMemcpyAsync(ctx->rowpart.p, parts4, pbytes, cudaMemcpyHostToDevice, ctx->stream));
+  int rc = launch_merge_shards(ctx, ctx->rowpart.as<int32_t>(), n_parts, n1, threshold, dist_2_best,
+                               ctx->pairs.as<int32_t>(), ctx->mcnt.as<int32_t>(), dcap);
+  if (rc) return rc;
+  int32_t* hn = static_cast<int32_t*>(ctx->pinned);
+  VS_CUDA(ctx, cudaMemcpyAsync(hn, ctx->mcnt.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *n = *hn;
+  const int m = *n < cap ? *n : cap;
+  if (m > 0) VS_CUDA(ctx, cudaMemcpy(pairs, ctx->pairs.p, (size_t)m * 8, cudaMemcpyDeviceToHost));
+  if (*n > cap) return vs_fail(ctx, VSLAM_E_CAPACITY, "more matches than the output capacity");
+  return VSLAM_OK;
+}
+
 float vslam_last_match_ms(vslam_ctx* ctx) { return ctx ? ctx->last_match_ms : 0.f; }
 
 int vslam_event_record(vslam_ctx* ctx, int slot) {

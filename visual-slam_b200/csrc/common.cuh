@@ -121,6 +121,11 @@ int launch_match_large(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_
                        int threshold, double ratio, int32_t* pairs, int32_t* count, int cap,
                        int32_t* best2_out /*nullable: [n1][3], skips the match predicate*/);
 bool match_fits_fused(int n1, int n2);
+// DB-sharded matching: part4 [n1][4] = (m1, a1 + index_offset, m2, col_ok) of one shard; merge of n_parts parts
+int launch_match_shard(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_t* d2, int n2, int index_offset,
+                       int threshold, double ratio, int32_t* part4);
+int launch_merge_shards(vslam_ctx* ctx, const int32_t* parts4, int n_parts, int n1, int threshold, double ratio,
+                        int32_t* pairs, int32_t* count, int cap);
 // jobs_i2: [n_jobs][2] set indices into (offsets, counts); fills MatchJob records on the device
 int launch_build_store_jobs(vslam_ctx* ctx, const int32_t* jobs_i2, int n_jobs, const uint32_t* desc,
                             const int64_t* offsets, const int32_t* counts, int n_sets, int32_t* pairs,

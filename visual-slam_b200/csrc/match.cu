@@ -474,16 +474,21 @@ int launch_match_jobs(vslam_ctx* ctx, const MatchJob* jobs_dev, int n_jobs, int 
 
 bool match_fits_fused(int n1, int n2) { return fused_smem_bytes(n1, n2) <= 200 * 1024 && n1 <= kMaxIndex && n2 <= kMaxIndex; }
 
-int launch_match_large(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_t* d2, int n2,
-                       int threshold, double ratio, int32_t* pairs, int32_t* count, int cap,
-                       int32_t* best2_out) {
-  if (n1 > kMaxIndex) return vs_fail(ctx, VSLAM_E_LIMIT, "more than 2^20 query descriptors");
-  // columns per CTA: aim at two CTAs per SM, keep ranges a multiple of the stage size
+// columns per CTA of the split path: aim at two CTAs per SM, keep ranges a multiple of the stage size
+static int split_range(const vslam_ctx* ctx, int n2) {
   const int target = ctx->num_sms * 2;
   int range = (n2 + target - 1) / target;
   range = ((range + kChunk - 1) / kChunk) * kChunk;
   if (range < kChunk) range = kChunk;
   if (range > 8192) range = 8192;
+  return range;
+}
+
+int launch_match_large(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_t* d2, int n2,
+                       int threshold, double ratio, int32_t* pairs, int32_t* count, int cap,
+                       int32_t* best2_out) {
+  if (n1 > kMaxIndex) return vs_fail(ctx, VSLAM_E_LIMIT, "more than 2^20 query descriptors");
+  const int range = split_range(ctx, n2);
   const int nsplit = (n2 + range - 1) / range;
   VS_CUDA(ctx, ctx->rowpart.reserve((size_t)nsplit * n1 * sizeof(uint2) + (size_t)n1 * sizeof(int3)));
   VS_CUDA(ctx, ctx->colstat.reserve((size_t)n2 * sizeof(uint2)));
@@ -505,6 +510,88 @@ int launch_match_large(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_
     finalize_large_kernel<<<1, 1024, 0, ctx->stream>>>(rowstat, p.colstat, n1, threshold, ratio, pairs, count, cap);
     ctx->launches++;
   }
+  VS_CUDA(ctx, cudaGetLastError());
+  return VSLAM_OK;
+}
+
+// ---- DB-sharded matching (BASELINE config 4 across GPUs) -------------------------------------
+// One shard of desc2 per GPU, all of desc1 on every GPU: the column statistics T(d2[j], desc1) are complete
+// locally; the row statistics are partial.  A shard reports per query i the int4 (m1, a1 + index_offset, m2,
+// col_ok) with col_ok = "T(d2[a1], desc1) passes and names i".  Merging shards is the associative operator of
+// the row triple (lowest global index wins ties); the winner's col_ok is the mutual check.
+__global__ void shard_part_kernel(const int3* __restrict__ rowstat, const uint2* __restrict__ colstat, int n1,
+                                  int index_offset, int threshold, double ratio, int4* __restrict__ part) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n1) return;
+  const int3 R = rowstat[i];
+  const uint2 C = colstat[R.y];
+  const bool col_ok = passes(C.x >> kShift, C.y >> kShift, threshold, ratio) && (int)(C.x & kIdxMask) == i;
+  part[i] = make_int4(R.x, R.y + index_offset, R.z, col_ok ? 1 : 0);
+}
+
+__global__ void __launch_bounds__(1024)
+    merge_shards_kernel(const int4* __restrict__ parts, int n_parts, int n1, int threshold, double ratio,
+                        int32_t* pairs, int32_t* count, int cap) {
+  __shared__ int warp_sums[32];
+  __shared__ int running;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) running = 0;
+  __syncthreads();
+  for (int base = 0; base < n1; base += 1024) {
+    const int i = base + tid;
+    bool ok = false;
+    int j = 0;
+    if (i < n1) {
+      int4 best = parts[i];
+      for (int s = 1; s < n_parts; ++s) {
+        const int4 v = parts[(size_t)s * n1 + i];
+        const int m2 = min(min(best.z, v.z), max(best.x, v.x));
+        if (v.x < best.x || (v.x == best.x && v.y < best.y)) best = v;
+        best.z = m2;
+      }
+      j = best.y;
+      ok = passes(best.x, best.z, threshold, ratio) && best.w != 0;
+    }
+    const unsigned bal = __ballot_sync(0xFFFFFFFFu, ok);
+    if (lane == 0) warp_sums[warp] = __popc(bal);
+    __syncthreads();
+    int off = running, tot = 0;
+    for (int w = 0; w < 32; ++w) {
+      if (w < warp) off += warp_sums[w];
+      tot += warp_sums[w];
+    }
+    const int pos = off + __popc(bal & ((1u << lane) - 1));
+    if (ok && pos < cap) {
+      pairs[2 * pos] = i;
+      pairs[2 * pos + 1] = j;
+    }
+    __syncthreads();
+    if (tid == 0) running += tot;
+    __syncthreads();
+  }
+  if (tid == 0) *count = running;
+}
+
+int launch_match_shard(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_t* d2, int n2, int index_offset,
+                       int threshold, double ratio, int32_t* part4) {
+  // row statistics land in ctx->rowpart (after the partials), column statistics in ctx->colstat
+  int rc = launch_match_large(ctx, d1, n1, d2, n2, threshold, ratio, nullptr, nullptr, 0, part4 /*scratch: 12 B/row*/);
+  if (rc) return rc;
+  const int range = split_range(ctx, n2);
+  const int nsplit = (n2 + range - 1) / range;
+  const int3* rowstat = reinterpret_cast<const int3*>(ctx->rowpart.as<uint2>() + (size_t)nsplit * n1);
+  shard_part_kernel<<<(n1 + 255) / 256, 256, 0, ctx->stream>>>(rowstat, ctx->colstat.as<uint2>(), n1, index_offset,
+                                                               threshold, ratio, reinterpret_cast<int4*>(part4));
+  ctx->launches++;
+  VS_CUDA(ctx, cudaGetLastError());
+  return VSLAM_OK;
+}
+
+int launch_merge_shards(vslam_ctx* ctx, const int32_t* parts4, int n_parts, int n1, int threshold, double ratio,
+                        int32_t* pairs, int32_t* count, int cap) {
+  merge_shards_kernel<<<1, 1024, 0, ctx->stream>>>(reinterpret_cast<const int4*>(parts4), n_parts, n1, threshold, ratio,
+                                                   pairs, count, cap);
+  ctx->launches++;
   VS_CUDA(ctx, cudaGetLastError());
   return VSLAM_OK;
 }

@@ -37,7 +37,7 @@ ABI_SYMBOLS = [
     "vslam_event_record", "vslam_event_elapsed_ms",
     "vslam_cam_project", "vslam_cam_unproject", "vslam_find_inliers_essential", "vslam_project_landmarks",
     "vslam_stereo_batch_epipolar", "vslam_stereo_plan_set_epipolar", "vslam_stereo_plan_download_inliers",
-    "vslam_stereo_plan_last_epipolar_ms",
+    "vslam_stereo_plan_last_epipolar_ms", "vslam_match_shard", "vslam_match_merge_shards",
 ]
 
 VSLAM_OPT_FP_CONTRACT = 1
@@ -143,6 +143,8 @@ def load_library():
     L.vslam_popc_peak.argtypes = [vp, C.POINTER(d)]
     L.vslam_event_record.argtypes = [vp, i]
     L.vslam_event_elapsed_ms.argtypes = [vp, i, i, C.POINTER(C.c_float)]
+    L.vslam_match_shard.argtypes = [vp, vp, i, vp, i, i, i, d, vp]
+    L.vslam_match_merge_shards.argtypes = [vp, vp, i, i, i, d, vp, i, C.POINTER(i)]
     cam = C.POINTER(Camera)
     L.vslam_cam_project.argtypes = [vp, cam, vp, i, vp]
     L.vslam_cam_unproject.argtypes = [vp, cam, vp, i, vp]
@@ -356,6 +358,27 @@ class Context:
         self._check(self.lib.vslam_project_landmarks(self.h, _ptr(pose), C.byref(cam), _ptr(xyz), len(xyz),
                                                      float(cam_z_threshold), _ptr(xy), _ptr(idx), cap, C.byref(n)))
         return xy[:n.value].copy(), idx[:n.value].copy()
+
+    def match_shard(self, d1, d2_shard, index_offset, threshold=70, dist_2_best=1.2):
+        """One DB shard of a sharded matchDescriptors: -> part [n1][4] int32 (m1, global a1, m2, mutual flag)."""
+        d1 = np.ascontiguousarray(d1, np.uint32).reshape(-1, 8)
+        d2 = np.ascontiguousarray(d2_shard, np.uint32).reshape(-1, 8)
+        part = np.empty((len(d1), 4), np.int32)
+        self._check(self.lib.vslam_match_shard(self.h, _ptr(d1), len(d1), _ptr(d2), len(d2), int(index_offset),
+                                               int(threshold), float(dist_2_best), _ptr(part)))
+        return part
+
+    def match_merge_shards(self, parts, threshold=70, dist_2_best=1.2, cap=None):
+        """parts: [n_parts][n1][4] int32 from match_shard (any order) -> matches [m][2], as match() on the whole DB."""
+        parts = np.ascontiguousarray(parts, np.int32)
+        assert parts.ndim == 3 and parts.shape[2] == 4
+        n_parts, n1 = parts.shape[:2]
+        cap = n1 if cap is None else cap
+        pairs = np.empty((max(cap, 1), 2), np.int32)
+        n = C.c_int(0)
+        self._check(self.lib.vslam_match_merge_shards(self.h, _ptr(parts), n_parts, n1, int(threshold),
+                                                      float(dist_2_best), _ptr(pairs), cap, C.byref(n)))
+        return pairs[:n.value].copy()
 
     def best2(self, q, db):
         q = np.ascontiguousarray(q, np.uint32).reshape(-1, 8)

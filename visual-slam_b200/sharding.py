@@ -34,3 +34,19 @@ def max_over_ranks(value, dist=None):
         t = t.cuda()
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+
+
+def gather_shard_parts(part, dist=None):
+    """Config 4 with desc2 sharded over ranks: gather every rank's [n1][4] int32 part (16 bytes per query --
+    the only exchange of the sharded matcher) into [world][n1][4] on every rank.  With NCCL the parts travel as
+    device tensors; with gloo (CPU tests) as host tensors."""
+    part = np.ascontiguousarray(part, np.int32)
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        return part[None].copy()
+    import torch
+    t = torch.from_numpy(part)
+    if dist.get_backend() == "nccl":
+        t = t.cuda()
+    out = [torch.empty_like(t) for _ in range(dist.get_world_size())]
+    dist.all_gather(out, t)
+    return torch.stack(out).cpu().numpy()
