@@ -195,7 +195,7 @@ def run_reference(args):
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample_txt},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(args):
@@ -316,13 +316,35 @@ def run_ours(args):
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
                                 "sample": "%d of the same synthetic pairs on %d host threads (reference functions from "
                                           "keypoints.h in oracle/_ref; gftt = C restatement pinned to cv2)" % (done, cores)}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Libraries under us (NCCL prints its version banner) write to fd 1; the contract is ONE JSON line on stdout.
+    Everything else goes to stderr: fd 1 is pointed at fd 2 and the JSON line is written to the saved descriptor."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _REAL_STDOUT is None:
+        os.write(1, data)
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
     args = parse()
+    quiet_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:
