@@ -57,6 +57,10 @@ typedef struct vslam_desc_store vslam_desc_store;
 #define VSLAM_OPT_BATCH_DEPTH 4 /* chunks in flight in vslam_stereo_batch, 1..4 (default 4): upload,
                                    compute and download of consecutive chunks overlap */
 
+#define VSLAM_OPT_MATCH_SPLIT_SMALL 5 /* 1 (default): a batch with fewer matching jobs than half the SM count
+                                        spreads every job's columns over all SMs (latency of a single stereo
+                                        pair); 0: always one CTA per job.  Results identical. */
+
 /* ---- context ------------------------------------------------------------------------ */
 int vslam_create(int device, vslam_ctx** out);
 void vslam_destroy(vslam_ctx* ctx);

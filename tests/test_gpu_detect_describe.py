@@ -155,3 +155,21 @@ def test_stereo_batch_chunked_pipeline(ctx):
             assert np.array_equal(out["desc"][2 * k + side, :c], out["desc"][2 * r + side, :c])
         m = out["n_matches"][k]
         assert m == out["n_matches"][r] and np.array_equal(out["matches"][k, :m], out["matches"][r, :m])
+
+
+@pytest.mark.parametrize("n", [1, 3, 40])
+def test_stereo_batch_small_counts_split_matcher(ctx, n):
+    """Small batches take the column-split matcher; the lists equal those of the one-CTA-per-job matcher."""
+    from visnav_b200.keypoints import VSLAM_OPT_MATCH_SPLIT_SMALL
+    base = wl.synth_stereo_batch(3, workers=1)
+    imgs = np.ascontiguousarray(base[np.arange(n) % 3])
+    a = ctx.stereo_batch(imgs, 1500)
+    ctx.set_option(VSLAM_OPT_MATCH_SPLIT_SMALL, 0)
+    try:
+        b = ctx.stereo_batch(imgs, 1500)
+    finally:
+        ctx.set_option(VSLAM_OPT_MATCH_SPLIT_SMALL, 1)
+    assert np.array_equal(a["n_matches"], b["n_matches"]) and (a["n_matches"] > 0).all()
+    for k in range(n):
+        m = a["n_matches"][k]
+        assert np.array_equal(a["matches"][k, :m], b["matches"][k, :m])

@@ -147,3 +147,30 @@ def test_match_db_sharded_config4_full_size(ctx):
     got = ctx.match_merge_shards(np.stack(parts))
     assert np.array_equal(got, ctx.match(q, db))
     assert np.array_equal(got, np.stack([np.arange(1500), 133 * np.arange(1500)], 1))
+
+
+@pytest.mark.parametrize("split", [1, 0])
+@pytest.mark.parametrize("n_sets", [2, 5, 13])
+def test_match_batch_small_batches_both_paths(ctx, oracle_port, split, n_sets):
+    """Few jobs: the column-split path (every job spread over all SMs) and the one-CTA-per-job path give the
+    oracle's lists -- ragged set sizes, an empty set, sets smaller than one stage, ties."""
+    from visnav_b200.keypoints import VSLAM_OPT_MATCH_SPLIT_SMALL
+    kf = wl.keyframe_descriptors(n_sets, 1400, 25)
+    rng = np.random.default_rng(n_sets)
+    sizes = [1400, 1337, 0, 63, 64, 65, 700, 1, 1400, 999, 130, 1400, 512][:n_sets]
+    kf_list = [kf[i][:sizes[i]] for i in range(n_sets)]
+    if n_sets > 4:
+        kf_list[4] = kf_list[1][:64].copy()        # identical descriptors in two sets: distance 0 ties
+    store = DescStore(ctx, kf_list)
+    jobs = wl.keyframe_pair_jobs(n_sets)
+    jobs = np.concatenate([jobs, jobs[:, ::-1][:3]])
+    ctx.set_option(VSLAM_OPT_MATCH_SPLIT_SMALL, split)
+    try:
+        for thr, ratio in [(70, 1.2), (256, 1.0)]:
+            matches, counts = ctx.match_batch(store, jobs, thr, ratio)
+            for (i, j), m, c in zip(jobs, matches, counts):
+                want = oracle_port.match(kf_list[i], kf_list[j], thr, ratio)
+                assert c == len(want) and np.array_equal(m[:c], want), (split, i, j, thr)
+    finally:
+        ctx.set_option(VSLAM_OPT_MATCH_SPLIT_SMALL, 1)
+    store.close()

@@ -44,6 +44,22 @@ for rep in range(20):
 out["c1_match_call_ms"] = 1e3 * float(np.median(t)); out["c1_match_kernel_ms"] = ctx.last_match_ms()
 print("c1", out["c1_match_call_ms"], out["c1_match_kernel_ms"], flush=True)
 
+# config 1: ONE stereo pair the way slam.cpp:1125-1143 issues it (two detectKeypointsAndDescriptors calls + one
+# matchDescriptors call, host buffers), and the same pair through one vslam_stereo_batch call
+pl, pr = wl.synth_stereo_pair(0)
+one = np.ascontiguousarray(np.stack([pl, pr])[None])
+t3, t1 = [], []
+for rep in range(30):
+    t0 = time.perf_counter()
+    _, _, dl = ctx.detect_describe(pl, 1500)
+    _, _, dr = ctx.detect_describe(pr, 1500)
+    m = ctx.match(dl, dr, 70, 1.2)
+    t3.append(time.perf_counter() - t0)
+    t0 = time.perf_counter(); o1 = ctx.stereo_batch(one, 1500); t1.append(time.perf_counter() - t0)
+out["c1_single_pair"] = dict(three_calls_ms=1e3 * float(np.median(t3)), one_batch_call_ms=1e3 * float(np.median(t1)),
+                             keypoints=[len(dl), len(dr)], matches=len(m))
+print("c1 pair", out["c1_single_pair"], flush=True)
+
 # stereo plan: stage times
 npairs = int(os.environ.get("PROBE_PAIRS", "256"))
 imgs = wl.synth_stereo_batch(npairs)

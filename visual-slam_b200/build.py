@@ -40,7 +40,8 @@ def build_native(force=False, verbose=False):
         o = os.path.join(CSRC, src[:-3] + ".o")
         objs.append(o)
         if force or _stale(o, [s] + hdrs):
-            cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
+            extra = os.environ.get("VSLAM_NVCC_EXTRA", "").split()   # e.g. -DVSLAM_SEL_PROFILE for latency work
+            cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
             procs.append((src, subprocess.Popen(cmd, cwd=CSRC, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
     for src, p in procs:
         out, _ = p.communicate()

@@ -130,6 +130,7 @@ int vslam_set_option(vslam_ctx* ctx, int option, int value) {
   if (!ctx) return VSLAM_E_ARG;
   if (option == VSLAM_OPT_FP_CONTRACT) ctx->fp_contract = value != 0;
   else if (option == VSLAM_OPT_MATCH_CSA) ctx->match_csa = value != 0;
+  else if (option == VSLAM_OPT_MATCH_SPLIT_SMALL) ctx->match_split_small = value != 0;
   else if (option == VSLAM_OPT_BATCH_CHUNK && value >= 1 && value <= 4096) ctx->batch_chunk = value;
   else if (option == VSLAM_OPT_BATCH_DEPTH && value >= 1 && value <= vslam_ctx::kMaxBatchDepth) ctx->batch_depth = value;
   else return vs_fail(ctx, VSLAM_E_ARG, "unknown option");
@@ -500,6 +501,7 @@ struct vslam_stereo_plan {
   DevImages im{};
   DevBuf images, xy, ang, desc, nkp, matches, nmatch, jobs;
   DevBuf cand, candcnt, imgmax, selws;
+  DevBuf mrow, mcol;            // scratch of the small-batch column-split matcher (plans run on their own streams)
   DevBuf inliers, ninl, epiws;  // optional fused findInliersEssential stage (vslam_stereo_plan_set_epipolar)
   bool epi_on = false;
   vslam_epipolar epi{};
@@ -517,7 +519,7 @@ void vslam_stereo_plan_destroy(vslam_stereo_plan* plan) {
   cudaDeviceSynchronize();
   DevBuf* bufs[] = {&plan->images, &plan->xy, &plan->ang, &plan->desc, &plan->nkp, &plan->matches, &plan->nmatch,
                     &plan->jobs, &plan->cand, &plan->candcnt, &plan->imgmax, &plan->selws, &plan->inliers,
-                    &plan->ninl, &plan->epiws};
+                    &plan->ninl, &plan->epiws, &plan->mrow, &plan->mcol};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 6; ++i)
     if (plan->ev[i]) cudaEventDestroy(plan->ev[i]);
@@ -626,7 +628,7 @@ int vslam_stereo_plan_run(vslam_stereo_plan* plan, int count, int num_features, 
   cudaEventRecord(plan->ev[3], ctx->stream);
   if (!rc)
     rc = launch_match_jobs(ctx, plan->jobs.as<MatchJob>(), count, plan->cap, plan->cap, match_threshold,
-                           match_dist_2_best, plan->cap);
+                           match_dist_2_best, plan->cap, &plan->mrow, &plan->mcol);
   cudaEventRecord(plan->ev[4], ctx->stream);
   if (!rc && plan->epi_on) {
     // matching_utils.h:63-88 on the matcher's device output: left corners of pair k are image 2k, right 2k+1

@@ -42,6 +42,7 @@ struct vslam_ctx {
   std::string err;
   int fp_contract = 1;
   int match_csa = 1;
+  int match_split_small = 1;  // batches with fewer jobs than SMs/2: split every job's columns over CTAs
   long long launches = 0;
   float last_match_ms = 0.f;
   // scratch for the single-call entry points
@@ -115,8 +116,9 @@ struct MatchJob {
   int32_t* pairs;  // [cap][2]
   int32_t* count;  // out
 };
+// rowpart / colstat: scratch of the small-batch column-split path (nullptr: the ctx's own, ctx stream only)
 int launch_match_jobs(vslam_ctx* ctx, const MatchJob* jobs_dev, int n_jobs, int max_n1, int max_n2,
-                      int threshold, double ratio, int cap);
+                      int threshold, double ratio, int cap, DevBuf* rowpart = nullptr, DevBuf* colstat = nullptr);
 int launch_match_large(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_t* d2, int n2,
                        int threshold, double ratio, int32_t* pairs, int32_t* count, int cap,
                        int32_t* best2_out /*nullable: [n1][3], skips the match predicate*/);

@@ -410,6 +410,106 @@ __global__ void __launch_bounds__(1024) finalize_large_kernel(const int3* __rest
   if (tid == 0) *count = running;
 }
 
+// ---- few jobs: every job's columns are split across CTAs (grid = column ranges x jobs) ----------------
+// One CTA per job leaves most SMs idle when a batch holds fewer jobs than the GPU has CTA slots (a single stereo
+// pair: 0.44 ms on one SM).  Here job blockIdx.y hands column range blockIdx.x to a CTA; a second launch merges the
+// per-range row partials and finalises each job (one CTA per job).  Counts may live on the device (MatchJob).
+struct SplitJobsParams {
+  const MatchJob* jobs;
+  int max_n1, max_n2;
+  int range, nsplit;  // columns per CTA (multiple of kChunk), ranges per job
+  uint2* rowpart;     // [n_jobs][nsplit][max_n1]
+  uint2* colstat;     // [n_jobs][max_n2]
+  int threshold;
+  double ratio;
+  int cap;
+};
+
+template <bool kCsa>
+__global__ void __launch_bounds__(kThreads, 2) match_split_jobs_kernel(const SplitJobsParams p) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const MatchJob job = p.jobs[blockIdx.y];
+  const int n1 = job.n1p ? *job.n1p : job.n1;
+  const int n2 = job.n2p ? *job.n2p : job.n2;
+  const int c0 = blockIdx.x * p.range;
+  if (n1 <= 0 || n2 <= 0 || n1 > p.max_n1 || n2 > p.max_n2 || c0 >= n2) return;  // uniform per CTA
+  unsigned char* rest;
+  const ScanSmem sm = carve(smem_raw, &rest);
+  uint2* cs = reinterpret_cast<uint2*>(rest);
+  const int tid = threadIdx.x;
+  const int ncols = min(p.range, n2 - c0);
+  if (tid == 0) {
+    for (int s = 0; s < kStages; ++s) mbar_init(&sm.full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  for (int j = tid; j < ncols; j += kThreads) cs[j] = make_uint2(kSent, kSent);
+  __syncthreads();
+  scan_rows_cols<kCsa>(reinterpret_cast<const uint4*>(job.d1), n1,
+                       reinterpret_cast<const uint4*>(job.d2) + (size_t)c0 * 2, ncols,
+                       p.rowpart + ((size_t)blockIdx.y * p.nsplit + blockIdx.x) * p.max_n1, cs, sm);
+  uint2* colstat = p.colstat + (size_t)blockIdx.y * p.max_n2;
+  for (int j = tid; j < ncols; j += kThreads) colstat[c0 + j] = cs[j];
+}
+
+__global__ void __launch_bounds__(1024) finalize_split_jobs_kernel(const SplitJobsParams p) {
+  __shared__ int warp_sums[32];
+  __shared__ int running;
+  const MatchJob job = p.jobs[blockIdx.x];
+  const int n1 = job.n1p ? *job.n1p : job.n1;
+  const int n2 = job.n2p ? *job.n2p : job.n2;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (n1 <= 0 || n2 <= 0 || n1 > p.max_n1 || n2 > p.max_n2) {
+    if (tid == 0) *job.count = (n1 > p.max_n1 || n2 > p.max_n2) ? -1 : 0;
+    return;
+  }
+  const int used = (n2 + p.range - 1) / p.range;
+  const uint2* rowpart = p.rowpart + (size_t)blockIdx.x * p.nsplit * p.max_n1;
+  const uint2* colstat = p.colstat + (size_t)blockIdx.x * p.max_n2;
+  if (tid == 0) running = 0;
+  __syncthreads();
+  for (int base = 0; base < n1; base += 1024) {
+    const int i = base + tid;
+    bool ok = false;
+    int j = 0;
+    if (i < n1) {
+      int m1 = 256, a1 = 0, m2 = 256;
+      for (int s = 0; s < used; ++s) {
+        const uint2 v = rowpart[(size_t)s * p.max_n1 + i];
+        const int d1 = v.x >> kShift, d2 = v.y >> kShift;
+        if (d1 < m1) {  // strictly better: earlier ranges keep ties (lowest index wins)
+          m2 = min(m1, d2);
+          m1 = d1;
+          a1 = s * p.range + (int)(v.x & kIdxMask);
+        } else {
+          m2 = min(m2, d1);
+        }
+      }
+      if (passes(m1, m2, p.threshold, p.ratio)) {
+        j = a1;
+        const uint2 C = colstat[j];
+        ok = passes(C.x >> kShift, C.y >> kShift, p.threshold, p.ratio) && (int)(C.x & kIdxMask) == i;
+      }
+    }
+    const unsigned bal = __ballot_sync(0xFFFFFFFFu, ok);
+    if (lane == 0) warp_sums[warp] = __popc(bal);
+    __syncthreads();
+    int off = running, tot = 0;
+    for (int w = 0; w < 32; ++w) {
+      if (w < warp) off += warp_sums[w];
+      tot += warp_sums[w];
+    }
+    const int pos = off + __popc(bal & ((1u << lane) - 1));
+    if (ok && pos < p.cap) {
+      job.pairs[2 * pos] = i;
+      job.pairs[2 * pos + 1] = j;
+    }
+    __syncthreads();
+    if (tid == 0) running += tot;
+    __syncthreads();
+  }
+  if (tid == 0) *job.count = running;
+}
+
 __global__ void build_store_jobs_kernel(const int2* __restrict__ jobs, int n_jobs, const uint32_t* desc,
                                        const int64_t* __restrict__ offsets, const int32_t* __restrict__ counts,
                                        int n_sets, int32_t* pairs, int32_t* out_counts, int cap, MatchJob* out) {
@@ -452,11 +552,40 @@ static size_t fused_smem_bytes(int max_n1, int max_n2) {
 }
 
 int launch_match_jobs(vslam_ctx* ctx, const MatchJob* jobs_dev, int n_jobs, int max_n1, int max_n2,
-                      int threshold, double ratio, int cap) {
+                      int threshold, double ratio, int cap, DevBuf* rowpart_buf, DevBuf* colstat_buf) {
+  if (!rowpart_buf) rowpart_buf = &ctx->rowpart;  // callers that run on their own stream bring their own scratch
+  if (!colstat_buf) colstat_buf = &ctx->colstat;
   if (n_jobs <= 0) return VSLAM_OK;
   if (max_n1 > kMaxIndex || max_n2 > kMaxIndex) return vs_fail(ctx, VSLAM_E_LIMIT, "descriptor set larger than 2^20");
   const size_t smem = fused_smem_bytes(max_n1, max_n2);
   if (smem > 200 * 1024) return vs_fail(ctx, VSLAM_E_LIMIT, "job too large for the fused matcher");
+  // Fewer jobs than CTA slots and jobs worth splitting: spread every job's columns over the idle SMs
+  // (one stereo pair: 0.44 ms on one SM -> 0.05 ms on all of them).
+  const int slots = ctx->num_sms * 2;
+  if (ctx->match_split_small && n_jobs * 2 <= ctx->num_sms && (long long)max_n1 * max_n2 > 256LL * 256LL) {
+    const int per_job = slots / n_jobs;  // >= 4
+    int range = (max_n2 + per_job - 1) / per_job;
+    range = ((range + kChunk - 1) / kChunk) * kChunk;
+    if (range > 8192) range = 8192;
+    SplitJobsParams sp;
+    sp.jobs = jobs_dev;
+    sp.max_n1 = max_n1; sp.max_n2 = max_n2;
+    sp.range = range;
+    sp.nsplit = (max_n2 + range - 1) / range;
+    VS_CUDA(ctx, rowpart_buf->reserve((size_t)n_jobs * sp.nsplit * max_n1 * sizeof(uint2)));
+    VS_CUDA(ctx, colstat_buf->reserve((size_t)n_jobs * max_n2 * sizeof(uint2)));
+    sp.rowpart = rowpart_buf->as<uint2>();
+    sp.colstat = colstat_buf->as<uint2>();
+    sp.threshold = threshold; sp.ratio = ratio; sp.cap = cap;
+    const size_t ssm = (size_t)kScanSmemBytes + (size_t)range * sizeof(uint2);
+    auto sk = ctx->match_csa ? match_split_jobs_kernel<true> : match_split_jobs_kernel<false>;
+    VS_CUDA(ctx, cudaFuncSetAttribute(sk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssm));
+    sk<<<dim3(sp.nsplit, n_jobs), kThreads, ssm, ctx->stream>>>(sp);
+    finalize_split_jobs_kernel<<<n_jobs, 1024, 0, ctx->stream>>>(sp);
+    ctx->launches += 2;
+    VS_CUDA(ctx, cudaGetLastError());
+    return VSLAM_OK;
+  }
   MatchParams p;
   p.jobs = jobs_dev;
   p.threshold = threshold;

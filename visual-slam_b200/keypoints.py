@@ -44,6 +44,7 @@ VSLAM_OPT_FP_CONTRACT = 1
 VSLAM_OPT_MATCH_CSA = 2
 VSLAM_OPT_BATCH_CHUNK = 3
 VSLAM_OPT_BATCH_DEPTH = 4
+VSLAM_OPT_MATCH_SPLIT_SMALL = 5
 
 
 class VslamError(RuntimeError):
