@@ -94,6 +94,7 @@ __device__ __forceinline__ uint32_t hamming256(const uint32_t (&a)[8], const uin
     const uint32_t s1 = xor3(x0, x1, x2), c1 = maj3(x0, x1, x2);
     const uint32_t s2 = xor3(x3, x4, x5), c2 = maj3(x3, x4, x5);
     const uint32_t s3 = xor3(s1, s2, x6), c3 = maj3(s1, s2, x6);
+    // (stopping one adder earlier -- 5 POPC, 14 LOP3 -- measured slower: 5.94e11 vs 6.14e11 distances/s)
     const uint32_t t = xor3(c1, c2, c3), f = maj3(c1, c2, c3);
     return (__popc(s3) + __popc(x7)) + 2u * __popc(t) + 4u * __popc(f);
   } else {
