@@ -1,0 +1,71 @@
+#!/usr/bin/env python3
+"""Randomised parity sweep: random image sizes / contents / feature caps and random descriptor-set sizes, CUDA path
+vs the CPU oracle (test infrastructure), for FUZZ_SECONDS (default 60).  Prints one JSON summary; exit 1 on any
+difference.  Complements tests/ (fixed cases) after kernel rewrites."""
+import json, os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import oracle, visnav_b200
+from visnav_b200 import workloads as wl
+from visnav_b200.keypoints import DescStore
+
+budget = float(os.environ.get("FUZZ_SECONDS", "60"))
+seed = int(os.environ.get("FUZZ_SEED", "1"))
+rng = np.random.default_rng(seed)
+ctx = visnav_b200.Context(0)
+o = oracle.load_oracle()
+stats = dict(seed=seed, images=0, corners=0, descriptors=0, match_calls=0, batch_jobs=0, failures=[])
+t_end = time.time() + budget
+it = 0
+while time.time() < t_end and len(stats["failures"]) < 5:
+    it += 1
+    kind = it % 4
+    w, h = int(rng.integers(40, 1300)), int(rng.integers(40, 900))
+    if kind == 0:
+        img = wl.synth_image(int(rng.integers(0, 1 << 30)), w, h)
+    elif kind == 1:
+        img = rng.integers(0, 256, (h, w), dtype=np.uint8)                       # dense noise
+    elif kind == 2:
+        img = (wl.synth_image(int(rng.integers(0, 1 << 30)), w, h) // 16 * 16).astype(np.uint8)  # quantised: ties
+    else:
+        img = np.kron(rng.integers(0, 256, ((h + 7) // 8, (w + 7) // 8), dtype=np.uint8), np.ones((8, 8), np.uint8))[:h, :w]
+        img = np.ascontiguousarray(img)                                          # blocks: plateaus
+    nf = int(rng.choice([0, 1, 50, 500, 1500, 4000]))
+    try:
+        xy, ang, desc = ctx.detect_describe(img, nf, True)
+    except Exception as e:  # documented limits (candidate list overflow) are not parity failures
+        if "overflow" in str(e):
+            continue
+        raise
+    wxy, wang, wdesc = o.detect_describe(img, nf)
+    ok = np.array_equal(xy, wxy) and (len(xy) == 0 or np.abs(ang - wang).max() <= 1e-5) and np.array_equal(desc, wdesc)
+    stats["images"] += 1; stats["corners"] += len(wxy); stats["descriptors"] += len(wdesc)
+    if not ok:
+        stats["failures"].append(dict(what="detect_describe", w=w, h=h, kind=kind, nf=nf, got=len(xy), want=len(wxy)))
+    # matching: random sizes, correlated sets, random threshold / ratio
+    n1, n2 = int(rng.integers(0, 2200)), int(rng.integers(0, 2200))
+    base = wl.random_descriptors(max(n1, n2, 1), int(rng.integers(0, 1 << 30)))
+    d1 = base[:n1]
+    d2 = wl.flip_bits(base[rng.permutation(max(n1, n2, 1))[:n2]], int(rng.integers(0, 60)), rng) if n2 else base[:0]
+    thr, ratio = int(rng.choice([70, 40, 256, 100])), float(rng.choice([1.2, 1.0, 1.5]))
+    got, want = ctx.match(d1, d2, thr, ratio), o.match(d1, d2, thr, ratio)
+    stats["match_calls"] += 1
+    if not np.array_equal(got, want):
+        stats["failures"].append(dict(what="match", n1=n1, n2=n2, thr=thr, ratio=ratio, got=len(got), want=len(want)))
+    if it % 8 == 0:   # batched jobs on a store (both matcher layouts depending on the job count)
+        ns = int(rng.integers(2, 7))
+        sets = [wl.flip_bits(base[:int(rng.integers(0, len(base) + 1))], 10, rng) for _ in range(ns)]
+        store = DescStore(ctx, sets)
+        jobs = np.array([(a, b) for a in range(ns) for b in range(ns) if a != b], np.int32)
+        ms, cs = ctx.match_batch(store, jobs, thr, ratio)
+        for (a, b), m, c in zip(jobs, ms, cs):
+            want = o.match(sets[a], sets[b], thr, ratio)
+            stats["batch_jobs"] += 1
+            if c != len(want) or not np.array_equal(m[:c], want):
+                stats["failures"].append(dict(what="match_batch", a=int(a), b=int(b), sizes=[len(s) for s in sets]))
+        store.close()
+stats["iterations"] = it
+print(json.dumps(stats))
+os.makedirs("gpurun_out", exist_ok=True)
+json.dump(stats, open("gpurun_out/fuzz.json", "w"), indent=1)
+sys.exit(1 if stats["failures"] else 0)
