@@ -66,6 +66,10 @@ int vslam_create(int device, vslam_ctx** out);
 void vslam_destroy(vslam_ctx* ctx);
 const char* vslam_last_error(vslam_ctx* ctx);
 int vslam_set_option(vslam_ctx* ctx, int option, int value);
+/* cv::goodFeaturesToTrack's useHarrisDetector / k (featureselect.cpp:376-380 -> cornerHarris, corner.cpp:104-153)
+ * for every detection call of this ctx.  The reference always passes false (keypoints.h:138-139): default off,
+ * k = 0.04 is OpenCV's default.  Response = a*c - b*b - k*(a + c)^2 on the same box-filtered covariance. */
+int vslam_set_harris(vslam_ctx* ctx, int use_harris_detector, double k);
 /* the CUDA stream (cudaStream_t) all work of this ctx is issued on; for event timing */
 void* vslam_stream(vslam_ctx* ctx);
 int vslam_sync(vslam_ctx* ctx);

@@ -70,8 +70,14 @@ class Oracle:
             lib.vso_response.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, _f32p]
             lib.vso_gftt.restype = C.c_int
             lib.vso_gftt.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, _f32p, C.c_int]
+            lib.vso_set_harris.restype = None
+            lib.vso_set_harris.argtypes = [C.c_int, C.c_double]
             lib.vso_best2.restype = None
             lib.vso_best2.argtypes = [_u32p, C.c_int, _u32p, C.c_int, _i32p]
+
+    def set_harris(self, on, k=0.04):
+        """goodFeaturesToTrack(useHarrisDetector, k) for the restatement's detection functions (port only)."""
+        self.lib.vso_set_harris(int(bool(on)), float(k))
 
     # --- detection -------------------------------------------------------------------------
     def response(self, img):

@@ -57,6 +57,15 @@ static inline int r101(int i, int n) {
  *   (corner.cpp:93-99).
  * lam is h*w floats, dense.
  */
+/* cv::goodFeaturesToTrack's useHarrisDetector / k for vso_response / vso_gftt / vso_detect (test knob; the
+ * reference passes false, keypoints.h:138-139).  cornerHarris shares everything with cornerMinEigenVal up to the
+ * box-filtered covariance (corner.cpp:237-322); calcHarris (corner.cpp:104-153) then runs its universal-intrinsics
+ * loop (float k, float operations) over all but the last (w*h) % 4 pixels of the continuous image and the scalar
+ * tail (double k) over the rest. */
+static int g_harris_on = 0;
+static double g_harris_k = 0.04;
+void vso_set_harris(int on, double k) { g_harris_on = on; g_harris_k = k; }
+
 int vso_response(const uint8_t* img, int w, int h, int pitch, float* lam) {
   if (!img || !lam || w <= 0 || h <= 0 || pitch < w) return -1;
   const double s = 1.0 / (4.0 * 3.0 * 255.0); /* corner.cpp:247-253 */
@@ -116,6 +125,23 @@ int vso_response(const uint8_t* img, int w, int h, int pitch, float* lam) {
         v = v + rs[((size_t)y * w + x) * 3 + k];
         v = v + rs[((size_t)yp * w + x) * 3 + k];
         abc[k] = (float)v;
+      }
+      if (g_harris_on) {
+        const size_t i = (size_t)y * w + x;
+        float ac_bb = abc[0] * abc[2];
+        float bb2 = abc[1] * abc[1];
+        ac_bb = ac_bb - bb2;
+        float ac = abc[0] + abc[2];
+        if (i < (npx & ~(size_t)3)) { /* corner.cpp:129-141 */
+          float t = (float)g_harris_k * ac;
+          t = t * ac;
+          lam[i] = ac_bb - t;
+        } else { /* corner.cpp:144-150 */
+          double t = g_harris_k * (double)ac;
+          t = t * (double)ac;
+          lam[i] = (float)((double)ac_bb - t);
+        }
+        continue;
       }
       float a = abc[0] * 0.5f;
       float b = abc[1];

@@ -66,3 +66,34 @@ def test_real_euroc_pair_vs_opencv_and_reference(ctx):
     m = int(out["n_matches"][0])
     assert np.array_equal(out["matches"][0, :m], g["matches"])
     assert np.array_equal(out["desc"][0, :out["n_kp"][0]], g["desc_l"])
+
+
+def test_harris_option_vs_opencv(ctx, oracle_port):
+    """vslam_set_harris(1, 0.04): corners == cv2.goodFeaturesToTrack(useHarrisDetector=True) (+ the 19-px filter),
+    response == cv2.cornerHarris bit for bit on the small fixture (incl. calcHarris' double-precision tail), and ==
+    the oracle on other sizes; switching it off restores the min-eigenvalue detector."""
+    from visnav_b200 import workloads as wl
+    g = _load("harris")
+    ctx.set_harris(True, 0.04)
+    oracle_port.set_harris(True, 0.04)
+    try:
+        for name in "abc":
+            w, h, seed, nf = (int(v) for v in g["meta_" + name])
+            img = g["img_" + name] if g["img_" + name].size else wl.synth_image(seed, w, h)
+            c = g["corners_unopt_" + name]
+            keep = (c[:, 0] >= 19) & (c[:, 0] < w - 19) & (c[:, 1] >= 19) & (c[:, 1] < h - 19)
+            assert np.array_equal(ctx.detect(img, nf), c[keep].astype(np.float64)), name
+            if "harris_unopt_" + name in g.files:
+                assert np.array_equal(ctx.response(img).view(np.uint32), g["harris_unopt_" + name].view(np.uint32))
+        for w, h, seed in [(203, 77, 3), (333, 201, 4), (752, 480, 8)]:
+            img = wl.synth_image(seed, w, h)
+            assert np.array_equal(ctx.response(img).view(np.uint32), oracle_port.response(img).view(np.uint32)), (w, h)
+            assert np.array_equal(ctx.detect(img, 500), oracle_port.detect(img, 500))
+        edges = np.zeros((120, 160), np.uint8)
+        edges[:, 80:] = 200                                   # a pure edge: every Harris response <= 0 -> no corner
+        assert len(ctx.detect(edges, 100)) == 0 == len(oracle_port.detect(edges, 100))
+    finally:
+        ctx.set_harris(False)
+        oracle_port.set_harris(False)
+    g2 = _load("gftt_161x123")
+    assert np.array_equal(ctx.response(g2["img"]).view(np.uint32), g2["lam_unopt"].view(np.uint32))

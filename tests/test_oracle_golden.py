@@ -146,3 +146,26 @@ def test_real_euroc_pair(oracle_port, oracle_ref):
     assert np.array_equal(oracle_port.match(descs["l"], descs["r"], 70, 1.2), g["matches"])
     if oracle_ref is not None:
         assert np.array_equal(oracle_ref.match(descs["l"], descs["r"], 70, 1.2), g["matches"])
+
+
+def test_harris_option_matches_opencv(oracle_port):
+    """goodFeaturesToTrack(useHarrisDetector=True, k=0.04).  Restatement == cv2 corners (scalar
+    and default dispatch agree on the fixtures) and == cv2.cornerHarris bit for bit on the small image, whose pixel
+    count is not a multiple of 4 (calcHarris' double-precision scalar tail, corner.cpp:144-150)."""
+    g = np.load(os.path.join(GOLD, "harris.npz"))
+    from visnav_b200 import workloads as wl
+    oracle_port.set_harris(True, 0.04)
+    try:
+        for name in "abc":
+            w, h, seed, nf = (int(v) for v in g["meta_" + name])
+            img = g["img_" + name] if g["img_" + name].size else wl.synth_image(seed, w, h)
+            assert np.array_equal(oracle_port.gftt(img, nf), g["corners_unopt_" + name]), name
+            assert np.array_equal(g["corners_unopt_" + name], g["corners_default_" + name])
+            if "harris_unopt_" + name in g.files:
+                assert (w * h) % 4 != 0
+                assert np.array_equal(oracle_port.response(img).view(np.uint32), g["harris_unopt_" + name].view(np.uint32))
+    finally:
+        oracle_port.set_harris(False)
+    # off again: the min-eigenvalue fixture still holds
+    g2 = np.load(os.path.join(GOLD, "gftt_161x123.npz"))
+    assert np.array_equal(oracle_port.response(g2["img"]).view(np.uint32), g2["lam_unopt"].view(np.uint32))

@@ -120,6 +120,27 @@ def geometry():
     np.savez_compressed(os.path.join(OUT, "geometry.npz"), **rec)
 
 
+def harris():
+    """goodFeaturesToTrack(useHarrisDetector=True, k=0.04) and cornerHarris by cv2 (scalar and default dispatch):
+    SURVEY 8a row a14 (the reference itself always passes false, keypoints.h:138-139)."""
+    rec = {}
+    for name, (w, h, seed, nf) in {"a": (161, 123, 9, 0), "b": (320, 240, 5, 300), "c": (752, 480, 1234, 1500)}.items():
+        img = wl.synth_image(seed, w, h)
+        rec["img_" + name] = img if w < 700 else np.zeros((0, 0), np.uint8)
+        rec["meta_" + name] = np.array([w, h, seed, nf])
+        for tag, opt in (("unopt", False), ("default", True)):
+            cv2.setUseOptimized(opt)
+            pts = cv2.goodFeaturesToTrack(img, nf, 0.01, 8, None, None, 3, True, 0.04)
+            rec["corners_%s_%s" % (tag, name)] = (np.zeros((0, 2), np.float32) if pts is None else
+                                                  pts.reshape(-1, 2).astype(np.float32))
+            if w < 200 and not opt:
+                rec["harris_unopt_" + name] = cv2.cornerHarris(img, 3, 3, 0.04)
+            cv2.setUseOptimized(True)
+        print("harris", name, len(rec["corners_unopt_" + name]), "default dispatch identical:",
+              np.array_equal(rec["corners_unopt_" + name], rec["corners_default_" + name]))
+    np.savez_compressed(os.path.join(OUT, "harris.npz"), **rec)
+
+
 def euroc():
     """One REAL EuRoC stereo pair bundled with the reference (data/euroc_V1, 752x480): decoded here with cv2
     (the decoded bytes are stored, so the fixture does not depend on a JPEG decoder), corners by cv2's
@@ -157,8 +178,11 @@ if __name__ == "__main__":
         geometry()
     elif len(sys.argv) > 1 and sys.argv[1] == "euroc":
         euroc()
+    elif len(sys.argv) > 1 and sys.argv[1] == "harris":
+        harris()
     else:
         main()
         landmarks()
         geometry()
         euroc()
+        harris()

@@ -112,6 +112,26 @@ def main():
     o = oracle.load_oracle()
     ref = oracle.load_ref()
     rep = dict(cv2=(cv2.__version__ if cv2 is not None else None), reference_library=ref is not None, sizes=[])
+    if cv2 is not None:
+        # response MAP vs cv2.cornerMinEigenVal (scalar dispatch) pixel by pixel: OpenCV's box filter keeps a RUNNING
+        # column sum in double (ColumnSum<double, float>); where an addition is inexact its rounding residue travels
+        # down the column, and far below a strong edge it can tip the float rounding of a WEAK response by one ulp.
+        # The band-parallel kernel (and the oracle) sum the three rows directly.
+        rm = []
+        for (w, h, seed) in [(752, 480, 1234), (1920, 1080, 77), (320, 240, 5)]:
+            img = wl.synth_image(seed, w, h)
+            cv2.setUseOptimized(False)
+            want = cv2.cornerMinEigenVal(img, 3, ksize=3)
+            cv2.setUseOptimized(True)
+            got = ctx.response(img)
+            diff = got.view(np.int32).astype(np.int64) - want.view(np.int32).astype(np.int64)
+            bad = np.nonzero(diff)
+            thr = float(want.max()) * 0.01
+            rm.append(dict(size="%dx%d" % (w, h), pixels=w * h, differing=int(len(bad[0])),
+                           max_ulp=int(np.abs(diff).max()), rate=len(bad[0]) / (w * h),
+                           largest_differing_response_over_threshold=(float(want[bad].max()) / thr if len(bad[0]) else 0.0),
+                           equals_oracle=bool(np.array_equal(got.view(np.uint32), o.response(img).view(np.uint32)))))
+        rep["response_map_vs_cv2_scalar"] = rm
     rep["sizes"].append(run_size(ctx, o, ref, 752, 480, 1500, a.pairs, 7000))
     rep["sizes"].append(run_size(ctx, o, ref, 1920, 1080, 4000, a.pairs_1080, 8000))
     rep["sizes"].append(run_size(ctx, o, ref, 321, 243, 300, 8, 9000))

@@ -137,6 +137,14 @@ int vslam_set_option(vslam_ctx* ctx, int option, int value) {
   return VSLAM_OK;
 }
 
+int vslam_set_harris(vslam_ctx* ctx, int use_harris_detector, double k) {
+  if (!ctx) return VSLAM_E_ARG;
+  if (!(k == k)) return vs_fail(ctx, VSLAM_E_ARG, "harris k is NaN");
+  ctx->harris_on = use_harris_detector != 0;
+  ctx->harris_k = k;
+  return VSLAM_OK;
+}
+
 void* vslam_stream(vslam_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 
 int vslam_sync(vslam_ctx* ctx) {

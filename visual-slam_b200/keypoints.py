@@ -37,7 +37,7 @@ ABI_SYMBOLS = [
     "vslam_event_record", "vslam_event_elapsed_ms",
     "vslam_cam_project", "vslam_cam_unproject", "vslam_find_inliers_essential", "vslam_project_landmarks",
     "vslam_stereo_batch_epipolar", "vslam_stereo_plan_set_epipolar", "vslam_stereo_plan_download_inliers",
-    "vslam_stereo_plan_last_epipolar_ms", "vslam_match_shard", "vslam_match_merge_shards",
+    "vslam_stereo_plan_last_epipolar_ms", "vslam_match_shard", "vslam_match_merge_shards", "vslam_set_harris",
 ]
 
 VSLAM_OPT_FP_CONTRACT = 1
@@ -144,6 +144,7 @@ def load_library():
     L.vslam_popc_peak.argtypes = [vp, C.POINTER(d)]
     L.vslam_event_record.argtypes = [vp, i]
     L.vslam_event_elapsed_ms.argtypes = [vp, i, i, C.POINTER(C.c_float)]
+    L.vslam_set_harris.argtypes = [vp, i, d]
     L.vslam_match_shard.argtypes = [vp, vp, i, vp, i, i, i, d, vp]
     L.vslam_match_merge_shards.argtypes = [vp, vp, i, i, i, d, vp, i, C.POINTER(i)]
     cam = C.POINTER(Camera)
@@ -213,6 +214,10 @@ class Context:
 
     def set_option(self, opt, value):
         self._check(self.lib.vslam_set_option(self.h, opt, int(value)))
+
+    def set_harris(self, use_harris_detector, k=0.04):
+        """goodFeaturesToTrack(useHarrisDetector, k) for this context's detection calls (reference: always False)."""
+        self._check(self.lib.vslam_set_harris(self.h, int(bool(use_harris_detector)), float(k)))
 
     def stream(self):
         return self.lib.vslam_stream(self.h)
