@@ -188,6 +188,10 @@ int vslam_stereo_plan_last_ms(vslam_stereo_plan* plan, float* ms);
 int vslam_desc_store_create(vslam_ctx* ctx, const uint32_t* desc, const int64_t* offsets,
                             const int32_t* counts, int n_sets, vslam_desc_store** out);
 void vslam_desc_store_destroy(vslam_desc_store* s);
+/* Appends one descriptor set (a new keyframe: slam.cpp:1153-1154 copies kd into feature_corners) and returns its
+ * set index; earlier indices stay valid.  Amortised O(count): the device buffers grow geometrically. */
+int vslam_desc_store_append(vslam_desc_store* s, const uint32_t* desc, int count, int* set_index);
+int vslam_desc_store_size(const vslam_desc_store* s);
 /* jobs: n_jobs x 2 int32 (set index of descriptors_1, set index of descriptors_2).
  * Outputs: matches [n_jobs][cap][2], n_matches [n_jobs] (host; either may be NULL). */
 int vslam_match_batch(vslam_ctx* ctx, const vslam_desc_store* s, const int32_t* jobs, int n_jobs,

@@ -123,3 +123,33 @@ def test_geometry_dropin_header():
     want = [w for w in want if 0 <= w[1] <= 752 and 0 <= w[2] <= 480]
     assert [int(r[0]) for r in proj] == [w[0] for w in want]
     assert np.abs(np.array([[float(r[1]), float(r[2])] for r in proj]) - np.array([w[1:] for w in want])).max() < 1e-8
+
+
+EXE_STORE = os.path.join(ROOT, "tests", "cpp", "test_dropin_store")
+
+
+def _build_store():
+    cmd = ["g++", "-std=c++14", "-O2", "-I", os.path.join(ROOT, "tests", "cpp", "stubs"), "-I", os.path.join(ROOT, "include"),
+           "-o", EXE_STORE, os.path.join(ROOT, "tests", "cpp", "test_dropin_store.cpp"), "-L",
+           os.path.join(ROOT, "visual-slam_b200", "csrc"), "-lvisnav_b200",
+           "-Wl,-rpath," + os.path.join(ROOT, "visual-slam_b200", "csrc")]
+    subprocess.run(cmd, check=True)
+
+
+def test_keyframe_store_header_compiles_and_fails_loudly_without_gpu():
+    import torch
+    _build_store()
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    p = subprocess.run([EXE_STORE], capture_output=True, text=True)
+    assert p.returncode == 3 and "no usable sm_100 GPU" in p.stdout
+
+
+@pytest.mark.gpu
+def test_keyframe_store_header():
+    """KeyframeStore (include/visnav/keyframe_store_b200.h): keyframes appended one by one (ragged, one empty), the
+    newest matched against all earlier ones in one call == matchDescriptors on the same pairs."""
+    _build_store()
+    p = subprocess.run([EXE_STORE], capture_output=True, text=True)
+    assert p.returncode == 0 and p.stdout.startswith("ok 7 jobs"), p.stdout[-400:] + p.stderr[-400:]
+    assert int(p.stdout.split()[3]) > 1000

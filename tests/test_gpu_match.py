@@ -174,3 +174,22 @@ def test_match_batch_small_batches_both_paths(ctx, oracle_port, split, n_sets):
     finally:
         ctx.set_option(VSLAM_OPT_MATCH_SPLIT_SMALL, 1)
     store.close()
+
+
+def test_desc_store_append(ctx, oracle_port):
+    """vslam_desc_store_append: sets added after creation (buffers grow and move) match like sets given at
+    creation; earlier indices stay valid."""
+    kf = wl.keyframe_descriptors(9, 900, 25)
+    sets = [kf[0][:700], kf[1]]
+    store = DescStore(ctx, sets)
+    for k in range(2, 9):
+        s = kf[k][:900 - 90 * (k % 4)] if k != 5 else kf[k][:0]
+        assert store.append(s) == k
+        sets.append(s)
+        assert len(store) == k + 1
+        jobs = np.array([(k, j) for j in range(k)] + [(0, k)], np.int32)
+        matches, counts = ctx.match_batch(store, jobs, 70, 1.2)
+        for (a, b), m, c in zip(jobs, matches, counts):
+            want = oracle_port.match(sets[a], sets[b], 70, 1.2)
+            assert c == len(want) and np.array_equal(m[:c], want), (k, a, b)
+    store.close()

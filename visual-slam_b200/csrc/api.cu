@@ -941,7 +941,26 @@ struct vslam_desc_store {
   DevBuf desc, offsets, counts;
   int n_sets = 0;
   int max_count = 0;
+  // host mirrors, so that sets can be appended (vslam_desc_store_append) without reading the device back
+  std::vector<int64_t> h_offsets;
+  std::vector<int32_t> h_counts;
+  int64_t total = 0;  // descriptors stored (== the next free slot)
 };
+
+// grow a device buffer to at least `need` bytes keeping its first `keep` bytes
+static cudaError_t grow_preserve(DevBuf& b, size_t need, size_t keep) {
+  if (need <= b.bytes) return cudaSuccess;
+  void* np = nullptr;
+  const size_t want = need * 2 + 256;
+  cudaError_t e = cudaMalloc(&np, want);
+  if (e != cudaSuccess) return e;
+  if (b.p && keep) e = cudaMemcpy(np, b.p, keep, cudaMemcpyDeviceToDevice);
+  if (e != cudaSuccess) { cudaFree(np); return e; }
+  if (b.p) cudaFree(b.p);
+  b.p = np;
+  b.bytes = want;
+  return cudaSuccess;
+}
 
 extern "C" {
 
@@ -971,6 +990,9 @@ int vslam_desc_store_create(vslam_ctx* ctx, const uint32_t* desc, const int64_t*
   vslam_desc_store* s = new (std::nothrow) vslam_desc_store();
   if (!s) return VSLAM_E_CUDA;
   s->ctx = ctx; s->n_sets = n_sets; s->max_count = maxc;
+  s->h_offsets.assign(offsets, offsets + n_sets);
+  s->h_counts.assign(counts, counts + n_sets);
+  s->total = total;
   cudaError_t e = s->desc.reserve((size_t)(total > 0 ? total : 1) * 32);
   if (e == cudaSuccess) e = s->offsets.reserve((size_t)n_sets * 8);
   if (e == cudaSuccess) e = s->counts.reserve((size_t)n_sets * 4);
@@ -985,6 +1007,33 @@ int vslam_desc_store_create(vslam_ctx* ctx, const uint32_t* desc, const int64_t*
   *out = s;
   return VSLAM_OK;
 }
+
+int vslam_desc_store_append(vslam_desc_store* s, const uint32_t* desc, int count, int* set_index) {
+  if (!s) return VSLAM_E_ARG;
+  vslam_ctx* ctx = s->ctx;
+  if (count < 0 || (count > 0 && !desc)) return vs_fail(ctx, VSLAM_E_ARG, "bad append arguments");
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // no matching job may still read the buffers that move
+  const int idx = s->n_sets;
+  VS_CUDA(ctx, grow_preserve(s->desc, (size_t)(s->total + count + 1) * 32, (size_t)s->total * 32));
+  VS_CUDA(ctx, grow_preserve(s->offsets, (size_t)(idx + 1) * 8, (size_t)idx * 8));
+  VS_CUDA(ctx, grow_preserve(s->counts, (size_t)(idx + 1) * 4, (size_t)idx * 4));
+  const int64_t off = s->total;
+  const int32_t cnt = count;
+  if (count > 0)
+    VS_CUDA(ctx, cudaMemcpy(s->desc.as<uint8_t>() + (size_t)off * 32, desc, (size_t)count * 32, cudaMemcpyHostToDevice));
+  VS_CUDA(ctx, cudaMemcpy(s->offsets.as<int64_t>() + idx, &off, 8, cudaMemcpyHostToDevice));
+  VS_CUDA(ctx, cudaMemcpy(s->counts.as<int32_t>() + idx, &cnt, 4, cudaMemcpyHostToDevice));
+  s->h_offsets.push_back(off);
+  s->h_counts.push_back(cnt);
+  s->total += count;
+  s->n_sets = idx + 1;
+  if (count > s->max_count) s->max_count = count;
+  if (set_index) *set_index = idx;
+  return VSLAM_OK;
+}
+
+int vslam_desc_store_size(const vslam_desc_store* s) { return s ? s->n_sets : 0; }
 
 int vslam_match_batch(vslam_ctx* ctx, const vslam_desc_store* s, const int32_t* jobs, int n_jobs, int threshold,
                       double dist_2_best, int32_t* matches, int32_t* n_matches, int cap) {

@@ -38,6 +38,7 @@ ABI_SYMBOLS = [
     "vslam_cam_project", "vslam_cam_unproject", "vslam_find_inliers_essential", "vslam_project_landmarks",
     "vslam_stereo_batch_epipolar", "vslam_stereo_plan_set_epipolar", "vslam_stereo_plan_download_inliers",
     "vslam_stereo_plan_last_epipolar_ms", "vslam_match_shard", "vslam_match_merge_shards", "vslam_set_harris",
+    "vslam_desc_store_append", "vslam_desc_store_size",
 ]
 
 VSLAM_OPT_FP_CONTRACT = 1
@@ -145,6 +146,8 @@ def load_library():
     L.vslam_event_record.argtypes = [vp, i]
     L.vslam_event_elapsed_ms.argtypes = [vp, i, i, C.POINTER(C.c_float)]
     L.vslam_set_harris.argtypes = [vp, i, d]
+    L.vslam_desc_store_append.argtypes = [vp, vp, i, C.POINTER(i)]
+    L.vslam_desc_store_size.argtypes = [vp]
     L.vslam_match_shard.argtypes = [vp, vp, i, vp, i, i, i, d, vp]
     L.vslam_match_merge_shards.argtypes = [vp, vp, i, i, i, d, vp, i, C.POINTER(i)]
     cam = C.POINTER(Camera)
@@ -488,6 +491,17 @@ class DescStore:
         h = C.c_void_p()
         ctx._check(ctx.lib.vslam_desc_store_create(ctx.h, _ptr(flat), _ptr(offsets), _ptr(counts), len(counts), C.byref(h)))
         self.h = h
+
+    def append(self, desc):
+        """Adds one descriptor set (a new keyframe); returns its set index.  Earlier indices stay valid."""
+        d = np.ascontiguousarray(desc, np.uint32).reshape(-1, 8)
+        idx = C.c_int(-1)
+        self.ctx._check(self.ctx.lib.vslam_desc_store_append(self.h, _ptr(d), len(d), C.byref(idx)))
+        self.max_count = max(self.max_count, len(d))
+        return idx.value
+
+    def __len__(self):
+        return int(self.ctx.lib.vslam_desc_store_size(self.h))
 
     def close(self):
         if getattr(self, "h", None):
