@@ -249,6 +249,60 @@ int vslam_stereo_plan_set_epipolar(vslam_stereo_plan* plan, const vslam_epipolar
 int vslam_stereo_plan_download_inliers(vslam_stereo_plan* plan, int count, int32_t* inliers, int32_t* n_inliers);
 int vslam_stereo_plan_last_epipolar_ms(vslam_stereo_plan* plan, float* ms);
 
+/* ---- bag of words: vocabulary transform and BowVector scoring (DBoW2 half) --- */
+/* Replaces DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB> (= visnav::ORBVocabulary, ORBVocabulary.h:13) on
+ * the two calls the reference makes: voc->transform(descriptors, bow_vector, feature_vector, 4)
+ * (keypoints.h:253; TemplatedVocabulary.h:1127-1195, :1218-1260) and voc->score(v1, v2)
+ * (loop_closure_utils.h:119, :201; tracking.h:208; ScoringObject.cpp).  Results are bit-identical to the
+ * reference's: distances are integers, and the double sums are accumulated in the reference's order.
+ * Scoring / weighting values are DBoW2's enums (BowVector.h:35-53). */
+#define VSLAM_BOW_L1_NORM 0
+#define VSLAM_BOW_L2_NORM 1
+#define VSLAM_BOW_CHI_SQUARE 2
+#define VSLAM_BOW_KL 3 /* not provided: VSLAM_E_LIMIT */
+#define VSLAM_BOW_BHATTACHARYYA 4
+#define VSLAM_BOW_DOT_PRODUCT 5
+#define VSLAM_BOW_TF_IDF 0
+#define VSLAM_BOW_TF 1
+#define VSLAM_BOW_IDF 2
+#define VSLAM_BOW_BINARY 3
+typedef struct vslam_bow_vocab vslam_bow_vocab;
+typedef struct vslam_bow_db vslam_bow_db;
+/* Vocabulary from arrays: node i+1 (the root is node 0) has parent[i] (<= i), leaf flag is_leaf[i] (leaves get
+ * word ids in node order), descriptor desc[i][32] (cv::Mat row of cv::ORB = 8 little-endian u32) and weight[i]
+ * -- the fields of one line of the text format. */
+int vslam_bow_vocab_create(vslam_ctx* ctx, int k, int L, int scoring, int weighting, int n_nodes,
+                           const int32_t* parent, const uint8_t* is_leaf, const uint8_t* desc, const double* weight,
+                           vslam_bow_vocab** out);
+/* TemplatedVocabulary::loadFromTextFile (TemplatedVocabulary.h:1338-1425; slam.cpp:373): "k L scoring weighting",
+ * then "parent leaf b0 .. b31 weight" per node.  Blank lines are skipped (the reference turns a trailing newline
+ * into a phantom root child with an uninitialised descriptor). */
+int vslam_bow_vocab_load_text(vslam_ctx* ctx, const char* path, vslam_bow_vocab** out);
+void vslam_bow_vocab_destroy(vslam_bow_vocab* v);
+/* info = {k, L, scoring, weighting, number of nodes incl. the root, number of words} */
+int vslam_bow_vocab_info(const vslam_bow_vocab* v, int32_t info[6]);
+/* transform for `count` images at once: image i owns descriptors [set_begin[i], set_begin[i+1]) of desc
+ * [total][32].  Outputs per image: the BowVector as bow_ids / bow_vals [count][cap] in ascending word id
+ * (std::map order) and n_bow [count]; per feature (all nullable): its word id, the id of the node it passes at
+ * level L - levelsup (0 = root when that level is <= 0) and the word's weight -- feature f belongs to the
+ * FeatureVector entry feat_node[f] iff feat_weight[f] > 0.  At most 8192 features per image. */
+int vslam_bow_transform_batch(vslam_ctx* ctx, vslam_bow_vocab* v, const uint8_t* desc, const int32_t* set_begin,
+                              int count, int levelsup, uint32_t* bow_ids, double* bow_vals, int32_t* n_bow, int cap,
+                              uint32_t* feat_word, uint32_t* feat_node, double* feat_weight);
+/* voc->score(v1, v2); word ids ascend strictly. */
+int vslam_bow_score(vslam_ctx* ctx, vslam_bow_vocab* v, const uint32_t* ids1, const double* vals1, int n1,
+                    const uint32_t* ids2, const double* vals2, int n2, double* score);
+/* The keyframes' BowVectors (Camera::bow_vector, common_types.h:213) kept on the device; a query scores
+ * voc->score(query, entry) against EVERY entry in one launch and also returns the number of shared words
+ * (what detect_loop_candidates / detect_relocalization_candidate count through the inverted file,
+ * loop_closure_utils.h:152-185, tracking.h:176-203). */
+int vslam_bow_db_create(vslam_ctx* ctx, vslam_bow_vocab* v, vslam_bow_db** out);
+void vslam_bow_db_destroy(vslam_bow_db* db);
+int vslam_bow_db_add(vslam_bow_db* db, const uint32_t* ids, const double* vals, int n, int* index);
+int vslam_bow_db_size(const vslam_bow_db* db);
+int vslam_bow_db_query(vslam_ctx* ctx, vslam_bow_db* db, const uint32_t* ids, const double* vals, int n,
+                       double* scores, int32_t* n_common);
+
 /* ---- measurement helpers --------------------------------------------------------------- */
 /* CUDA events on vslam_stream(ctx): record event `slot` (0..3); elapsed ms between two recorded
  * slots (synchronises on the later one). */

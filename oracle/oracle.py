@@ -346,3 +346,155 @@ def load_ref():
     if not os.path.exists(path):
         return None
     return Oracle(C.CDLL(path), "reference")
+
+
+# --- bag of words (SURVEY 8f-4, DBoW2 half) ------------------------------------------------------------------
+def _as_u8(a):
+    return a.ctypes.data_as(C.POINTER(C.c_uint8))
+
+
+def _as_u32(a):
+    return a.ctypes.data_as(C.POINTER(C.c_uint32))
+
+
+def _as_f64(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _desc_bytes(desc):
+    """[n][32] u8 view of descriptors given as [n][8] u32 (little endian) or [n][32] u8."""
+    d = np.ascontiguousarray(desc)
+    if d.dtype == np.uint32:
+        d = d.view(np.uint8)
+    return np.ascontiguousarray(d, np.uint8).reshape(-1, 32)
+
+
+class BowVocab:
+    """The C restatement (visnav_oracle_bow.c) of TemplatedVocabulary<FORB>: transform and score."""
+    kind = "port"
+
+    def __init__(self, lib, handle):
+        self.lib, self.h = lib, handle
+        info = np.zeros(6, np.int32)
+        lib.vso_bow_vocab_info(C.c_void_p(handle), info.ctypes.data_as(C.POINTER(C.c_int32)))
+        self.k, self.L, self.scoring, self.weighting, self.n_nodes, self.n_words = (int(x) for x in info)
+
+    @classmethod
+    def _lib(cls):
+        lib = load_oracle().lib
+        lib.vso_bow_vocab_create.restype = C.c_void_p
+        lib.vso_bow_vocab_load_text.restype = C.c_void_p
+        lib.vso_bow_score.restype = C.c_double
+        return lib
+
+    @classmethod
+    def from_text(cls, path):
+        lib = cls._lib()
+        h = lib.vso_bow_vocab_load_text(path.encode())
+        if not h:
+            raise ValueError("not a vocabulary text file: %s" % path)
+        return cls(lib, h)
+
+    @classmethod
+    def from_arrays(cls, k, L, scoring, weighting, parent, is_leaf, desc, weight):
+        lib = cls._lib()
+        parent = np.ascontiguousarray(parent, np.int32)
+        is_leaf = np.ascontiguousarray(is_leaf, np.uint8)
+        desc = _desc_bytes(desc)
+        weight = np.ascontiguousarray(weight, np.float64)
+        h = lib.vso_bow_vocab_create(k, L, scoring, weighting, len(parent), parent.ctypes.data_as(C.POINTER(C.c_int32)),
+                                     _as_u8(is_leaf), _as_u8(desc), _as_f64(weight))
+        if not h:
+            raise ValueError("bad vocabulary arrays")
+        return cls(lib, h)
+
+    def close(self):
+        if self.h:
+            self.lib.vso_bow_vocab_free(C.c_void_p(self.h))
+            self.h = None
+
+    def transform(self, desc, levelsup=4):
+        """-> ids [m] u32 ascending, vals [m] f64, feat_word [n], feat_node [n], feat_weight [n]."""
+        d = _desc_bytes(desc)
+        n = len(d)
+        ids = np.zeros(max(n, 1), np.uint32)
+        vals = np.zeros(max(n, 1), np.float64)
+        fw = np.zeros(max(n, 1), np.uint32)
+        fn = np.zeros(max(n, 1), np.uint32)
+        fwt = np.zeros(max(n, 1), np.float64)
+        m = self.lib.vso_bow_transform(C.c_void_p(self.h), _as_u8(d), n, levelsup, _as_u32(ids), _as_f64(vals), _as_u32(fw), _as_u32(fn),
+                                       _as_f64(fwt))
+        return ids[:m].copy(), vals[:m].copy(), fw[:n].copy(), fn[:n].copy(), fwt[:n].copy()
+
+    def score(self, v1, v2):
+        i1, x1 = np.ascontiguousarray(v1[0], np.uint32), np.ascontiguousarray(v1[1], np.float64)
+        i2, x2 = np.ascontiguousarray(v2[0], np.uint32), np.ascontiguousarray(v2[1], np.float64)
+        return float(self.lib.vso_bow_score(self.scoring, _as_u32(i1), _as_f64(x1), len(i1), _as_u32(i2), _as_f64(x2), len(i2)))
+
+
+class BowVocabRef:
+    """The reference's own DBoW2 (oracle/_ref/libvisnav_ref_bow.so)."""
+    kind = "reference"
+
+    def __init__(self, lib, handle):
+        self.lib, self.h = lib, handle
+        info = np.zeros(6, np.int32)
+        lib.vref_bow_info(C.c_void_p(handle), info.ctypes.data_as(C.POINTER(C.c_int32)))
+        self.k, self.L, self.scoring, self.weighting, _, self.n_words = (int(x) for x in info)
+
+    @staticmethod
+    def lib():
+        path = os.path.join(_HERE, "_ref", "libvisnav_ref_bow.so")
+        if not os.path.exists(path):
+            return None
+        lib = C.CDLL(path)
+        lib.vref_bow_load_text.restype = C.c_void_p
+        lib.vref_bow_score.restype = C.c_double
+        return lib
+
+    @classmethod
+    def from_text(cls, path):
+        lib = cls.lib()
+        if lib is None:
+            return None
+        h = lib.vref_bow_load_text(path.encode())
+        if not h:
+            raise ValueError("the reference rejected %s" % path)
+        return cls(lib, h)
+
+    @classmethod
+    def create_save(cls, training_sets, k, L, weighting, scoring, path):
+        """TemplatedVocabulary::create (k-means++ tree) on the training descriptor sets + saveToTextFile."""
+        lib = cls.lib()
+        sets = [_desc_bytes(s) for s in training_sets]
+        begin = np.zeros(len(sets) + 1, np.int32)
+        begin[1:] = np.cumsum([len(s) for s in sets])
+        d = np.ascontiguousarray(np.concatenate(sets))
+        return int(lib.vref_bow_create_save(_as_u8(d), begin.ctypes.data_as(C.POINTER(C.c_int32)), len(sets), k, L, weighting,
+                                            scoring, path.encode()))
+
+    def close(self):
+        if self.h:
+            self.lib.vref_bow_free(C.c_void_p(self.h))
+            self.h = None
+
+    def transform(self, desc, levelsup=4):
+        """-> ids, vals, fv_node [n] (0xFFFFFFFF where the feature was stopped)."""
+        d = _desc_bytes(desc)
+        n = len(d)
+        ids = np.zeros(max(n, 1), np.uint32)
+        vals = np.zeros(max(n, 1), np.float64)
+        fv = np.zeros(max(n, 1), np.uint32)
+        m = self.lib.vref_bow_transform(C.c_void_p(self.h), _as_u8(d), n, levelsup, _as_u32(ids), _as_f64(vals), _as_u32(fv))
+        return ids[:m].copy(), vals[:m].copy(), fv[:n].copy()
+
+    def words(self, desc):
+        d = _desc_bytes(desc)
+        w = np.zeros(max(len(d), 1), np.uint32)
+        self.lib.vref_bow_words(C.c_void_p(self.h), _as_u8(d), len(d), _as_u32(w))
+        return w[:len(d)].copy()
+
+    def score(self, v1, v2):
+        i1, x1 = np.ascontiguousarray(v1[0], np.uint32), np.ascontiguousarray(v1[1], np.float64)
+        i2, x2 = np.ascontiguousarray(v2[0], np.uint32), np.ascontiguousarray(v2[1], np.float64)
+        return float(self.lib.vref_bow_score(C.c_void_p(self.h), _as_u32(i1), _as_f64(x1), len(i1), _as_u32(i2), _as_f64(x2), len(i2)))

@@ -171,8 +171,49 @@ def euroc():
           np.array_equal(rec["corners_unopt_r"], rec["corners_default_r"]))
 
 
+def bow():
+    """Bag of words by the reference's own DBoW2 (oracle/_ref/libvisnav_ref_bow.so): a vocabulary built by
+    TemplatedVocabulary::create (hierarchical k-means++, k = 5, L = 3) on synthetic training descriptors and written
+    by saveToTextFile (its trailing newline removed -- see vslam_bow_vocab_load_text), then, per scoring type, the
+    BowVectors / FeatureVector nodes of four feature sets (levelsup 2 and 4) and all pairwise scores."""
+    import oracle.oracle as oo
+    path = os.path.join(OUT, "bow_vocab.txt")
+    base = wl.random_descriptors(3000, 3)
+    rng = np.random.default_rng(4)
+    training = [wl.flip_bits(base[rng.integers(0, 3000, 80)], 30, rng) for _ in range(60)]
+    n_words = oo.BowVocabRef.create_save(training, 5, 3, 0, 0, path)
+    txt = open(path).read().rstrip("\n")
+    open(path, "w").write(txt)
+    sets = [wl.flip_bits(base[rng.integers(0, 3000, n)], 34, rng) for n in (500, 431, 64, 1)]
+    rec = {"n_words": n_words, "set_sizes": np.array([len(s) for s in sets])}
+    for i, s_ in enumerate(sets):
+        rec["set%d" % i] = s_
+    lines = txt.split("\n")
+    for scoring in (0, 1, 2, 4, 5):
+        for weighting in (0, 1, 2, 3):
+            tmp = os.path.join("/tmp", "bow_vocab_%d_%d.txt" % (scoring, weighting))
+            k_, l_ = lines[0].split()[:2]
+            open(tmp, "w").write("\n".join(["%s %s %d %d" % (k_, l_, scoring, weighting)] + lines[1:]))
+            r = oo.BowVocabRef.from_text(tmp)
+            vecs = []
+            for i, s_ in enumerate(sets):
+                for lu in (2, 4):
+                    ids, vals, fv = r.transform(s_, lu)
+                    key = "s%d_w%d_set%d_l%d_" % (scoring, weighting, i, lu)
+                    rec[key + "ids"], rec[key + "vals"], rec[key + "fv"] = ids, vals, fv
+                vecs.append((ids, vals))
+                if scoring == 0 and weighting == 0:
+                    rec["words_set%d" % i] = r.words(s_)
+            rec["s%d_w%d_scores" % (scoring, weighting)] = np.array([[r.score(a, b) for b in vecs] for a in vecs])
+            r.close()
+    np.savez_compressed(os.path.join(OUT, "bow.npz"), **rec)
+    print("bow: words", n_words, "vector sizes", [len(rec["s0_w0_set%d_l4_ids" % i]) for i in range(4)])
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "landmarks":
+    if len(sys.argv) > 1 and sys.argv[1] == "bow":
+        bow()
+    elif len(sys.argv) > 1 and sys.argv[1] == "landmarks":
         landmarks()
     elif len(sys.argv) > 1 and sys.argv[1] == "geometry":
         geometry()
@@ -186,3 +227,4 @@ if __name__ == "__main__":
         geometry()
         euroc()
         harris()
+        bow()

@@ -39,6 +39,9 @@ ABI_SYMBOLS = [
     "vslam_stereo_batch_epipolar", "vslam_stereo_plan_set_epipolar", "vslam_stereo_plan_download_inliers",
     "vslam_stereo_plan_last_epipolar_ms", "vslam_match_shard", "vslam_match_merge_shards", "vslam_set_harris",
     "vslam_desc_store_append", "vslam_desc_store_size",
+    "vslam_bow_vocab_create", "vslam_bow_vocab_load_text", "vslam_bow_vocab_destroy", "vslam_bow_vocab_info",
+    "vslam_bow_transform_batch", "vslam_bow_score", "vslam_bow_db_create", "vslam_bow_db_destroy", "vslam_bow_db_add",
+    "vslam_bow_db_size", "vslam_bow_db_query",
 ]
 
 VSLAM_OPT_FP_CONTRACT = 1
@@ -160,6 +163,19 @@ def load_library():
     L.vslam_stereo_plan_set_epipolar.argtypes = [vp, C.POINTER(Epipolar)]
     L.vslam_stereo_plan_download_inliers.argtypes = [vp, i, vp, vp]
     L.vslam_stereo_plan_last_epipolar_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    L.vslam_bow_vocab_create.argtypes = [vp, i, i, i, i, i, vp, vp, vp, vp, C.POINTER(vp)]
+    L.vslam_bow_vocab_load_text.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
+    L.vslam_bow_vocab_destroy.argtypes = [vp]
+    L.vslam_bow_vocab_destroy.restype = None
+    L.vslam_bow_vocab_info.argtypes = [vp, vp]
+    L.vslam_bow_transform_batch.argtypes = [vp, vp, vp, vp, i, i, vp, vp, vp, i, vp, vp, vp]
+    L.vslam_bow_score.argtypes = [vp, vp, vp, vp, i, vp, vp, i, C.POINTER(d)]
+    L.vslam_bow_db_create.argtypes = [vp, vp, C.POINTER(vp)]
+    L.vslam_bow_db_destroy.argtypes = [vp]
+    L.vslam_bow_db_destroy.restype = None
+    L.vslam_bow_db_add.argtypes = [vp, vp, vp, i, C.POINTER(i)]
+    L.vslam_bow_db_size.argtypes = [vp]
+    L.vslam_bow_db_query.argtypes = [vp, vp, vp, vp, i, vp, vp]
     _lib = L
     return L
 
@@ -506,6 +522,140 @@ class DescStore:
     def close(self):
         if getattr(self, "h", None):
             self.ctx.lib.vslam_desc_store_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+BOW_SCORING = {"L1_NORM": 0, "L2_NORM": 1, "CHI_SQUARE": 2, "KL": 3, "BHATTACHARYYA": 4, "DOT_PRODUCT": 5}
+BOW_WEIGHTING = {"TF_IDF": 0, "TF": 1, "IDF": 2, "BINARY": 3}
+
+
+def _desc_bytes(desc):
+    """[n][32] u8 view of descriptors given as [n][8] u32 (little endian) or [n][32] u8 (cv::ORB rows)."""
+    d = np.ascontiguousarray(desc)
+    if d.dtype == np.uint32:
+        d = d.view(np.uint8)
+    return np.ascontiguousarray(d, np.uint8).reshape(-1, 32)
+
+
+class BowVocabulary:
+    """visnav::ORBVocabulary (ORBVocabulary.h:13 = DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB>) on the
+    device: transform() and score() as the reference calls them (keypoints.h:253, loop_closure_utils.h:119)."""
+
+    def __init__(self, ctx, handle):
+        self.ctx, self.h = ctx, handle
+        info = np.zeros(6, np.int32)
+        ctx.lib.vslam_bow_vocab_info(handle, _ptr(info))
+        self.k, self.L, self.scoring, self.weighting, self.n_nodes, self.n_words = (int(x) for x in info)
+
+    @classmethod
+    def load_text(cls, ctx, path):
+        """TemplatedVocabulary::loadFromTextFile (slam.cpp:373)."""
+        h = C.c_void_p()
+        ctx._check(ctx.lib.vslam_bow_vocab_load_text(ctx.h, str(path).encode(), C.byref(h)))
+        return cls(ctx, h)
+
+    @classmethod
+    def from_arrays(cls, ctx, k, L, scoring, weighting, parent, is_leaf, desc, weight):
+        parent = np.ascontiguousarray(parent, np.int32)
+        is_leaf = np.ascontiguousarray(is_leaf, np.uint8)
+        desc = _desc_bytes(desc)
+        weight = np.ascontiguousarray(weight, np.float64)
+        assert len(is_leaf) == len(parent) == len(desc) == len(weight)
+        h = C.c_void_p()
+        ctx._check(ctx.lib.vslam_bow_vocab_create(ctx.h, int(k), int(L), int(scoring), int(weighting), len(parent),
+                                                  _ptr(parent), _ptr(is_leaf), _ptr(desc), _ptr(weight), C.byref(h)))
+        return cls(ctx, h)
+
+    def transform_batch(self, desc_sets, levelsup=4, cap=None):
+        """voc->transform(features, bow_vector, feature_vector, levelsup) for a list of descriptor sets.
+        -> list of (ids u32 ascending, vals f64) per image, and feat_word, feat_node, feat_weight (flat, per feature;
+        feature f is in FeatureVector[feat_node[f]] iff feat_weight[f] > 0) with set_begin."""
+        sets = [_desc_bytes(s) for s in desc_sets]
+        begin = np.zeros(len(sets) + 1, np.int32)
+        if sets:
+            begin[1:] = np.cumsum([len(s) for s in sets])
+        total = int(begin[-1])
+        flat = np.ascontiguousarray(np.concatenate(sets)) if total else np.zeros((0, 32), np.uint8)
+        if cap is None:
+            cap = max(1, max((len(s) for s in sets), default=1))
+        n = len(sets)
+        ids = np.zeros((max(n, 1), cap), np.uint32)
+        vals = np.zeros((max(n, 1), cap), np.float64)
+        n_bow = np.zeros(max(n, 1), np.int32)
+        fw = np.zeros(max(total, 1), np.uint32)
+        fn = np.zeros(max(total, 1), np.uint32)
+        fwt = np.zeros(max(total, 1), np.float64)
+        self.ctx._check(self.ctx.lib.vslam_bow_transform_batch(self.ctx.h, self.h, _ptr(flat), _ptr(begin), n, int(levelsup),
+                                                               _ptr(ids), _ptr(vals), _ptr(n_bow), cap, _ptr(fw), _ptr(fn),
+                                                               _ptr(fwt)))
+        vecs = [(ids[i, :n_bow[i]].copy(), vals[i, :n_bow[i]].copy()) for i in range(n)]
+        return vecs, fw[:total], fn[:total], fwt[:total], begin
+
+    def transform(self, desc, levelsup=4):
+        """One image: (ids, vals), FeatureVector as {node id: [feature indices]} (FeatureVector.cpp:28-42)."""
+        vecs, fw, fn, fwt, _ = self.transform_batch([desc], levelsup)
+        fv = {}
+        for f in np.nonzero(fwt > 0)[0]:
+            fv.setdefault(int(fn[f]), []).append(int(f))
+        return vecs[0], dict(sorted(fv.items()))
+
+    def score(self, v1, v2):
+        i1, x1 = np.ascontiguousarray(v1[0], np.uint32), np.ascontiguousarray(v1[1], np.float64)
+        i2, x2 = np.ascontiguousarray(v2[0], np.uint32), np.ascontiguousarray(v2[1], np.float64)
+        out = C.c_double(0.0)
+        self.ctx._check(self.ctx.lib.vslam_bow_score(self.ctx.h, self.h, _ptr(i1), _ptr(x1), len(i1), _ptr(i2), _ptr(x2),
+                                                     len(i2), C.byref(out)))
+        return out.value
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.ctx.lib.vslam_bow_vocab_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class BowDatabase:
+    """The keyframes' BowVectors on the device; query() = voc->score(query, entry) for every entry plus the number
+    of shared words (loop_closure_utils.h:152-201, tracking.h:176-208)."""
+
+    def __init__(self, ctx, voc):
+        self.ctx, self.voc = ctx, voc
+        h = C.c_void_p()
+        ctx._check(ctx.lib.vslam_bow_db_create(ctx.h, voc.h, C.byref(h)))
+        self.h = h
+
+    def add(self, vec):
+        ids, vals = np.ascontiguousarray(vec[0], np.uint32), np.ascontiguousarray(vec[1], np.float64)
+        idx = C.c_int(-1)
+        self.ctx._check(self.ctx.lib.vslam_bow_db_add(self.h, _ptr(ids), _ptr(vals), len(ids), C.byref(idx)))
+        return idx.value
+
+    def __len__(self):
+        return int(self.ctx.lib.vslam_bow_db_size(self.h))
+
+    def query(self, vec):
+        ids, vals = np.ascontiguousarray(vec[0], np.uint32), np.ascontiguousarray(vec[1], np.float64)
+        n = len(self)
+        scores = np.zeros(max(n, 1), np.float64)
+        common = np.zeros(max(n, 1), np.int32)
+        self.ctx._check(self.ctx.lib.vslam_bow_db_query(self.ctx.h, self.h, _ptr(ids), _ptr(vals), len(ids), _ptr(scores),
+                                                        _ptr(common)))
+        return scores[:n], common[:n]
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.ctx.lib.vslam_bow_db_destroy(self.h)
             self.h = None
 
     def __del__(self):
