@@ -303,6 +303,33 @@ int vslam_bow_db_size(const vslam_bow_db* db);
 int vslam_bow_db_query(vslam_ctx* ctx, vslam_bow_db* db, const uint32_t* ids, const double* vals, int n,
                        double* scores, int32_t* n_common);
 
+/* ---- cv::ORB front end of the bag-of-words path (ORB half) ------------------- */
+/* Replaces orb->detectAndCompute(img, cv::Mat(), keypoints, descriptors) of visnav::compute_bow_vector
+ * (keypoints.h:249-250) with orb = cv::ORB::create(nfeatures, scale_factor, nlevels, edge_threshold, 0, 2,
+ * cv::ORB::FAST_SCORE) (patchSize 31, fast_threshold 20 by default), for `count` images of one size at once.
+ * kp [count][cap][6] = cv::KeyPoint {pt.x, pt.y, size, angle, response, octave}; desc [count][cap][32]; n_kp [count].
+ * Level by level; inside a level in raster order (the reference's order there is std::nth_element's: unspecified).
+ * Ties at a level's cut-off score all stay (KeyPointsFilter::retainBest), so n_kp may exceed nfeatures: give cap
+ * some room (VSLAM_E_CAPACITY otherwise). */
+typedef struct {
+  int nfeatures;
+  float scale_factor; /* 1.2f */
+  int nlevels;        /* 8; at most 8 */
+  int edge_threshold; /* 19 */
+  int fast_threshold; /* 20 */
+} vslam_orb_params;
+int vslam_orb_detect_compute_batch(vslam_ctx* ctx, const uint8_t* images, int count, int w, int h, int pitch,
+                                   size_t image_stride, const vslam_orb_params* prm, float* kp, uint8_t* desc,
+                                   int32_t* n_kp, int cap);
+/* visnav::compute_bow_vector (keypoints.h:243-254) for `count` images: ORB as above, then
+ * voc->transform(descriptors, bow_vector, feature_vector, levelsup) -- the descriptors never leave the device.
+ * BowVector outputs as vslam_bow_transform_batch; kp / desc / n_kp / feat_node / feat_weight (all nullable) give the
+ * keypoints and, per keypoint, its FeatureVector node and word weight ([count][cap] each). */
+int vslam_compute_bow_vector_batch(vslam_ctx* ctx, vslam_bow_vocab* v, const uint8_t* images, int count, int w, int h,
+                                   int pitch, size_t image_stride, const vslam_orb_params* prm, int levelsup,
+                                   uint32_t* bow_ids, double* bow_vals, int32_t* n_bow, int bow_cap, float* kp,
+                                   uint8_t* desc, int32_t* n_kp, uint32_t* feat_node, double* feat_weight, int cap);
+
 /* ---- measurement helpers --------------------------------------------------------------- */
 /* CUDA events on vslam_stream(ctx): record event `slot` (0..3); elapsed ms between two recorded
  * slots (synchronises on the later one). */

@@ -498,3 +498,34 @@ class BowVocabRef:
         i1, x1 = np.ascontiguousarray(v1[0], np.uint32), np.ascontiguousarray(v1[1], np.float64)
         i2, x2 = np.ascontiguousarray(v2[0], np.uint32), np.ascontiguousarray(v2[1], np.float64)
         return float(self.lib.vref_bow_score(C.c_void_p(self.h), _as_u32(i1), _as_f64(x1), len(i1), _as_u32(i2), _as_f64(x2), len(i2)))
+
+
+# --- cv::ORB as compute_bow_vector configures it (ORB half) -----------------------------------------------
+def gaussian_kernel7():
+    """getGaussianKernel(7, 2, CV_32F): exp(-x^2 / (2 sigma^2)) normalised in double, rounded to float."""
+    x = np.arange(-3, 4, dtype=np.float64)
+    k = np.exp(-(x * x) / 8.0)
+    return (k / k.sum()).astype(np.float32)
+
+
+def orb_detect_compute(img, nfeatures=1500, nlevels=8, scale_factor=1.2, edge_threshold=19, fast_threshold=20, fused=1):
+    """The C restatement (visnav_oracle_orb.c) of cv::ORB::create(nfeatures, 1.2f, 8, 19, 0, 2, FAST_SCORE)
+    ->detectAndCompute.  -> kp [n, 6] float32 (x, y, size, angle, response, octave), desc [n, 32] uint8; level by
+    level, raster order inside a level."""
+    lib = load_oracle().lib
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    f = lib.vso_orb_detect_compute
+    f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_void_p,
+                  C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    f.restype = C.c_int
+    k7 = gaussian_kernel7()
+    cap = nfeatures * 2 + 4096
+    while True:
+        kp = np.zeros((cap, 6), np.float32)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = f(img.ctypes.data, w, h, w, nfeatures, nlevels, float(np.float32(scale_factor)), edge_threshold,
+              fast_threshold, k7.ctypes.data, fused, kp.ctypes.data, desc.ctypes.data, cap, None)
+        if n <= cap:
+            return kp[:n].copy(), desc[:n].copy()
+        cap = n

@@ -210,8 +210,29 @@ def bow():
     print("bow: words", n_words, "vector sizes", [len(rec["s0_w0_set%d_l4_ids" % i]) for i in range(4)])
 
 
+def orb():
+    """cv::ORB as visnav::compute_bow_vector configures it (keypoints.h:249), by cv2 itself: keypoints and descriptors
+    of a synthetic image (workloads.synth_image(1234), not stored) and of the real EuRoC image already in
+    euroc_pair.npz, for 1500 and 300 features; sorted by (octave, y, x) -- the reference's order inside a level is
+    std::nth_element's.  Also the Gaussian kernel and one blurred image (the float separable filter)."""
+    rec = {"k7": cv2.getGaussianKernel(7, 2, cv2.CV_32F).ravel().astype(np.float32)}
+    imgs = {"synth": wl.synth_image(1234, 752, 480), "euroc": np.load(os.path.join(OUT, "euroc_pair.npz"))["img_l"]}
+    for name, img in imgs.items():
+        for nf in (1500, 300):
+            o = cv2.ORB_create(nf, 1.2, 8, 19, 0, 2, cv2.ORB_FAST_SCORE)
+            kps, d = o.detectAndCompute(img, None)
+            order = sorted(range(len(kps)), key=lambda i: (kps[i].octave, kps[i].pt[1], kps[i].pt[0]))
+            rec["%s_%d_kp" % (name, nf)] = np.array([[kps[i].pt[0], kps[i].pt[1], kps[i].size, kps[i].angle, kps[i].response,
+                                                      kps[i].octave] for i in order], np.float32)
+            rec["%s_%d_desc" % (name, nf)] = d[order]
+            print("orb", name, nf, len(kps))
+    np.savez_compressed(os.path.join(OUT, "orb.npz"), **rec)
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "bow":
+    if len(sys.argv) > 1 and sys.argv[1] == "orb":
+        orb()
+    elif len(sys.argv) > 1 and sys.argv[1] == "bow":
         bow()
     elif len(sys.argv) > 1 and sys.argv[1] == "landmarks":
         landmarks()
@@ -228,3 +249,4 @@ if __name__ == "__main__":
         euroc()
         harris()
         bow()
+        orb()

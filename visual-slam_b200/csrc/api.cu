@@ -115,6 +115,7 @@ void vslam_destroy(vslam_ctx* ctx) {
                     &ctx->imgmax, &ctx->selws, &ctx->d1, &ctx->d2, &ctx->pairs, &ctx->mcnt, &ctx->rowpart,
                     &ctx->colstat, &ctx->jobs, &ctx->lm, &ctx->pyr, &ctx->geo};
   for (DevBuf* b : bufs) b->release();
+  for (DevBuf& b : ctx->orb) b.release();
   for (int i = 0; i < 8; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
   for (int i = 0; i < 2; ++i)

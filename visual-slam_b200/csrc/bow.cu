@@ -73,6 +73,8 @@ struct DescendParams {
   int nid_level;  // L - levelsup
   const uint4* feat;  // [n] x 2 uint4
   int n;
+  const int32_t* counts;  // nullable: features are [image][cap] slots, image i holds counts[i] of them
+  int cap;
   uint32_t* word;   // [n]
   uint32_t* node;   // [n]
   double* weight;   // [n]
@@ -82,6 +84,7 @@ __global__ void __launch_bounds__(256) bow_descend_kernel(const DescendParams p)
   const int lane = threadIdx.x & 31;
   const int f = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (f >= p.n) return;
+  if (p.counts && f % p.cap >= p.counts[f / p.cap]) return;
   const uint4 a0 = __ldg(p.feat + 2 * (size_t)f), a1 = __ldg(p.feat + 2 * (size_t)f + 1);
   int begin = 0, count = p.root_children;
   int level = 0;
@@ -117,7 +120,9 @@ __global__ void __launch_bounds__(256) bow_descend_kernel(const DescendParams p)
 struct BowVecParams {
   const uint32_t* word;    // [total] per feature
   const double* weight;    // [total]
-  const int32_t* set_begin;  // [count + 1]
+  const int32_t* set_begin;  // [count + 1], or nullptr: image i owns features [i * feat_cap, i * feat_cap + counts[i])
+  const int32_t* counts;
+  int feat_cap;
   const double* word_weight;
   int weighting, must_normalize, norm_l2;
   uint32_t* ids;   // [count][cap]
@@ -151,8 +156,8 @@ __global__ void __launch_bounds__(kBowThreads) bow_vector_kernel(const BowVecPar
   __shared__ int s_total;
   __shared__ double s_norm;
   const int img = blockIdx.x;
-  const int f0 = p.set_begin[img];
-  const int n = p.set_begin[img + 1] - f0;
+  const int f0 = p.set_begin ? p.set_begin[img] : img * p.feat_cap;
+  const int n = p.set_begin ? p.set_begin[img + 1] - f0 : min(p.counts[img], p.feat_cap);
   int np2 = 32;
   while (np2 < n) np2 <<= 1;
   uint32_t* keys = reinterpret_cast<uint32_t*>(smem_raw);
@@ -529,6 +534,8 @@ int vslam_bow_transform_batch(vslam_ctx* ctx, vslam_bow_vocab* v, const uint8_t*
     dp.nid_level = v->L - levelsup;
     dp.feat = reinterpret_cast<const uint4*>(in);
     dp.n = total;
+    dp.counts = nullptr;
+    dp.cap = 0;
     dp.word = reinterpret_cast<uint32_t*>(feat);
     dp.node = reinterpret_cast<uint32_t*>(feat + o_node);
     dp.weight = reinterpret_cast<double*>(feat + o_w);
@@ -540,6 +547,8 @@ int vslam_bow_transform_batch(vslam_ctx* ctx, vslam_bow_vocab* v, const uint8_t*
   bp.word = reinterpret_cast<const uint32_t*>(feat);
   bp.weight = reinterpret_cast<const double*>(feat + o_w);
   bp.set_begin = reinterpret_cast<const int32_t*>(in + o_begin);
+  bp.counts = nullptr;
+  bp.feat_cap = 0;
   bp.word_weight = v->word_weight.as<double>();
   bp.weighting = v->weighting;
   bp.must_normalize = must_normalize(v->scoring);
@@ -562,6 +571,92 @@ int vslam_bow_transform_batch(vslam_ctx* ctx, vslam_bow_vocab* v, const uint8_t*
   VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   for (int i = 0; i < count; ++i)
     if (n_bow[i] > cap) return vs_fail(ctx, VSLAM_E_CAPACITY, "BowVector capacity too small");
+  return VSLAM_OK;
+}
+
+// visnav::compute_bow_vector (keypoints.h:243-254) for a batch: ORB (orb.cu) -> descent -> BowVector, all on the device
+int vslam_compute_bow_vector_batch(vslam_ctx* ctx, vslam_bow_vocab* v, const uint8_t* images, int count, int w, int h,
+                                   int pitch, size_t image_stride, const vslam_orb_params* prm, int levelsup,
+                                   uint32_t* bow_ids, double* bow_vals, int32_t* n_bow, int bow_cap, float* kp,
+                                   uint8_t* desc, int32_t* n_kp, uint32_t* feat_node, double* feat_weight, int cap) {
+  if (!ctx) return VSLAM_E_ARG;
+  if (!v || v->ctx != ctx || !images || !prm || count < 0 || w <= 0 || h <= 0 || pitch < w || cap <= 0 || bow_cap <= 0 ||
+      image_stride < (size_t)pitch * (h - 1) + w || (count > 0 && (!bow_ids || !bow_vals || !n_bow)))
+    return vs_fail(ctx, VSLAM_E_ARG, "bad compute_bow_vector arguments");
+  if (cap > kMaxFeatures) return vs_fail(ctx, VSLAM_E_LIMIT, "more than 8192 features in one image");
+  if (count == 0) return VSLAM_OK;
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t bytes = image_stride * (size_t)(count - 1) + (size_t)pitch * (h - 1) + w;
+  VS_CUDA(ctx, ctx->orb[6].reserve(bytes + 64));
+  VS_CUDA(ctx, cudaMemcpyAsync(ctx->orb[6].p, images, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  OrbDeviceOut o;
+  int rc = launch_orb(ctx, ctx->orb[6].as<uint8_t>(), count, w, h, pitch, image_stride, prm, cap, &o);
+  if (rc) return rc;
+  const int total = count * cap;
+  const size_t o_node = up256((size_t)total * 4), o_w = o_node + up256((size_t)total * 4);
+  VS_CUDA(ctx, v->feat.reserve(o_w + (size_t)total * 8 + 8));
+  const size_t o_vals = up256((size_t)count * bow_cap * 4);
+  VS_CUDA(ctx, v->bow.reserve(o_vals + (size_t)count * bow_cap * 8));
+  VS_CUDA(ctx, v->cnt.reserve((size_t)count * 4));
+  uint8_t* feat = v->feat.as<uint8_t>();
+  uint8_t* bow = v->bow.as<uint8_t>();
+  const bool empty = v->n_words == 0;  // empty(): transform clears both vectors
+  if (!empty) {
+    VS_CUDA(ctx, cudaMemsetAsync(feat, 0, o_w + (size_t)total * 8, ctx->stream));
+    DescendParams dp;
+    dp.slot_desc = v->slot_desc.as<uint4>();
+    dp.slot_info = v->slot_info.as<int4>();
+    dp.slot_weight = v->slot_weight.as<double>();
+    dp.root_children = v->root_children;
+    dp.nid_level = v->L - levelsup;
+    dp.feat = reinterpret_cast<const uint4*>(o.desc);
+    dp.n = total;
+    dp.counts = o.n_kp;
+    dp.cap = cap;
+    dp.word = reinterpret_cast<uint32_t*>(feat);
+    dp.node = reinterpret_cast<uint32_t*>(feat + o_node);
+    dp.weight = reinterpret_cast<double*>(feat + o_w);
+    bow_descend_kernel<<<(total + 7) / 8, 256, 0, ctx->stream>>>(dp);
+    BowVecParams bp;
+    bp.word = dp.word;
+    bp.weight = dp.weight;
+    bp.set_begin = nullptr;
+    bp.counts = o.n_kp;
+    bp.feat_cap = cap;
+    bp.word_weight = v->word_weight.as<double>();
+    bp.weighting = v->weighting;
+    bp.must_normalize = must_normalize(v->scoring);
+    bp.norm_l2 = norm_is_l2(v->scoring);
+    bp.ids = reinterpret_cast<uint32_t*>(bow);
+    bp.vals = reinterpret_cast<double*>(bow + o_vals);
+    bp.n_out = v->cnt.as<int32_t>();
+    bp.cap = bow_cap;
+    int np2 = 32;
+    while (np2 < cap) np2 <<= 1;
+    bow_vector_kernel<<<count, kBowThreads, (size_t)np2 * 4, ctx->stream>>>(bp);
+    ctx->launches += 2;
+    VS_CUDA(ctx, cudaGetLastError());
+    VS_CUDA(ctx, cudaMemcpyAsync(n_bow, v->cnt.p, (size_t)count * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaMemcpyAsync(bow_ids, bow, (size_t)count * bow_cap * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaMemcpyAsync(bow_vals, bow + o_vals, (size_t)count * bow_cap * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (feat_node) VS_CUDA(ctx, cudaMemcpyAsync(feat_node, feat + o_node, (size_t)total * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (feat_weight) VS_CUDA(ctx, cudaMemcpyAsync(feat_weight, feat + o_w, (size_t)total * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  } else {
+    for (int i = 0; i < count; ++i) n_bow[i] = 0;
+    if (feat_node) memset(feat_node, 0, (size_t)total * 4);
+    if (feat_weight) memset(feat_weight, 0, (size_t)total * 8);
+  }
+  std::vector<int32_t> status((size_t)count), counts((size_t)count);
+  VS_CUDA(ctx, cudaMemcpyAsync(counts.data(), o.n_kp, (size_t)count * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  VS_CUDA(ctx, cudaMemcpyAsync(status.data(), o.status, (size_t)count * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (kp) VS_CUDA(ctx, cudaMemcpyAsync(kp, o.kp, (size_t)total * 24, cudaMemcpyDeviceToHost, ctx->stream));
+  if (desc) VS_CUDA(ctx, cudaMemcpyAsync(desc, o.desc, (size_t)total * 32, cudaMemcpyDeviceToHost, ctx->stream));
+  VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (n_kp) memcpy(n_kp, counts.data(), (size_t)count * 4);
+  rc = orb_check_status(ctx, counts.data(), status.data(), count, cap);
+  if (rc) return rc;
+  for (int i = 0; i < count; ++i)
+    if (n_bow[i] > bow_cap) return vs_fail(ctx, VSLAM_E_CAPACITY, "BowVector capacity too small");
   return VSLAM_OK;
 }
 

@@ -53,6 +53,7 @@ struct vslam_ctx {
   DevBuf d1, d2, pairs, mcnt, rowpart, colstat, jobs;
   DevBuf lm;  // vslam_match_landmarks staging
   DevBuf geo;  // geometry.cu staging (camera models, essential inliers, landmark projection)
+  DevBuf orb[8];  // orb.cu: pyramid, blurred pyramid, candidates, counters/tables, keypoints, descriptors, staging
   DevBuf pyr;  // vslam_pyramid_detect_describe_batch: levels 1.. of the chunk in flight
   void* pinned = nullptr;  // small pinned staging block for counts
   // pipeline plans of vslam_stereo_batch, kept between calls (same geometry -> no reallocation)
@@ -137,6 +138,16 @@ int launch_build_store_jobs(vslam_ctx* ctx, const int32_t* jobs_i2, int n_jobs, 
 int launch_popc_peak(vslam_ctx* ctx, double* popc_per_s);
 // pyramid.cu: dst level = 2x2 rounded mean of src (dst.w = src.w / 2, dst.h = src.h / 2)
 int launch_pyr_down(vslam_ctx* ctx, const DevImages& src, const DevImages& dst, int count);
+// orb.cu: cv::ORB front end on images already on the device; outputs stay on the device
+struct OrbDeviceOut {
+  float* kp;        // [count][cap][6]
+  uint8_t* desc;    // [count][cap][32]
+  int32_t* n_kp;    // [count]
+  int32_t* status;  // [count]
+};
+int launch_orb(vslam_ctx* ctx, const uint8_t* images_dev, int count, int w, int h, int pitch, size_t stride,
+               const vslam_orb_params* prm, int cap, OrbDeviceOut* out);
+int orb_check_status(vslam_ctx* ctx, const int32_t* n_kp, const int32_t* status, int count, int cap);
 // landmarks.cu
 int launch_match_landmarks(vslam_ctx* ctx, const double* kp_xy, const uint32_t* kp_desc, int n_kp,
                            const double* proj_xy, int n_proj, const int32_t* obs_off, const uint32_t* obs_desc,

@@ -1,0 +1,676 @@
+// orb.cu -- cv::ORB::detectAndCompute as visnav::compute_bow_vector configures it (reference keypoints.h:249:
+// cv::ORB::create(num_features, 1.2, 8, 19, 0, 2, cv::ORB::FAST_SCORE); patchSize 31, fastThreshold 20), batched over
+// images, for sm_100a.  SURVEY.md §8f-4, ORB half: the second detector the reference runs per keyframe, feeding the
+// vocabulary transform (bow.cu).
+//
+// Semantics (thirdparty/opencv/modules; every stage below was first restated on the CPU -- oracle/visnav_oracle_orb.c
+// -- and pinned to cv2.ORB):
+//   pyramid      features2d/src/orb.cpp:1063-1130: level l is cvRound(size / 1.2^l), made from level l-1 by
+//                resize(INTER_LINEAR_EXACT): 8.8 fixed-point taps (imgproc/src/resize.cpp:733-771, :344-398, :691-731)
+//   FAST-9/16    features2d/src/fast.cpp:56-290: corner iff 9 contiguous ring pixels are all brighter than v + t or
+//                all darker than v - t; score = the largest t that keeps it a corner (fast_score.cpp:119-215);
+//                kept iff the score is strictly above its 8 neighbours' scores
+//   selection    keypoint.cpp:105-117 (19 px border), :69-90 retainBest: every keypoint whose score reaches the n-th
+//                largest of its level (ties all stay); per-level budgets orb.cpp:843-856
+//   orientation  orb.cpp:181-216 intensity centroid over the radius-15 disc, fastAtan2 (mathfuncs_core.simd.hpp:50-71)
+//   blur         GaussianBlur(7x7, sigma 2) on a sub-matrix -> the float separable filter (smooth.dispatch.cpp:611-757,
+//                filter.dispatch.cpp:290-375), multiply-adds fused as OpenCV's AVX2 dispatch executes them (measured
+//                against cv2: 0 differing pixels in 12 M with fused adds, 57 without)
+//   descriptor   orb.cpp:219-268 with bit_pattern_31_ = the reference's own rBRIEF table (rbrief_pattern.inc)
+// Keypoint ORDER inside a level is std::nth_element's in the reference (unspecified); here: raster order.  The set,
+// and every keypoint's fields and descriptor, are the reference's.
+//
+// Data layout in HBM: one pyramid slab per image (levels back to back, row pitch a multiple of 16 bytes), a second
+// slab for the blurred levels; per (image, level) a candidate list of packed keys (score << 24 | y << 12 | x) with a
+// 256-bin score histogram; keypoints [count][cap] x {x, y, size, angle, response, octave} floats and [count][cap][32]
+// descriptor bytes.  All byte/integer work except the blur and the rotation of the sampling pattern.
+#include <math.h>
+
+#include <vector>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int kMaxLevels = 8;
+constexpr int kMaxLevelKp = 8192;  // keypoints one level may keep (sorted in shared memory)
+
+struct OrbGeom {
+  int nlevels;
+  int w[kMaxLevels], h[kMaxLevels], pitch[kMaxLevels];
+  long long off[kMaxLevels];  // byte offset of the level inside an image's slab
+  long long slab;             // bytes per image
+  float scale[kMaxLevels];
+  int nper[kMaxLevels];
+  int cand_off[kMaxLevels];   // offset of the level's candidate list inside an image's candidate block (keys)
+  int cand_cap[kMaxLevels];
+  int cand_total;             // keys per image
+  int tab_off[kMaxLevels];    // offset of the level's resize tables ({x ofs, x c1} x w, {y ofs, y c1} x h)
+};
+
+// ---- level 0: copy the caller's images into the slabs -----------------------------------------------------------
+__global__ void orb_copy_level0_kernel(const uint8_t* src, int w, int h, int pitch, size_t stride, OrbGeom g, uint8_t* pyr) {
+  const int img = blockIdx.z;
+  const int y = blockIdx.y;
+  const uint8_t* s = src + (size_t)img * stride + (size_t)y * pitch;
+  uint8_t* d = pyr + (size_t)img * g.slab + (size_t)y * g.pitch[0];
+  for (int x = blockIdx.x * blockDim.x + threadIdx.x; x < w; x += gridDim.x * blockDim.x) d[x] = s[x];
+}
+
+// ---- resize INTER_LINEAR_EXACT: one thread per destination pixel ---------------------------------------------------
+// tab: [w] {ofs, c1} then [h] {ofs, c1} (uint16 pairs); c0 = 256 - c1.  Destination pixels left of / beyond the
+// interpolated range carry c1 = 0 and the edge offset, which reproduces hlineResize's replicated ends and vlineSet.
+__global__ void orb_resize_kernel(OrbGeom g, int l, const ushort2* tab, uint8_t* pyr) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y;
+  const int img = blockIdx.z;
+  if (x >= g.w[l]) return;
+  const ushort2 tx = tab[x], ty = tab[g.w[l] + y];
+  const int sw = g.w[l - 1], sh = g.h[l - 1];
+  const uint8_t* s = pyr + (size_t)img * g.slab + g.off[l - 1];
+  const int x1 = min(tx.x + 1, sw - 1), y1 = min(ty.x + 1, sh - 1);
+  const uint8_t* r0 = s + (size_t)ty.x * g.pitch[l - 1];
+  const uint8_t* r1 = s + (size_t)y1 * g.pitch[l - 1];
+  const uint32_t cx1 = tx.y, cx0 = 256u - cx1, cy1 = ty.y, cy0 = 256u - cy1;
+  const uint32_t a = cx0 * r0[tx.x] + cx1 * r0[x1];  // ufixedpoint16 row values
+  const uint32_t b = cx0 * r1[tx.x] + cx1 * r1[x1];
+  const uint32_t v = (a * cy0 + b * cy1 + 32768u) >> 16;
+  pyr[(size_t)img * g.slab + g.off[l] + (size_t)y * g.pitch[l] + x] = (uint8_t)min(v, 255u);
+}
+
+// ---- FAST-9/16 score + 3x3 non-maximum suppression + border filter -------------------------------------------------
+constexpr int kFastTW = 64, kFastTH = 16;             // outputs per CTA
+constexpr int kFastIW = kFastTW + 8, kFastIH = kFastTH + 8;  // image tile: 1 (NMS halo) + 3 (ring) on every side
+constexpr int kFastSW = kFastTW + 2, kFastSH = kFastTH + 2;  // score tile
+
+__device__ __forceinline__ int ring_offset(int k, int pitch) {
+  // fast_score.cpp:52-56: (dx, dy) of ring pixel k
+  const int dx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
+  const int dy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
+  return dx[k] + dy[k] * pitch;
+}
+
+// 9 contiguous set bits in the 16-bit ring mask (cyclic)?
+__device__ __forceinline__ bool has_arc9(uint32_t m) {
+  m |= m << 16;
+  uint32_t x = m & (m >> 1);
+  x &= x >> 2;
+  x &= x >> 4;      // bit i: 8 contiguous from i
+  x &= m >> 8;      // 9 contiguous
+  return (x & 0xFFFFu) != 0;
+}
+
+__device__ int fast_corner_score(const uint8_t* p, int pitch, int threshold) {
+  const int v = p[0];
+  int d[16];
+  uint32_t bright_m = 0, dark_m = 0;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    d[k] = v - (int)p[ring_offset(k, pitch)];
+    dark_m |= (uint32_t)(d[k] > threshold) << k;     // ring pixel darker than v - t
+    bright_m |= (uint32_t)(d[k] < -threshold) << k;  // brighter than v + t
+  }
+  if (!has_arc9(bright_m) && !has_arc9(dark_m)) return 0;
+  // score = max over the 16 arcs of min(d) and of min(-d), minus 1 (cornerScore<16>); arc minima / maxima by doubling:
+  // windows of 2, 4, 8 ring pixels, then the ninth
+  int lo[16], hi[16], t1[16], t2[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    lo[k] = min(d[k], d[(k + 1) & 15]);
+    hi[k] = max(d[k], d[(k + 1) & 15]);
+  }
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    t1[k] = min(lo[k], lo[(k + 2) & 15]);
+    t2[k] = max(hi[k], hi[(k + 2) & 15]);
+  }
+  // The two sides are accumulated apart (as OpenCV's q0 / q1): nvcc 12.9 miscompiles the per-arc form
+  // best = max(best, max(mn, -mx)) for sm_100a (it returns max |d| - 1; tools/probes/t_fast2.cu shows it).
+  int dark = -1000, bright = 1000;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    dark = max(dark, min(min(t1[k], t1[(k + 4) & 15]), d[(k + 8) & 15]));
+    bright = min(bright, max(max(t2[k], t2[(k + 4) & 15]), d[(k + 8) & 15]));
+  }
+  return max(dark, -bright) - 1;
+}
+
+struct FastParams {
+  OrbGeom g;
+  const uint8_t* pyr;
+  int threshold, edge;
+  uint32_t* cand;      // [count][cand_total]
+  uint32_t* cand_cnt;  // [count][kMaxLevels]
+  uint32_t* hist;      // [count][kMaxLevels][256]
+  int tiles_x[kMaxLevels], tiles_y[kMaxLevels], tile_first[kMaxLevels + 1];
+};
+
+__global__ void __launch_bounds__(256) orb_fast_kernel(const FastParams p) {
+  __shared__ uint8_t s_img[kFastIH][kFastIW + 8];
+  __shared__ uint8_t s_score[kFastSH][kFastSW + 2];
+  const int img = blockIdx.y;
+  int l = 0;
+  while (l + 1 < p.g.nlevels && (int)blockIdx.x >= p.tile_first[l + 1]) ++l;
+  const int t = blockIdx.x - p.tile_first[l];
+  const int tx0 = (t % p.tiles_x[l]) * kFastTW, ty0 = (t / p.tiles_x[l]) * kFastTH;
+  const int W = p.g.w[l], H = p.g.h[l], pitch = p.g.pitch[l];
+  const uint8_t* base = p.pyr + (size_t)img * p.g.slab + p.g.off[l];
+  for (int i = threadIdx.x; i < kFastIH * kFastIW; i += blockDim.x) {
+    const int yy = i / kFastIW, xx = i % kFastIW;
+    const int gx = tx0 - 4 + xx, gy = ty0 - 4 + yy;
+    s_img[yy][xx] = (gx >= 0 && gx < W && gy >= 0 && gy < H) ? base[(size_t)gy * pitch + gx] : 0;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < kFastSH * kFastSW; i += blockDim.x) {
+    const int yy = i / kFastSW, xx = i % kFastSW;
+    const int gx = tx0 - 1 + xx, gy = ty0 - 1 + yy;
+    int sc = 0;
+    if (gx >= 3 && gx < W - 3 && gy >= 3 && gy < H - 3) {  // fast.cpp:96, :206
+      const uint8_t* c = &s_img[yy + 3][xx + 3];
+      const int v = c[0];
+      // an arc of 9 holds one pixel of every opposite pair: two quick rejections before the full ring
+      const int a0 = abs(v - c[3 * (kFastIW + 8)]), a8 = abs(v - c[-3 * (kFastIW + 8)]);
+      const int a4 = abs(v - c[3]), a12 = abs(v - c[-3]);
+      if (max(a0, a8) > p.threshold && max(a4, a12) > p.threshold) {
+        sc = fast_corner_score(c, kFastIW + 8, p.threshold);
+        if (sc < p.threshold) sc = 0;
+      }
+    }
+    s_score[yy][xx] = (uint8_t)sc;
+  }
+  __syncthreads();
+  const int edge = p.edge;
+  if (H <= 2 * edge || W <= 2 * edge) return;  // runByImageBorder clears everything (keypoint.cpp:109-110)
+  for (int i = threadIdx.x; i < kFastTH * kFastTW; i += blockDim.x) {
+    const int yy = i / kFastTW, xx = i % kFastTW;
+    const int gx = tx0 + xx, gy = ty0 + yy;
+    const int v = s_score[yy + 1][xx + 1];
+    if (v == 0 || gx < edge || gx >= W - edge || gy < edge || gy >= H - edge) continue;
+    const uint8_t* s = &s_score[yy + 1][xx + 1];
+    constexpr int sp = kFastSW + 2;
+    if (v > s[1] && v > s[-1] && v > s[-sp - 1] && v > s[-sp] && v > s[-sp + 1] && v > s[sp - 1] && v > s[sp] &&
+        v > s[sp + 1]) {
+      const uint32_t pos = atomicAdd(p.cand_cnt + img * kMaxLevels + l, 1u);
+      if (pos < (uint32_t)p.g.cand_cap[l])
+        p.cand[(size_t)img * p.g.cand_total + p.g.cand_off[l] + pos] = ((uint32_t)v << 24) | ((uint32_t)gy << 12) | (uint32_t)gx;
+      atomicAdd(p.hist + ((size_t)img * kMaxLevels + l) * 256 + v, 1u);
+    }
+  }
+}
+
+// ---- retainBest per level + raster order: one CTA per image -----------------------------------------------------------
+struct SelectParams {
+  OrbGeom g;
+  const uint32_t* cand;
+  const uint32_t* cand_cnt;
+  const uint32_t* hist;
+  float* kp;        // [count][cap][6]
+  int32_t* n_kp;    // [count]
+  int32_t* status;  // [count]: bit 0 = a level overflowed its candidate list, bit 1 = more than kMaxLevelKp kept
+  int cap;
+};
+
+__device__ void bitonic_asc_u32_blk(uint32_t* keys, int n) {
+  for (int k = 2; k <= n; k <<= 1)
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int l = i ^ j;
+        if (l > i) {
+          const uint32_t a = keys[i], b = keys[l];
+          if (((i & k) == 0) ? (a > b) : (a < b)) {
+            keys[i] = b;
+            keys[l] = a;
+          }
+        }
+      }
+      __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(1024) orb_select_kernel(const SelectParams p) {
+  __shared__ uint32_t s_keys[kMaxLevelKp];
+  __shared__ int s_thr, s_keep, s_cnt;
+  const int img = blockIdx.x;
+  int out = 0;
+  int status = 0;
+  for (int l = 0; l < p.g.nlevels; ++l) {
+    const uint32_t raw = p.cand_cnt[img * kMaxLevels + l];
+    const int n = (int)min(raw, (uint32_t)p.g.cand_cap[l]);
+    if (raw > (uint32_t)p.g.cand_cap[l]) status |= 1;
+    if (threadIdx.x == 0) {
+      // KeyPointsFilter::retainBest (keypoint.cpp:69-90): nothing to do unless there are more than n_points; then
+      // everything whose response reaches the n_points-th largest stays
+      const uint32_t* h = p.hist + ((size_t)img * kMaxLevels + l) * 256;
+      int thr = 0;
+      if (n > p.g.nper[l]) {
+        if (p.g.nper[l] == 0) {
+          thr = 256;
+        } else {
+          int acc = 0;
+          for (thr = 255; thr > 0; --thr) {
+            acc += (int)h[thr];
+            if (acc >= p.g.nper[l]) break;
+          }
+        }
+      }
+      s_thr = thr;
+      s_cnt = 0;
+    }
+    __syncthreads();
+    const uint32_t thr = (uint32_t)s_thr;
+    const uint32_t* c = p.cand + (size_t)img * p.g.cand_total + p.g.cand_off[l];
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const uint32_t key = c[i];
+      if ((key >> 24) >= thr) {
+        const int pos = atomicAdd(&s_cnt, 1);
+        if (pos < kMaxLevelKp) s_keys[pos] = (key << 8) | (key >> 24);  // y, x on top: raster order; score below
+      }
+    }
+    __syncthreads();
+    int m = s_cnt;
+    if (m > kMaxLevelKp) {
+      status |= 2;
+      m = kMaxLevelKp;
+    }
+    int np2 = 32;
+    while (np2 < m) np2 <<= 1;
+    for (int i = m + threadIdx.x; i < np2; i += blockDim.x) s_keys[i] = 0xFFFFFFFFu;
+    __syncthreads();
+    bitonic_asc_u32_blk(s_keys, np2);
+    const float sc = p.g.scale[l];
+    for (int i = threadIdx.x; i < m; i += blockDim.x) {
+      const uint32_t k = s_keys[i];
+      const int x = (k >> 8) & 0xFFF, y = k >> 20;
+      if (out + i < p.cap) {
+        float* o = p.kp + ((size_t)img * p.cap + out + i) * 6;
+        o[0] = __fmul_rn((float)x, sc);   // allKeypoints[i].pt *= scale (orb.cpp:993-997)
+        o[1] = __fmul_rn((float)y, sc);
+        o[2] = __fmul_rn(31.f, sc);       // size = patchSize * scale (:907)
+        o[3] = 0.f;                       // angle: orb_angle_kernel
+        o[4] = (float)(k & 0xFF);
+        o[5] = (float)l;
+      }
+    }
+    out += m;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    p.n_kp[img] = out;
+    p.status[img] = status;
+  }
+}
+
+// ---- orientation: one warp per keypoint ---------------------------------------------------------------------------------
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
+  // core/src/mathfuncs_core.simd.hpp:34-71, every operation rounded on its own (cv2 evaluates it unfused)
+  const float p1 = 0.9997878412794807f * (float)(180 / 3.1415926535897932384626433832795);
+  const float p3 = -0.3258083974640975f * (float)(180 / 3.1415926535897932384626433832795);
+  const float p5 = 0.1555786518463281f * (float)(180 / 3.1415926535897932384626433832795);
+  const float p7 = -0.04432655554792128f * (float)(180 / 3.1415926535897932384626433832795);
+  const float eps = (float)2.2204460492503131e-16;
+  const float ax = fabsf(x), ay = fabsf(y);
+  float a;
+  if (ax >= ay) {
+    const float c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+    const float c2 = __fmul_rn(c, c);
+    a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+  } else {
+    const float c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+    const float c2 = __fmul_rn(c, c);
+    a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+  }
+  if (x < 0) a = __fsub_rn(180.f, a);
+  if (y < 0) a = __fsub_rn(360.f, a);
+  return a;
+}
+
+struct KpParams {
+  OrbGeom g;
+  const uint8_t* pyr;   // unblurred (angles) or blurred (descriptors) slabs
+  float* kp;
+  const int32_t* n_kp;
+  uint8_t* desc;
+  int cap;
+};
+
+__constant__ int c_umax[16];   // orb.cpp:860-878 for halfPatchSize 15
+__constant__ int8_t c_pattern[256][4];
+
+__global__ void __launch_bounds__(256) orb_angle_kernel(const KpParams p) {
+  const int lane = threadIdx.x & 31;
+  const int j = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int img = blockIdx.y;
+  if (j >= min(p.n_kp[img], p.cap)) return;
+  float* k = p.kp + ((size_t)img * p.cap + j) * 6;
+  const int l = (int)k[5];
+  const float inv = __fdiv_rn(1.f, p.g.scale[l]);
+  // the level coordinates: x * scale / scale rounds back to x for every integer x below 4096
+  const int x = __float2int_rn(__fmul_rn(k[0], inv)), y = __float2int_rn(__fmul_rn(k[1], inv));
+  const int pitch = p.g.pitch[l];
+  const uint8_t* c = p.pyr + (size_t)img * p.g.slab + p.g.off[l] + (size_t)y * pitch + x;
+  int m10 = 0, m01 = 0;
+  if (lane < 31) {  // lane = row v + 15 of the disc
+    const int v = lane - 15;
+    const int d = c_umax[abs(v)];
+    const uint8_t* r = c + v * pitch;
+    int s = 0;
+    for (int u = -d; u <= d; ++u) {
+      const int val = r[u];
+      m10 += u * val;
+      s += val;
+    }
+    m01 = v * s;
+  }
+  m10 = __reduce_add_sync(0xFFFFFFFFu, m10);
+  m01 = __reduce_add_sync(0xFFFFFFFFu, m01);
+  if (lane == 0) k[3] = fast_atan2_deg((float)m01, (float)m10);
+}
+
+// ---- blur: separable 7-tap float filter, BORDER_REFLECT_101 ----------------------------------------------------------------
+constexpr int kBlurTW = 64, kBlurTH = 16;
+
+struct BlurParams {
+  OrbGeom g;
+  const uint8_t* pyr;
+  uint8_t* blur;
+  float k7[7];
+  int tiles_x[kMaxLevels], tile_first[kMaxLevels + 1];
+};
+
+__device__ __forceinline__ int reflect101(int p, int len) {
+  if (len == 1) return 0;
+  while (p < 0 || p >= len) p = p < 0 ? -p : 2 * len - 2 - p;
+  return p;
+}
+
+__global__ void __launch_bounds__(256) orb_blur_kernel(const BlurParams p) {
+  __shared__ uint8_t s_img[kBlurTH + 6][kBlurTW + 8];
+  __shared__ float s_row[kBlurTH + 6][kBlurTW];
+  const int img = blockIdx.y;
+  int l = 0;
+  while (l + 1 < p.g.nlevels && (int)blockIdx.x >= p.tile_first[l + 1]) ++l;
+  const int t = blockIdx.x - p.tile_first[l];
+  const int tx0 = (t % p.tiles_x[l]) * kBlurTW, ty0 = (t / p.tiles_x[l]) * kBlurTH;
+  const int W = p.g.w[l], H = p.g.h[l], pitch = p.g.pitch[l];
+  const uint8_t* base = p.pyr + (size_t)img * p.g.slab + p.g.off[l];
+  for (int i = threadIdx.x; i < (kBlurTH + 6) * (kBlurTW + 6); i += blockDim.x) {
+    const int yy = i / (kBlurTW + 6), xx = i % (kBlurTW + 6);
+    s_img[yy][xx] = base[(size_t)reflect101(ty0 - 3 + yy, H) * pitch + reflect101(tx0 - 3 + xx, W)];
+  }
+  __syncthreads();
+  // RowFilter<uchar, float>: s = k[0] * p[0]; s += k[i] * p[i], left to right (fused)
+  for (int i = threadIdx.x; i < (kBlurTH + 6) * kBlurTW; i += blockDim.x) {
+    const int yy = i / kBlurTW, xx = i % kBlurTW;
+    float s = __fmul_rn(p.k7[0], (float)s_img[yy][xx]);
+#pragma unroll
+    for (int q = 1; q < 7; ++q) s = __fmaf_rn(p.k7[q], (float)s_img[yy][xx + q], s);
+    s_row[yy][xx] = s;
+  }
+  __syncthreads();
+  // SymmColumnFilter: s = k[3] * r[0] + delta (0); s += k[3 + j] * (r[+j] + r[-j]); Cast<float, uchar> = cvRound, saturate
+  uint8_t* out = p.blur + (size_t)img * p.g.slab + p.g.off[l];
+  for (int i = threadIdx.x; i < kBlurTH * kBlurTW; i += blockDim.x) {
+    const int yy = i / kBlurTW, xx = i % kBlurTW;
+    const int gx = tx0 + xx, gy = ty0 + yy;
+    if (gx >= W || gy >= H) continue;
+    float s = __fmaf_rn(p.k7[3], s_row[yy + 3][xx], 0.f);
+#pragma unroll
+    for (int j = 1; j <= 3; ++j) s = __fmaf_rn(p.k7[3 + j], __fadd_rn(s_row[yy + 3 + j][xx], s_row[yy + 3 - j][xx]), s);
+    out[(size_t)gy * pitch + gx] = (uint8_t)min(max(__float2int_rn(s), 0), 255);
+  }
+}
+
+// ---- descriptors: one warp per keypoint, lane = descriptor byte ---------------------------------------------------------------
+__global__ void __launch_bounds__(256) orb_describe_kernel(const KpParams p) {
+  const int lane = threadIdx.x & 31;
+  const int j = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int img = blockIdx.y;
+  if (j >= min(p.n_kp[img], p.cap)) return;
+  const float* k = p.kp + ((size_t)img * p.cap + j) * 6;
+  const int l = (int)k[5];
+  const float inv = __fdiv_rn(1.f, p.g.scale[l]);  // orb.cpp:230
+  const int x = __float2int_rn(__fmul_rn(k[0], inv)), y = __float2int_rn(__fmul_rn(k[1], inv));
+  const int pitch = p.g.pitch[l];
+  const uint8_t* c = p.pyr + (size_t)img * p.g.slab + p.g.off[l] + (size_t)y * pitch + x;
+  // angle *= (float)(CV_PI / 180.f); a = cosf(angle), b = sinf(angle): evaluated in double and rounded once
+  const float angle = __fmul_rn(k[3], (float)(3.1415926535897932384626433832795 / 180.f));
+  const float a = (float)cos((double)angle), b = (float)sin((double)angle);
+  int val = 0;
+#pragma unroll
+  for (int bit = 0; bit < 8; ++bit) {
+    const int8_t* q = c_pattern[8 * lane + bit];
+    const float xa = __fsub_rn(__fmul_rn((float)q[0], a), __fmul_rn((float)q[1], b));
+    const float ya = __fadd_rn(__fmul_rn((float)q[0], b), __fmul_rn((float)q[1], a));
+    const float xb = __fsub_rn(__fmul_rn((float)q[2], a), __fmul_rn((float)q[3], b));
+    const float yb = __fadd_rn(__fmul_rn((float)q[2], b), __fmul_rn((float)q[3], a));
+    const int t0 = c[__float2int_rn(ya) * pitch + __float2int_rn(xa)];
+    const int t1 = c[__float2int_rn(yb) * pitch + __float2int_rn(xb)];
+    val |= (t0 < t1) << bit;
+  }
+  p.desc[((size_t)img * p.cap + j) * 32 + lane] = (uint8_t)val;
+}
+
+}  // namespace
+
+// ---- host side -------------------------------------------------------------------------------------------------------------
+static int cv_round_f(float v) { return (int)lrintf(v); }  // cvRound: round half to even
+
+// interpolationLinear::getCoeffs (resize.cpp:739-765) for one axis, as {offset, c1} pairs (c0 = 256 - c1)
+static void linear_table(int srcsize, int dstsize, std::vector<uint16_t>& tab) {
+  const double inv_scale = (double)dstsize / srcsize;
+  const double scale = 1.0 / inv_scale;
+  for (int val = 0; val < dstsize; ++val) {
+    const double fval = scale * ((double)val + 0.5) - 0.5;
+    const int ival = (int)floor(fval);
+    uint16_t ofs = 0, c1 = 0;
+    if (ival >= 0 && srcsize > 1) {
+      if (ival < srcsize - 1) {
+        ofs = (uint16_t)ival;
+        const double frac = fval - (double)ival;
+        c1 = frac < 0 ? 0 : (uint16_t)lrint(frac * 256.0);
+      } else {
+        ofs = (uint16_t)(srcsize - 1);  // beyond max_x: the last source pixel
+      }
+    }  // left of min_x: source pixel 0
+    tab.push_back(ofs);
+    tab.push_back(c1);
+  }
+}
+
+// Runs the whole ORB front end for `count` images already on the device; outputs stay on the device (ctx->orb[...]).
+int launch_orb(vslam_ctx* ctx, const uint8_t* images_dev, int count, int w, int h, int pitch, size_t stride,
+               const vslam_orb_params* prm, int cap, OrbDeviceOut* out) {
+  if (prm->nlevels < 1 || prm->nlevels > kMaxLevels) return vs_fail(ctx, VSLAM_E_LIMIT, "ORB: 1..8 pyramid levels");
+  if (w >= 4096 || h >= 4096) return vs_fail(ctx, VSLAM_E_LIMIT, "ORB: images up to 4095 x 4095");
+  if (prm->nfeatures < 0 || prm->edge_threshold < 16 || prm->fast_threshold < 1 || prm->fast_threshold > 254 ||
+      !(prm->scale_factor > 1.f))
+    return vs_fail(ctx, VSLAM_E_ARG, "ORB: nfeatures >= 0, edge_threshold >= 16 (patch radius), 1 <= fast_threshold <= 254, scale_factor > 1");
+  OrbGeom g;
+  memset(&g, 0, sizeof g);
+  g.nlevels = prm->nlevels;
+  const double scale_factor = (double)prm->scale_factor;  // ORB_Impl keeps the float argument in a double
+  {
+    // per-level budgets, orb.cpp:843-856 (float arithmetic)
+    const float factor = (float)(1.0 / scale_factor);
+    float nd = prm->nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)g.nlevels));
+    int sum = 0;
+    for (int l = 0; l < g.nlevels - 1; ++l) {
+      g.nper[l] = cv_round_f(nd);
+      sum += g.nper[l];
+      nd *= factor;
+    }
+    g.nper[g.nlevels - 1] = std::max(prm->nfeatures - sum, 0);
+  }
+  std::vector<uint16_t> tab;
+  long long off = 0;
+  int cand_off = 0;
+  for (int l = 0; l < g.nlevels; ++l) {
+    g.scale[l] = (float)pow(scale_factor, (double)l);  // getScale, orb.cpp:653-656
+    const float inv = 1.0f / g.scale[l];
+    g.w[l] = cv_round_f(w * inv);
+    g.h[l] = cv_round_f(h * inv);
+    if (g.w[l] < 1 || g.h[l] < 1) return vs_fail(ctx, VSLAM_E_LIMIT, "ORB: image too small for the pyramid");
+    g.pitch[l] = (g.w[l] + 15) & ~15;
+    g.off[l] = off;
+    off += (long long)g.pitch[l] * g.h[l];
+    off = (off + 255) & ~255LL;
+    g.cand_off[l] = cand_off;
+    g.cand_cap[l] = ((g.w[l] + 1) / 2) * ((g.h[l] + 1) / 2) + 16;  // strict 3x3 maxima: at most one per 2x2 block
+    cand_off += g.cand_cap[l];
+    g.tab_off[l] = (int)(tab.size() / 2);
+    if (l > 0) {
+      linear_table(g.w[l - 1], g.w[l], tab);
+      linear_table(g.h[l - 1], g.h[l], tab);
+    }
+  }
+  g.slab = off;
+  g.cand_total = cand_off;
+
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  DevBuf& b_pyr = ctx->orb[0];
+  DevBuf& b_blur = ctx->orb[1];
+  DevBuf& b_cand = ctx->orb[2];
+  DevBuf& b_misc = ctx->orb[3];  // cand_cnt | hist | n_kp | status | tables
+  DevBuf& b_kp = ctx->orb[4];
+  DevBuf& b_desc = ctx->orb[5];
+  VS_CUDA(ctx, b_pyr.reserve((size_t)g.slab * count + 64));
+  VS_CUDA(ctx, b_blur.reserve((size_t)g.slab * count + 64));
+  VS_CUDA(ctx, b_cand.reserve((size_t)g.cand_total * count * 4));
+  const size_t o_hist = ((size_t)count * kMaxLevels * 4 + 255) & ~(size_t)255;
+  const size_t o_nkp = o_hist + (size_t)count * kMaxLevels * 256 * 4;
+  const size_t o_status = o_nkp + (((size_t)count * 4 + 255) & ~(size_t)255);
+  const size_t o_tab = o_status + (((size_t)count * 4 + 255) & ~(size_t)255);
+  VS_CUDA(ctx, b_misc.reserve(o_tab + tab.size() * 2 + 256));
+  VS_CUDA(ctx, b_kp.reserve((size_t)count * cap * 6 * 4));
+  VS_CUDA(ctx, b_desc.reserve((size_t)count * cap * 32));
+  uint8_t* misc = b_misc.as<uint8_t>();
+  cudaStream_t st = ctx->stream;
+  VS_CUDA(ctx, cudaMemsetAsync(misc, 0, o_nkp, st));  // candidate counters and histograms
+  if (!tab.empty()) VS_CUDA(ctx, cudaMemcpyAsync(misc + o_tab, tab.data(), tab.size() * 2, cudaMemcpyHostToDevice, st));
+  static bool tables_done[64] = {};
+  if (ctx->device < 64 && !tables_done[ctx->device]) {
+    // umax of the radius-15 disc (orb.cpp:860-878) and the sampling pattern
+    int umax[17];
+    const int half = 15;
+    int v, v0;
+    const int vmax = (int)floorf(half * sqrtf(2.f) / 2 + 1), vmin = (int)ceilf(half * sqrtf(2.f) / 2);
+    for (v = 0; v <= vmax; ++v) umax[v] = (int)lrint(sqrt((double)half * half - v * v));
+    for (v = half, v0 = 0; v >= vmin; --v) {
+      while (umax[v0] == umax[v0 + 1]) ++v0;
+      umax[v] = v0;
+      ++v0;
+    }
+    static const int8_t pattern[256][4] = {
+#include "rbrief_pattern.inc"
+    };
+    VS_CUDA(ctx, cudaMemcpyToSymbol(c_umax, umax, 16 * sizeof(int)));
+    VS_CUDA(ctx, cudaMemcpyToSymbol(c_pattern, pattern, sizeof pattern));
+    tables_done[ctx->device] = true;
+  }
+  uint8_t* pyr = b_pyr.as<uint8_t>();
+  orb_copy_level0_kernel<<<dim3((w + 255) / 256, h, count), 256, 0, st>>>(images_dev, w, h, pitch, stride, g, pyr);
+  ctx->launches += 1;
+  for (int l = 1; l < g.nlevels; ++l) {
+    if (g.w[l] == g.w[l - 1] && g.h[l] == g.h[l - 1])
+      return vs_fail(ctx, VSLAM_E_LIMIT, "ORB: two pyramid levels of the same size");  // resize() would copy
+    orb_resize_kernel<<<dim3((g.w[l] + 127) / 128, g.h[l], count), 128, 0, st>>>(
+        g, l, reinterpret_cast<const ushort2*>(misc + o_tab) + g.tab_off[l], pyr);
+    ctx->launches += 1;
+  }
+  VS_CUDA(ctx, cudaGetLastError());
+  FastParams fp;
+  fp.g = g;
+  fp.pyr = pyr;
+  fp.threshold = prm->fast_threshold;
+  fp.edge = prm->edge_threshold;
+  fp.cand = b_cand.as<uint32_t>();
+  fp.cand_cnt = reinterpret_cast<uint32_t*>(misc);
+  fp.hist = reinterpret_cast<uint32_t*>(misc + o_hist);
+  BlurParams bp;
+  bp.g = g;
+  bp.pyr = pyr;
+  bp.blur = b_blur.as<uint8_t>();
+  {
+    // getGaussianKernel(7, 2, CV_32F): exp(-x^2 / (2 sigma^2)) normalised, computed in double and rounded to float
+    // (smooth.dispatch.cpp getGaussianKernelBitExact; checked against cv2.getGaussianKernel bit for bit in
+    // tests/test_oracle_orb.py)
+    double kd[7], sum = 0;
+    for (int i = 0; i < 7; ++i) { kd[i] = exp(-(double)((i - 3) * (i - 3)) / (2.0 * 2.0 * 2.0)); sum += kd[i]; }
+    for (int i = 0; i < 7; ++i) bp.k7[i] = (float)(kd[i] / sum);
+  }
+  int tf = 0, tb = 0;
+  for (int l = 0; l < g.nlevels; ++l) {
+    fp.tiles_x[l] = (g.w[l] + kFastTW - 1) / kFastTW;
+    fp.tiles_y[l] = (g.h[l] + kFastTH - 1) / kFastTH;
+    fp.tile_first[l] = tf;
+    tf += fp.tiles_x[l] * fp.tiles_y[l];
+    bp.tiles_x[l] = (g.w[l] + kBlurTW - 1) / kBlurTW;
+    bp.tile_first[l] = tb;
+    tb += bp.tiles_x[l] * ((g.h[l] + kBlurTH - 1) / kBlurTH);
+  }
+  fp.tile_first[g.nlevels] = tf;
+  bp.tile_first[g.nlevels] = tb;
+  orb_fast_kernel<<<dim3(tf, count), 256, 0, st>>>(fp);
+  SelectParams sp;
+  sp.g = g;
+  sp.cand = fp.cand;
+  sp.cand_cnt = fp.cand_cnt;
+  sp.hist = fp.hist;
+  sp.kp = b_kp.as<float>();
+  sp.n_kp = reinterpret_cast<int32_t*>(misc + o_nkp);
+  sp.status = reinterpret_cast<int32_t*>(misc + o_status);
+  sp.cap = cap;
+  orb_select_kernel<<<count, 1024, 0, st>>>(sp);
+  KpParams kp;
+  kp.g = g;
+  kp.pyr = pyr;
+  kp.kp = sp.kp;
+  kp.n_kp = sp.n_kp;
+  kp.desc = b_desc.as<uint8_t>();
+  kp.cap = cap;
+  orb_angle_kernel<<<dim3((cap + 7) / 8, count), 256, 0, st>>>(kp);
+  orb_blur_kernel<<<dim3(tb, count), 256, 0, st>>>(bp);
+  kp.pyr = bp.blur;
+  orb_describe_kernel<<<dim3((cap + 7) / 8, count), 256, 0, st>>>(kp);
+  ctx->launches += 5;
+  VS_CUDA(ctx, cudaGetLastError());
+  out->kp = sp.kp;
+  out->desc = kp.desc;
+  out->n_kp = sp.n_kp;
+  out->status = sp.status;
+  return VSLAM_OK;
+}
+
+int orb_check_status(vslam_ctx* ctx, const int32_t* n_kp, const int32_t* status, int count, int cap) {
+  for (int i = 0; i < count; ++i) {
+    if (status[i] & 1) return vs_fail(ctx, VSLAM_E_LIMIT, "ORB: candidate list overflow");
+    if (status[i] & 2) return vs_fail(ctx, VSLAM_E_LIMIT, "ORB: more than 8192 keypoints kept on one pyramid level");
+  }
+  for (int i = 0; i < count; ++i)
+    if (n_kp[i] > cap) return vs_fail(ctx, VSLAM_E_CAPACITY, "ORB: keypoint capacity too small (ties at the cut-off score all stay)");
+  return VSLAM_OK;
+}
+
+extern "C" int vslam_orb_detect_compute_batch(vslam_ctx* ctx, const uint8_t* images, int count, int w, int h, int pitch,
+                                              size_t image_stride, const vslam_orb_params* prm, float* kp, uint8_t* desc,
+                                              int32_t* n_kp, int cap) {
+  if (!ctx) return VSLAM_E_ARG;
+  if (!images || !prm || count < 0 || w <= 0 || h <= 0 || pitch < w || cap <= 0 || !kp || !desc || !n_kp ||
+      image_stride < (size_t)pitch * (h - 1) + w)
+    return vs_fail(ctx, VSLAM_E_ARG, "bad ORB arguments");
+  if (count == 0) return VSLAM_OK;
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t bytes = image_stride * (size_t)(count - 1) + (size_t)pitch * (h - 1) + w;
+  VS_CUDA(ctx, ctx->orb[6].reserve(bytes + 64));
+  VS_CUDA(ctx, cudaMemcpyAsync(ctx->orb[6].p, images, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  OrbDeviceOut out;
+  int rc = launch_orb(ctx, ctx->orb[6].as<uint8_t>(), count, w, h, pitch, image_stride, prm, cap, &out);
+  if (rc) return rc;
+  std::vector<int32_t> status((size_t)count);
+  VS_CUDA(ctx, cudaMemcpyAsync(n_kp, out.n_kp, (size_t)count * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  VS_CUDA(ctx, cudaMemcpyAsync(status.data(), out.status, (size_t)count * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  VS_CUDA(ctx, cudaMemcpyAsync(kp, out.kp, (size_t)count * cap * 24, cudaMemcpyDeviceToHost, ctx->stream));
+  VS_CUDA(ctx, cudaMemcpyAsync(desc, out.desc, (size_t)count * cap * 32, cudaMemcpyDeviceToHost, ctx->stream));
+  VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return orb_check_status(ctx, n_kp, status.data(), count, cap);
+}

@@ -41,7 +41,7 @@ ABI_SYMBOLS = [
     "vslam_desc_store_append", "vslam_desc_store_size",
     "vslam_bow_vocab_create", "vslam_bow_vocab_load_text", "vslam_bow_vocab_destroy", "vslam_bow_vocab_info",
     "vslam_bow_transform_batch", "vslam_bow_score", "vslam_bow_db_create", "vslam_bow_db_destroy", "vslam_bow_db_add",
-    "vslam_bow_db_size", "vslam_bow_db_query",
+    "vslam_bow_db_size", "vslam_bow_db_query", "vslam_orb_detect_compute_batch", "vslam_compute_bow_vector_batch",
 ]
 
 VSLAM_OPT_FP_CONTRACT = 1
@@ -176,6 +176,9 @@ def load_library():
     L.vslam_bow_db_add.argtypes = [vp, vp, vp, i, C.POINTER(i)]
     L.vslam_bow_db_size.argtypes = [vp]
     L.vslam_bow_db_query.argtypes = [vp, vp, vp, vp, i, vp, vp]
+    L.vslam_orb_detect_compute_batch.argtypes = [vp, vp, i, i, i, i, sz, C.POINTER(OrbParams), vp, vp, vp, i]
+    L.vslam_compute_bow_vector_batch.argtypes = [vp, vp, vp, i, i, i, i, sz, C.POINTER(OrbParams), i, vp, vp, vp, i, vp, vp,
+                                                 vp, vp, vp, i]
     _lib = L
     return L
 
@@ -263,6 +266,20 @@ class Context:
         self._pinned = getattr(self, "_pinned", [])
         self._pinned.append(p)
         return arr
+
+    def orb_detect_compute_batch(self, images, num_features=1500, params=None, cap=None):
+        """cv::ORB::create(num_features, 1.2, 8, 19, 0, 2, FAST_SCORE)->detectAndCompute for [count, h, w] images
+        (keypoints.h:249-250).  -> kp [count, cap, 6] (x, y, size, angle, response, octave), desc [count, cap, 32], n_kp."""
+        images = _image_batch(images)
+        count, h, w = images.shape
+        prm = params or OrbParams(num_features)
+        cap = cap or prm.nfeatures + prm.nfeatures // 4 + 256
+        kp = np.zeros((max(count, 1), cap, 6), np.float32)
+        desc = np.zeros((max(count, 1), cap, 32), np.uint8)
+        n_kp = np.zeros(max(count, 1), np.int32)
+        self._check(self.lib.vslam_orb_detect_compute_batch(self.h, _ptr(images), count, w, h, w, w * h, C.byref(prm),
+                                                            _ptr(kp), _ptr(desc), _ptr(n_kp), cap))
+        return kp[:count], desc[:count], n_kp[:count]
 
     def launch_count(self):
         return int(self.lib.vslam_launch_count(self.h))
@@ -531,6 +548,23 @@ class DescStore:
             pass
 
 
+class OrbParams(C.Structure):
+    """vslam_orb_params: cv::ORB::create(nfeatures, scale_factor, nlevels, edge_threshold, 0, 2, FAST_SCORE, 31, fast_threshold);
+    the defaults are the reference's call (keypoints.h:249)."""
+    _fields_ = [("nfeatures", C.c_int), ("scale_factor", C.c_float), ("nlevels", C.c_int), ("edge_threshold", C.c_int),
+                ("fast_threshold", C.c_int)]
+
+    def __init__(self, nfeatures=1500, scale_factor=1.2, nlevels=8, edge_threshold=19, fast_threshold=20):
+        super().__init__(int(nfeatures), float(scale_factor), int(nlevels), int(edge_threshold), int(fast_threshold))
+
+
+def _image_batch(images):
+    images = np.ascontiguousarray(images)
+    if images.dtype != np.uint8 or images.ndim != 3:
+        raise VslamError("images must be a [count, h, w] uint8 array")
+    return images
+
+
 BOW_SCORING = {"L1_NORM": 0, "L2_NORM": 1, "CHI_SQUARE": 2, "KL": 3, "BHATTACHARYYA": 4, "DOT_PRODUCT": 5}
 BOW_WEIGHTING = {"TF_IDF": 0, "TF": 1, "IDF": 2, "BINARY": 3}
 
@@ -604,6 +638,28 @@ class BowVocabulary:
         for f in np.nonzero(fwt > 0)[0]:
             fv.setdefault(int(fn[f]), []).append(int(f))
         return vecs[0], dict(sorted(fv.items()))
+
+    def compute_bow_vector_batch(self, images, num_features=1500, levelsup=4, params=None, cap=None):
+        """visnav::compute_bow_vector (keypoints.h:243-254) for [count, h, w] images: cv::ORB, then transform; the
+        descriptors stay on the device.  -> list of (ids, vals), and a dict with kp [count, cap, 6], desc [count, cap,
+        32], n_kp, feat_node, feat_weight."""
+        images = _image_batch(images)
+        count, h, w = images.shape
+        prm = params or OrbParams(num_features)
+        cap = cap or min(8192, prm.nfeatures + prm.nfeatures // 4 + 256)
+        ids = np.zeros((max(count, 1), cap), np.uint32)
+        vals = np.zeros((max(count, 1), cap), np.float64)
+        n_bow = np.zeros(max(count, 1), np.int32)
+        kp = np.zeros((max(count, 1), cap, 6), np.float32)
+        desc = np.zeros((max(count, 1), cap, 32), np.uint8)
+        n_kp = np.zeros(max(count, 1), np.int32)
+        fn = np.zeros((max(count, 1), cap), np.uint32)
+        fwt = np.zeros((max(count, 1), cap), np.float64)
+        self.ctx._check(self.ctx.lib.vslam_compute_bow_vector_batch(
+            self.ctx.h, self.h, _ptr(images), count, w, h, w, w * h, C.byref(prm), int(levelsup), _ptr(ids), _ptr(vals),
+            _ptr(n_bow), cap, _ptr(kp), _ptr(desc), _ptr(n_kp), _ptr(fn), _ptr(fwt), cap))
+        vecs = [(ids[i, :n_bow[i]].copy(), vals[i, :n_bow[i]].copy()) for i in range(count)]
+        return vecs, dict(kp=kp[:count], desc=desc[:count], n_kp=n_kp[:count], feat_node=fn[:count], feat_weight=fwt[:count])
 
     def score(self, v1, v2):
         i1, x1 = np.ascontiguousarray(v1[0], np.uint32), np.ascontiguousarray(v1[1], np.float64)
