@@ -100,17 +100,24 @@ __device__ __forceinline__ bool has_arc9(uint32_t m) {
   return (x & 0xFFFFu) != 0;
 }
 
-__device__ int fast_corner_score(const uint8_t* p, int pitch, int threshold) {
+// corner test of FAST_t<16> (fast.cpp:206-262) as two 16-bit ring masks
+__device__ __forceinline__ bool fast_is_corner(const uint8_t* p, int pitch, int threshold) {
   const int v = p[0];
-  int d[16];
   uint32_t bright_m = 0, dark_m = 0;
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
-    d[k] = v - (int)p[ring_offset(k, pitch)];
-    dark_m |= (uint32_t)(d[k] > threshold) << k;     // ring pixel darker than v - t
-    bright_m |= (uint32_t)(d[k] < -threshold) << k;  // brighter than v + t
+    const int d = v - (int)p[ring_offset(k, pitch)];
+    dark_m |= (uint32_t)(d > threshold) << k;     // ring pixel darker than v - t
+    bright_m |= (uint32_t)(d < -threshold) << k;  // brighter than v + t
   }
-  if (!has_arc9(bright_m) && !has_arc9(dark_m)) return 0;
+  return has_arc9(bright_m) || has_arc9(dark_m);
+}
+
+__device__ int fast_corner_score(const uint8_t* p, int pitch) {
+  const int v = p[0];
+  int d[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) d[k] = v - (int)p[ring_offset(k, pitch)];
   // score = max over the 16 arcs of min(d) and of min(-d), minus 1 (cornerScore<16>); arc minima / maxima by doubling:
   // windows of 2, 4, 8 ring pixels, then the ninth
   int lo[16], hi[16], t1[16], t2[16];
@@ -146,37 +153,64 @@ struct FastParams {
 };
 
 __global__ void __launch_bounds__(256) orb_fast_kernel(const FastParams p) {
-  __shared__ uint8_t s_img[kFastIH][kFastIW + 8];
+  __shared__ __align__(16) uint8_t s_img[kFastIH][kFastIW + 8];
   __shared__ uint8_t s_score[kFastSH][kFastSW + 2];
+  __shared__ uint16_t s_queue[2][kFastSH * kFastSW];
+  __shared__ int s_qn[2];
   const int img = blockIdx.y;
+  if (threadIdx.x < 2) s_qn[threadIdx.x] = 0;
   int l = 0;
   while (l + 1 < p.g.nlevels && (int)blockIdx.x >= p.tile_first[l + 1]) ++l;
   const int t = blockIdx.x - p.tile_first[l];
   const int tx0 = (t % p.tiles_x[l]) * kFastTW, ty0 = (t / p.tiles_x[l]) * kFastTH;
   const int W = p.g.w[l], H = p.g.h[l], pitch = p.g.pitch[l];
   const uint8_t* base = p.pyr + (size_t)img * p.g.slab + p.g.off[l];
-  for (int i = threadIdx.x; i < kFastIH * kFastIW; i += blockDim.x) {
-    const int yy = i / kFastIW, xx = i % kFastIW;
-    const int gx = tx0 - 4 + xx, gy = ty0 - 4 + yy;
-    s_img[yy][xx] = (gx >= 0 && gx < W && gy >= 0 && gy < H) ? base[(size_t)gy * pitch + gx] : 0;
+  // the image tile by 32-bit words: tile columns start at a multiple of 4 and the row pitch is a multiple of 16, so
+  // a word lies entirely inside [0, pitch) or entirely outside (bytes between W and pitch are never used below)
+  constexpr int kWords = kFastIW / 4;
+  for (int i = threadIdx.x; i < kFastIH * kWords; i += blockDim.x) {
+    const int yy = i / kWords, wx = i % kWords;
+    const int gx = tx0 - 4 + 4 * wx, gy = ty0 - 4 + yy;
+    uint32_t word = 0;
+    if (gx >= 0 && gx < pitch && gy >= 0 && gy < H) word = *reinterpret_cast<const uint32_t*>(base + (size_t)gy * pitch + gx);
+    *reinterpret_cast<uint32_t*>(&s_img[yy][4 * wx]) = word;
   }
   __syncthreads();
+  // pass 1a: OpenCV's high-speed rejection (fast.cpp:208-222) -- an arc of 9 holds one pixel of each of the four
+  // opposite pairs (0,8) (2,10) (4,12) (6,14), all darker than v - t (class bit 0) or all brighter than v + t (bit 1).
+  // The survivors are queued so that the next passes run on dense warps.
   for (int i = threadIdx.x; i < kFastSH * kFastSW; i += blockDim.x) {
     const int yy = i / kFastSW, xx = i % kFastSW;
     const int gx = tx0 - 1 + xx, gy = ty0 - 1 + yy;
-    int sc = 0;
+    s_score[yy][xx] = 0;
     if (gx >= 3 && gx < W - 3 && gy >= 3 && gy < H - 3) {  // fast.cpp:96, :206
       const uint8_t* c = &s_img[yy + 3][xx + 3];
-      const int v = c[0];
-      // an arc of 9 holds one pixel of every opposite pair: two quick rejections before the full ring
-      const int a0 = abs(v - c[3 * (kFastIW + 8)]), a8 = abs(v - c[-3 * (kFastIW + 8)]);
-      const int a4 = abs(v - c[3]), a12 = abs(v - c[-3]);
-      if (max(a0, a8) > p.threshold && max(a4, a12) > p.threshold) {
-        sc = fast_corner_score(c, kFastIW + 8, p.threshold);
-        if (sc < p.threshold) sc = 0;
+      const int v = c[0], thr = p.threshold;
+      int d = 3;
+#pragma unroll
+      for (int k = 0; k < 8; k += 2) {
+        const int r0 = c[ring_offset(k, kFastIW + 8)], r1 = c[ring_offset(k + 8, kFastIW + 8)];
+        const int c0 = (int)(v - r0 > thr) | ((int)(r0 - v > thr) << 1);
+        const int c1 = (int)(v - r1 > thr) | ((int)(r1 - v > thr) << 1);
+        d &= c0 | c1;
       }
+      if (d) s_queue[0][atomicAdd(&s_qn[0], 1)] = (uint16_t)i;
     }
-    s_score[yy][xx] = (uint8_t)sc;
+  }
+  __syncthreads();
+  // pass 1b: the full ring test
+  for (int q = threadIdx.x; q < s_qn[0]; q += blockDim.x) {
+    const int i = s_queue[0][q];
+    const int yy = i / kFastSW, xx = i % kFastSW;
+    if (fast_is_corner(&s_img[yy + 3][xx + 3], kFastIW + 8, p.threshold)) s_queue[1][atomicAdd(&s_qn[1], 1)] = (uint16_t)i;
+  }
+  __syncthreads();
+  // pass 2: the score
+  for (int q = threadIdx.x; q < s_qn[1]; q += blockDim.x) {
+    const int i = s_queue[1][q];
+    const int yy = i / kFastSW, xx = i % kFastSW;
+    const int sc = fast_corner_score(&s_img[yy + 3][xx + 3], kFastIW + 8);
+    s_score[yy][xx] = (uint8_t)(sc >= p.threshold ? sc : 0);
   }
   __syncthreads();
   const int edge = p.edge;
@@ -229,7 +263,8 @@ __device__ void bitonic_asc_u32_blk(uint32_t* keys, int n) {
 
 __global__ void __launch_bounds__(1024) orb_select_kernel(const SelectParams p) {
   __shared__ uint32_t s_keys[kMaxLevelKp];
-  __shared__ int s_thr, s_keep, s_cnt;
+  __shared__ int s_thr, s_cnt;
+  __shared__ uint32_t s_hist[256];
   const int img = blockIdx.x;
   int out = 0;
   int status = 0;
@@ -237,10 +272,12 @@ __global__ void __launch_bounds__(1024) orb_select_kernel(const SelectParams p) 
     const uint32_t raw = p.cand_cnt[img * kMaxLevels + l];
     const int n = (int)min(raw, (uint32_t)p.g.cand_cap[l]);
     if (raw > (uint32_t)p.g.cand_cap[l]) status |= 1;
+    if (threadIdx.x < 256) s_hist[threadIdx.x] = p.hist[((size_t)img * kMaxLevels + l) * 256 + threadIdx.x];
+    __syncthreads();
     if (threadIdx.x == 0) {
       // KeyPointsFilter::retainBest (keypoint.cpp:69-90): nothing to do unless there are more than n_points; then
       // everything whose response reaches the n_points-th largest stays
-      const uint32_t* h = p.hist + ((size_t)img * kMaxLevels + l) * 256;
+      const uint32_t* h = s_hist;
       int thr = 0;
       if (n > p.g.nper[l]) {
         if (p.g.nper[l] == 0) {
@@ -330,11 +367,11 @@ struct KpParams {
   float* kp;
   const int32_t* n_kp;
   uint8_t* desc;
+  float2* rot;          // [count][cap] (cos, sin) of the keypoint angle, written by the angle kernel
+  const char4* pattern;   // [256] sampling pairs (xa, ya, xb, yb)
+  unsigned long long umax;  // orb.cpp:860-878 for halfPatchSize 15, 4 bits per row
   int cap;
 };
-
-__constant__ int c_umax[16];   // orb.cpp:860-878 for halfPatchSize 15
-__constant__ int8_t c_pattern[256][4];
 
 __global__ void __launch_bounds__(256) orb_angle_kernel(const KpParams p) {
   const int lane = threadIdx.x & 31;
@@ -351,7 +388,7 @@ __global__ void __launch_bounds__(256) orb_angle_kernel(const KpParams p) {
   int m10 = 0, m01 = 0;
   if (lane < 31) {  // lane = row v + 15 of the disc
     const int v = lane - 15;
-    const int d = c_umax[abs(v)];
+    const int d = (int)((p.umax >> (4 * abs(v))) & 15ull);
     const uint8_t* r = c + v * pitch;
     int s = 0;
     for (int u = -d; u <= d; ++u) {
@@ -363,7 +400,14 @@ __global__ void __launch_bounds__(256) orb_angle_kernel(const KpParams p) {
   }
   m10 = __reduce_add_sync(0xFFFFFFFFu, m10);
   m01 = __reduce_add_sync(0xFFFFFFFFu, m01);
-  if (lane == 0) k[3] = fast_atan2_deg((float)m01, (float)m10);
+  if (lane == 0) {
+    const float deg = fast_atan2_deg((float)m01, (float)m10);
+    k[3] = deg;
+    // orb.cpp:231-232: angle *= (float)(CV_PI / 180.f); a = cosf(angle), b = sinf(angle) -- evaluated in double and
+    // rounded once
+    const float angle = __fmul_rn(deg, (float)(3.1415926535897932384626433832795 / 180.f));
+    p.rot[(size_t)img * p.cap + j] = make_float2((float)cos((double)angle), (float)sin((double)angle));
+  }
 }
 
 // ---- blur: separable 7-tap float filter, BORDER_REFLECT_101 ----------------------------------------------------------------
@@ -384,7 +428,7 @@ __device__ __forceinline__ int reflect101(int p, int len) {
 }
 
 __global__ void __launch_bounds__(256) orb_blur_kernel(const BlurParams p) {
-  __shared__ uint8_t s_img[kBlurTH + 6][kBlurTW + 8];
+  __shared__ float s_img[kBlurTH + 6][kBlurTW + 8];
   __shared__ float s_row[kBlurTH + 6][kBlurTW];
   const int img = blockIdx.y;
   int l = 0;
@@ -395,15 +439,17 @@ __global__ void __launch_bounds__(256) orb_blur_kernel(const BlurParams p) {
   const uint8_t* base = p.pyr + (size_t)img * p.g.slab + p.g.off[l];
   for (int i = threadIdx.x; i < (kBlurTH + 6) * (kBlurTW + 6); i += blockDim.x) {
     const int yy = i / (kBlurTW + 6), xx = i % (kBlurTW + 6);
-    s_img[yy][xx] = base[(size_t)reflect101(ty0 - 3 + yy, H) * pitch + reflect101(tx0 - 3 + xx, W)];
+    // u8 -> f32 once per tile pixel, on the ALU/FMA pipes: the byte in the mantissa of 2^23, minus 2^23
+    const uint32_t b = base[(size_t)reflect101(ty0 - 3 + yy, H) * pitch + reflect101(tx0 - 3 + xx, W)];
+    s_img[yy][xx] = __fsub_rn(__uint_as_float(0x4B000000u | b), 8388608.f);
   }
   __syncthreads();
   // RowFilter<uchar, float>: s = k[0] * p[0]; s += k[i] * p[i], left to right (fused)
   for (int i = threadIdx.x; i < (kBlurTH + 6) * kBlurTW; i += blockDim.x) {
     const int yy = i / kBlurTW, xx = i % kBlurTW;
-    float s = __fmul_rn(p.k7[0], (float)s_img[yy][xx]);
+    float s = __fmul_rn(p.k7[0], s_img[yy][xx]);
 #pragma unroll
-    for (int q = 1; q < 7; ++q) s = __fmaf_rn(p.k7[q], (float)s_img[yy][xx + q], s);
+    for (int q = 1; q < 7; ++q) s = __fmaf_rn(p.k7[q], s_img[yy][xx + q], s);
     s_row[yy][xx] = s;
   }
   __syncthreads();
@@ -420,8 +466,21 @@ __global__ void __launch_bounds__(256) orb_blur_kernel(const BlurParams p) {
   }
 }
 
+// cvRound for |x| < 2^22 on the FMA/ALU pipes: adding 1.5 * 2^23 leaves the nearest-even integer in the mantissa
+__device__ __forceinline__ int round_small(float x) {
+  return __float_as_int(__fadd_rn(x, 12582912.f)) - 0x4B400000;
+}
+
 // ---- descriptors: one warp per keypoint, lane = descriptor byte ---------------------------------------------------------------
 __global__ void __launch_bounds__(256) orb_describe_kernel(const KpParams p) {
+  // the sampling pattern, transposed: s_pat[bit][lane] = pair 8 * lane + bit (lane-indexed reads of __constant__
+  // memory serialise 32-fold: 2.8 ms per 256 images before, measured)
+  __shared__ float4 s_pat[8][32];
+  {
+    const char4 q = p.pattern[8 * (threadIdx.x & 31) + (threadIdx.x >> 5)];
+    s_pat[threadIdx.x >> 5][threadIdx.x & 31] = make_float4((float)q.x, (float)q.y, (float)q.z, (float)q.w);
+  }
+  __syncthreads();
   const int lane = threadIdx.x & 31;
   const int j = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int img = blockIdx.y;
@@ -432,19 +491,19 @@ __global__ void __launch_bounds__(256) orb_describe_kernel(const KpParams p) {
   const int x = __float2int_rn(__fmul_rn(k[0], inv)), y = __float2int_rn(__fmul_rn(k[1], inv));
   const int pitch = p.g.pitch[l];
   const uint8_t* c = p.pyr + (size_t)img * p.g.slab + p.g.off[l] + (size_t)y * pitch + x;
-  // angle *= (float)(CV_PI / 180.f); a = cosf(angle), b = sinf(angle): evaluated in double and rounded once
-  const float angle = __fmul_rn(k[3], (float)(3.1415926535897932384626433832795 / 180.f));
-  const float a = (float)cos((double)angle), b = (float)sin((double)angle);
+  const float2 ab = p.rot[(size_t)img * p.cap + j];
+  const float a = ab.x, b = ab.y;
   int val = 0;
 #pragma unroll
   for (int bit = 0; bit < 8; ++bit) {
-    const int8_t* q = c_pattern[8 * lane + bit];
-    const float xa = __fsub_rn(__fmul_rn((float)q[0], a), __fmul_rn((float)q[1], b));
-    const float ya = __fadd_rn(__fmul_rn((float)q[0], b), __fmul_rn((float)q[1], a));
-    const float xb = __fsub_rn(__fmul_rn((float)q[2], a), __fmul_rn((float)q[3], b));
-    const float yb = __fadd_rn(__fmul_rn((float)q[2], b), __fmul_rn((float)q[3], a));
-    const int t0 = c[__float2int_rn(ya) * pitch + __float2int_rn(xa)];
-    const int t1 = c[__float2int_rn(yb) * pitch + __float2int_rn(xb)];
+    const float4 q = s_pat[bit][lane];
+    const float qx = q.x, qy = q.y, qz = q.z, qw = q.w;
+    const float xa = __fsub_rn(__fmul_rn(qx, a), __fmul_rn(qy, b));
+    const float ya = __fadd_rn(__fmul_rn(qx, b), __fmul_rn(qy, a));
+    const float xb = __fsub_rn(__fmul_rn(qz, a), __fmul_rn(qw, b));
+    const float yb = __fadd_rn(__fmul_rn(qz, b), __fmul_rn(qw, a));
+    const int t0 = c[round_small(ya) * pitch + round_small(xa)];
+    const int t1 = c[round_small(yb) * pitch + round_small(xb)];
     val |= (t0 < t1) << bit;
   }
   p.desc[((size_t)img * p.cap + j) * 32 + lane] = (uint8_t)val;
@@ -539,17 +598,19 @@ int launch_orb(vslam_ctx* ctx, const uint8_t* images_dev, int count, int w, int 
   const size_t o_hist = ((size_t)count * kMaxLevels * 4 + 255) & ~(size_t)255;
   const size_t o_nkp = o_hist + (size_t)count * kMaxLevels * 256 * 4;
   const size_t o_status = o_nkp + (((size_t)count * 4 + 255) & ~(size_t)255);
-  const size_t o_tab = o_status + (((size_t)count * 4 + 255) & ~(size_t)255);
+  const size_t o_pat = o_status + (((size_t)count * 4 + 255) & ~(size_t)255);
+  const size_t o_tab = o_pat + 1024;
   VS_CUDA(ctx, b_misc.reserve(o_tab + tab.size() * 2 + 256));
   VS_CUDA(ctx, b_kp.reserve((size_t)count * cap * 6 * 4));
   VS_CUDA(ctx, b_desc.reserve((size_t)count * cap * 32));
+  VS_CUDA(ctx, ctx->orb[7].reserve((size_t)count * cap * 8));
   uint8_t* misc = b_misc.as<uint8_t>();
   cudaStream_t st = ctx->stream;
   VS_CUDA(ctx, cudaMemsetAsync(misc, 0, o_nkp, st));  // candidate counters and histograms
   if (!tab.empty()) VS_CUDA(ctx, cudaMemcpyAsync(misc + o_tab, tab.data(), tab.size() * 2, cudaMemcpyHostToDevice, st));
-  static bool tables_done[64] = {};
-  if (ctx->device < 64 && !tables_done[ctx->device]) {
-    // umax of the radius-15 disc (orb.cpp:860-878) and the sampling pattern
+  // umax of the radius-15 disc (orb.cpp:860-878), 4 bits per row, and the sampling pattern (behind the resize tables)
+  unsigned long long umax_packed = 0;
+  {
     int umax[17];
     const int half = 15;
     int v, v0;
@@ -560,13 +621,12 @@ int launch_orb(vslam_ctx* ctx, const uint8_t* images_dev, int count, int w, int 
       umax[v] = v0;
       ++v0;
     }
-    static const int8_t pattern[256][4] = {
-#include "rbrief_pattern.inc"
-    };
-    VS_CUDA(ctx, cudaMemcpyToSymbol(c_umax, umax, 16 * sizeof(int)));
-    VS_CUDA(ctx, cudaMemcpyToSymbol(c_pattern, pattern, sizeof pattern));
-    tables_done[ctx->device] = true;
+    for (v = 0; v <= half; ++v) umax_packed |= (unsigned long long)umax[v] << (4 * v);
   }
+  static const int8_t pattern[256][4] = {
+#include "rbrief_pattern.inc"
+  };
+  VS_CUDA(ctx, cudaMemcpyAsync(misc + o_pat, pattern, sizeof pattern, cudaMemcpyHostToDevice, st));
   uint8_t* pyr = b_pyr.as<uint8_t>();
   orb_copy_level0_kernel<<<dim3((w + 255) / 256, h, count), 256, 0, st>>>(images_dev, w, h, pitch, stride, g, pyr);
   ctx->launches += 1;
@@ -627,6 +687,9 @@ int launch_orb(vslam_ctx* ctx, const uint8_t* images_dev, int count, int w, int 
   kp.kp = sp.kp;
   kp.n_kp = sp.n_kp;
   kp.desc = b_desc.as<uint8_t>();
+  kp.rot = ctx->orb[7].as<float2>();
+  kp.pattern = reinterpret_cast<const char4*>(misc + o_pat);
+  kp.umax = umax_packed;
   kp.cap = cap;
   orb_angle_kernel<<<dim3((cap + 7) / 8, count), 256, 0, st>>>(kp);
   orb_blur_kernel<<<dim3(tb, count), 256, 0, st>>>(bp);
