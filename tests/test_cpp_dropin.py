@@ -153,3 +153,65 @@ def test_keyframe_store_header():
     p = subprocess.run([EXE_STORE], capture_output=True, text=True)
     assert p.returncode == 0 and p.stdout.startswith("ok 7 jobs"), p.stdout[-400:] + p.stderr[-400:]
     assert int(p.stdout.split()[3]) > 1000
+
+
+EXE_BOW = os.path.join(ROOT, "tests", "cpp", "test_dropin_bow")
+
+
+def _build_bow():
+    cmd = ["g++", "-std=c++14", "-O2", "-I", os.path.join(ROOT, "tests", "cpp", "stubs"), "-I", os.path.join(ROOT, "include"),
+           "-o", EXE_BOW, os.path.join(ROOT, "tests", "cpp", "test_dropin_bow.cpp"), "-L",
+           os.path.join(ROOT, "visual-slam_b200", "csrc"), "-lvisnav_b200",
+           "-Wl,-rpath," + os.path.join(ROOT, "visual-slam_b200", "csrc")]
+    subprocess.run(cmd, check=True)
+
+
+def test_bow_header_compiles_and_fails_loudly_without_gpu():
+    import torch
+    _build_bow()
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    p = subprocess.run([EXE_BOW], capture_output=True, text=True)
+    assert p.returncode == 3 and "no usable sm_100 GPU" in p.stdout
+
+
+@pytest.mark.gpu
+def test_bow_header(tmp_path):
+    """include/visnav/bow_b200.h driven from C++ (Vocabulary::loadFromTextFile, compute_bow_vector, score,
+    BowDatabase) == the CPU oracles: cv::ORB restatement -> DBoW2 restatement on the same images."""
+    from oracle import oracle as oo
+    from visnav_b200 import workloads as wl
+    _build_bow()
+    voc = wl.synth_vocabulary(8, 3, 13, stop=0.05)
+    vpath = os.path.join(str(tmp_path), "voc.txt")
+    wl.write_vocabulary_text(vpath, voc, trailing_newline=True)
+    imgs = np.stack([wl.synth_image(700 + i, 320, 240) for i in range(3)] + [np.roll(wl.synth_image(700, 320, 240), -9, 1)])
+    ipath = os.path.join(str(tmp_path), "imgs.bin")
+    imgs.tofile(ipath)
+    p = subprocess.run([EXE_BOW, vpath, "320", "240", str(len(imgs)), ipath], capture_output=True, text=True)
+    assert p.returncode == 0, p.stdout[-400:] + p.stderr[-400:]
+    lines = p.stdout.strip().split("\n")
+    assert lines[0] == "voc 8 3 512"
+    o = oo.BowVocab.from_text(vpath)
+    want = []
+    for i, img in enumerate(imgs):
+        kp, desc = oo.orb_detect_compute(img, 1500)
+        ids, vals, fw, fn, fwt = o.transform(desc, 4)
+        want.append((ids, vals))
+        tag, nw, total, nnodes, listed = lines[1 + i].split()
+        assert tag == "v" and int(nw) == len(ids) and int(listed) == int((fwt > 0).sum())
+        assert int(nnodes) == len(set(fn[fwt > 0]))        # levelsup 4 > L = 3: every feature sits under the root (node 0)
+        s = 0.0
+        for x in vals:
+            s += x
+        assert float(total) == s
+    n = len(imgs)
+    scores = np.array([[o.score(a, b) for b in want] for a in want])
+    got = np.array([[float(x) for x in lines[1 + n + i].split()[1:]] for i in range(n)])
+    assert np.array_equal(got.view(np.uint64), scores.view(np.uint64))
+    for i in range(n):
+        q = np.array([float(x) for x in lines[1 + 2 * n + 2 * i].split()[1:]])
+        c = [int(x) for x in lines[2 + 2 * n + 2 * i].split()[1:]]
+        assert np.array_equal(q.view(np.uint64), scores[i].view(np.uint64))
+        assert c == [len(np.intersect1d(want[i][0], b[0])) for b in want]
+    assert scores[0, 3] > scores[0, 1] and scores[0, 3] > scores[0, 2]     # the shifted view of image 0 scores highest

@@ -79,9 +79,11 @@ __global__ void orb_resize_kernel(OrbGeom g, int l, const ushort2* tab, uint8_t*
 }
 
 // ---- FAST-9/16 score + 3x3 non-maximum suppression + border filter -------------------------------------------------
-constexpr int kFastTW = 64, kFastTH = 16;             // outputs per CTA
-constexpr int kFastIW = kFastTW + 8, kFastIH = kFastTH + 8;  // image tile: 1 (NMS halo) + 3 (ring) on every side
-constexpr int kFastSW = kFastTW + 2, kFastSH = kFastTH + 2;  // score tile
+constexpr int kFastTW = 62, kFastTH = 16;                     // outputs per CTA
+constexpr int kFastSW = kFastTW + 2, kFastSH = kFastTH + 2;   // score tile (1 px NMS halo): 64 wide = two lane passes
+constexpr int kFastIH = kFastTH + 8;                          // image tile rows: + 3 (ring) on every side
+constexpr int kFastIP = 80;                                   // image tile row pitch: 19 words + padding
+constexpr int kFastWords = 19;                                // 62 + 8 columns + up to 3 of alignment slack
 
 __device__ __forceinline__ int ring_offset(int k, int pitch) {
   // fast_score.cpp:52-56: (dx, dy) of ring pixel k
@@ -90,56 +92,47 @@ __device__ __forceinline__ int ring_offset(int k, int pitch) {
   return dx[k] + dy[k] * pitch;
 }
 
-// 9 contiguous set bits in the 16-bit ring mask (cyclic)?
-__device__ __forceinline__ bool has_arc9(uint32_t m) {
-  m |= m << 16;
-  uint32_t x = m & (m >> 1);
-  x &= x >> 2;
-  x &= x >> 4;      // bit i: 8 contiguous from i
-  x &= m >> 8;      // 9 contiguous
-  return (x & 0xFFFFu) != 0;
-}
-
-// corner test of FAST_t<16> (fast.cpp:206-262) as two 16-bit ring masks
-__device__ __forceinline__ bool fast_is_corner(const uint8_t* p, int pitch, int threshold) {
-  const int v = p[0];
-  uint32_t bright_m = 0, dark_m = 0;
+// High-speed rejection (fast.cpp:208-222) on the raw ring values: an arc of 9 holds one pixel of each opposite pair
+// (k, k + 8), k = 0, 2, 4, 6.  All-darker needs min(r_k, r_k+8) < v - t for every pair, all-brighter max(...) > v + t.
+__device__ __forceinline__ bool fast_pretest(const uint8_t* c, int thr) {
+  const int v = c[0];
+  int lo = 0, hi = 255;  // max over pairs of the pair minimum, min over pairs of the pair maximum
 #pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    const int d = v - (int)p[ring_offset(k, pitch)];
-    dark_m |= (uint32_t)(d > threshold) << k;     // ring pixel darker than v - t
-    bright_m |= (uint32_t)(d < -threshold) << k;  // brighter than v + t
+  for (int k = 0; k < 8; k += 2) {
+    const int r0 = c[ring_offset(k, kFastIP)], r1 = c[ring_offset(k + 8, kFastIP)];
+    lo = max(lo, min(r0, r1));
+    hi = min(hi, max(r0, r1));
   }
-  return has_arc9(bright_m) || has_arc9(dark_m);
+  return (v - lo > thr) | (hi - v > thr);
 }
 
-__device__ int fast_corner_score(const uint8_t* p, int pitch) {
-  const int v = p[0];
-  int d[16];
+// Corner test and score in one: with A = min over the 16 arcs of (max ring value of the arc) and B = max over the arcs
+// of (min ring value), the pixel is a corner at threshold t iff v - A > t (an all-darker arc) or B - v > t (an
+// all-brighter arc), and cornerScore<16> (fast_score.cpp:119-215) = max(v - A, B - v) - 1.  Arc extrema by doubling:
+// windows of 2, 4, 8 ring pixels, then the ninth.  The two sides are kept apart down to the last line: nvcc 12.9
+// miscompiles the per-arc form max(best, max(arc_min_d, -arc_max_d)) for sm_100a (tools/probes/t_fast2.cu).
+__device__ int fast_corner_score(const uint8_t* c) {
+  int r[16], lo[16], hi[16], t1[16], t2[16];
 #pragma unroll
-  for (int k = 0; k < 16; ++k) d[k] = v - (int)p[ring_offset(k, pitch)];
-  // score = max over the 16 arcs of min(d) and of min(-d), minus 1 (cornerScore<16>); arc minima / maxima by doubling:
-  // windows of 2, 4, 8 ring pixels, then the ninth
-  int lo[16], hi[16], t1[16], t2[16];
+  for (int k = 0; k < 16; ++k) r[k] = c[ring_offset(k, kFastIP)];
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
-    lo[k] = min(d[k], d[(k + 1) & 15]);
-    hi[k] = max(d[k], d[(k + 1) & 15]);
+    lo[k] = min(r[k], r[(k + 1) & 15]);
+    hi[k] = max(r[k], r[(k + 1) & 15]);
   }
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
     t1[k] = min(lo[k], lo[(k + 2) & 15]);
     t2[k] = max(hi[k], hi[(k + 2) & 15]);
   }
-  // The two sides are accumulated apart (as OpenCV's q0 / q1): nvcc 12.9 miscompiles the per-arc form
-  // best = max(best, max(mn, -mx)) for sm_100a (it returns max |d| - 1; tools/probes/t_fast2.cu shows it).
-  int dark = -1000, bright = 1000;
+  int a = 255, b = 0;
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
-    dark = max(dark, min(min(t1[k], t1[(k + 4) & 15]), d[(k + 8) & 15]));
-    bright = min(bright, max(max(t2[k], t2[(k + 4) & 15]), d[(k + 8) & 15]));
+    a = min(a, max(max(t2[k], t2[(k + 4) & 15]), r[(k + 8) & 15]));
+    b = max(b, min(min(t1[k], t1[(k + 4) & 15]), r[(k + 8) & 15]));
   }
-  return max(dark, -bright) - 1;
+  const int v = c[0];
+  return max(v - a, b - v) - 1;
 }
 
 struct FastParams {
@@ -153,75 +146,60 @@ struct FastParams {
 };
 
 __global__ void __launch_bounds__(256) orb_fast_kernel(const FastParams p) {
-  __shared__ __align__(16) uint8_t s_img[kFastIH][kFastIW + 8];
-  __shared__ uint8_t s_score[kFastSH][kFastSW + 2];
-  __shared__ uint16_t s_queue[2][kFastSH * kFastSW];
-  __shared__ int s_qn[2];
+  __shared__ __align__(16) uint8_t s_img[kFastIH][kFastIP];
+  __shared__ uint8_t s_score[kFastSH][kFastSW + 4];
+  __shared__ uint16_t s_queue[kFastSH * kFastSW];
+  __shared__ int s_qn;
   const int img = blockIdx.y;
-  if (threadIdx.x < 2) s_qn[threadIdx.x] = 0;
+  if (threadIdx.x == 0) s_qn = 0;
   int l = 0;
   while (l + 1 < p.g.nlevels && (int)blockIdx.x >= p.tile_first[l + 1]) ++l;
   const int t = blockIdx.x - p.tile_first[l];
   const int tx0 = (t % p.tiles_x[l]) * kFastTW, ty0 = (t / p.tiles_x[l]) * kFastTH;
   const int W = p.g.w[l], H = p.g.h[l], pitch = p.g.pitch[l];
   const uint8_t* base = p.pyr + (size_t)img * p.g.slab + p.g.off[l];
-  // the image tile by 32-bit words: tile columns start at a multiple of 4 and the row pitch is a multiple of 16, so
-  // a word lies entirely inside [0, pitch) or entirely outside (bytes between W and pitch are never used below)
-  constexpr int kWords = kFastIW / 4;
-  for (int i = threadIdx.x; i < kFastIH * kWords; i += blockDim.x) {
-    const int yy = i / kWords, wx = i % kWords;
-    const int gx = tx0 - 4 + 4 * wx, gy = ty0 - 4 + yy;
+  // the image tile by aligned 32-bit words (the row pitch is a multiple of 16, so a word lies entirely inside
+  // [0, pitch) or entirely outside; bytes between W and pitch are never used below).  Tile column of image x:
+  // x - gxb; score-tile position xx sits at image x = tx0 - 1 + xx, i.e. tile column xx + 3 + xoff.
+  const int gxb = (tx0 - 4) & ~3;
+  const int xoff = (tx0 - 4) - gxb;
+  for (int i = threadIdx.x; i < kFastIH * 32; i += blockDim.x) {
+    const int yy = i >> 5, wx = i & 31;
+    if (wx >= kFastWords) continue;
+    const int gx = gxb + 4 * wx, gy = ty0 - 4 + yy;
     uint32_t word = 0;
     if (gx >= 0 && gx < pitch && gy >= 0 && gy < H) word = *reinterpret_cast<const uint32_t*>(base + (size_t)gy * pitch + gx);
     *reinterpret_cast<uint32_t*>(&s_img[yy][4 * wx]) = word;
   }
   __syncthreads();
-  // pass 1a: OpenCV's high-speed rejection (fast.cpp:208-222) -- an arc of 9 holds one pixel of each of the four
-  // opposite pairs (0,8) (2,10) (4,12) (6,14), all darker than v - t (class bit 0) or all brighter than v + t (bit 1).
-  // The survivors are queued so that the next passes run on dense warps.
+  // pass 1: the high-speed rejection for every position; survivors are queued so that pass 2 runs on dense warps
   for (int i = threadIdx.x; i < kFastSH * kFastSW; i += blockDim.x) {
-    const int yy = i / kFastSW, xx = i % kFastSW;
+    const int yy = i >> 6, xx = i & 63;
     const int gx = tx0 - 1 + xx, gy = ty0 - 1 + yy;
     s_score[yy][xx] = 0;
-    if (gx >= 3 && gx < W - 3 && gy >= 3 && gy < H - 3) {  // fast.cpp:96, :206
-      const uint8_t* c = &s_img[yy + 3][xx + 3];
-      const int v = c[0], thr = p.threshold;
-      int d = 3;
-#pragma unroll
-      for (int k = 0; k < 8; k += 2) {
-        const int r0 = c[ring_offset(k, kFastIW + 8)], r1 = c[ring_offset(k + 8, kFastIW + 8)];
-        const int c0 = (int)(v - r0 > thr) | ((int)(r0 - v > thr) << 1);
-        const int c1 = (int)(v - r1 > thr) | ((int)(r1 - v > thr) << 1);
-        d &= c0 | c1;
-      }
-      if (d) s_queue[0][atomicAdd(&s_qn[0], 1)] = (uint16_t)i;
-    }
+    if (gx >= 3 && gx < W - 3 && gy >= 3 && gy < H - 3 &&  // fast.cpp:96, :206
+        fast_pretest(&s_img[yy + 3][xx + 3 + xoff], p.threshold))
+      s_queue[atomicAdd(&s_qn, 1)] = (uint16_t)i;
   }
   __syncthreads();
-  // pass 1b: the full ring test
-  for (int q = threadIdx.x; q < s_qn[0]; q += blockDim.x) {
-    const int i = s_queue[0][q];
-    const int yy = i / kFastSW, xx = i % kFastSW;
-    if (fast_is_corner(&s_img[yy + 3][xx + 3], kFastIW + 8, p.threshold)) s_queue[1][atomicAdd(&s_qn[1], 1)] = (uint16_t)i;
-  }
-  __syncthreads();
-  // pass 2: the score
-  for (int q = threadIdx.x; q < s_qn[1]; q += blockDim.x) {
-    const int i = s_queue[1][q];
-    const int yy = i / kFastSW, xx = i % kFastSW;
-    const int sc = fast_corner_score(&s_img[yy + 3][xx + 3], kFastIW + 8);
-    s_score[yy][xx] = (uint8_t)(sc >= p.threshold ? sc : 0);
+  // pass 2: ring test and score
+  for (int q = threadIdx.x; q < s_qn; q += blockDim.x) {
+    const int i = s_queue[q];
+    const int yy = i >> 6, xx = i & 63;
+    const int sc = fast_corner_score(&s_img[yy + 3][xx + 3 + xoff]);
+    if (sc >= p.threshold) s_score[yy][xx] = (uint8_t)sc;
   }
   __syncthreads();
   const int edge = p.edge;
   if (H <= 2 * edge || W <= 2 * edge) return;  // runByImageBorder clears everything (keypoint.cpp:109-110)
-  for (int i = threadIdx.x; i < kFastTH * kFastTW; i += blockDim.x) {
-    const int yy = i / kFastTW, xx = i % kFastTW;
+  for (int i = threadIdx.x; i < kFastTH * 64; i += blockDim.x) {
+    const int yy = i >> 6, xx = i & 63;
+    if (xx >= kFastTW) continue;
     const int gx = tx0 + xx, gy = ty0 + yy;
     const int v = s_score[yy + 1][xx + 1];
     if (v == 0 || gx < edge || gx >= W - edge || gy < edge || gy >= H - edge) continue;
     const uint8_t* s = &s_score[yy + 1][xx + 1];
-    constexpr int sp = kFastSW + 2;
+    constexpr int sp = kFastSW + 4;
     if (v > s[1] && v > s[-1] && v > s[-sp - 1] && v > s[-sp] && v > s[-sp + 1] && v > s[sp - 1] && v > s[sp] &&
         v > s[sp + 1]) {
       const uint32_t pos = atomicAdd(p.cand_cnt + img * kMaxLevels + l, 1u);
