@@ -315,7 +315,7 @@ typedef struct {
   int nfeatures;
   float scale_factor; /* 1.2f */
   int nlevels;        /* 8; at most 8 */
-  int edge_threshold; /* 19 */
+  int edge_threshold; /* 19; at least 19 (the reach of the rotated sampling pattern) */
   int fast_threshold; /* 20 */
 } vslam_orb_params;
 int vslam_orb_detect_compute_batch(vslam_ctx* ctx, const uint8_t* images, int count, int w, int h, int pitch,

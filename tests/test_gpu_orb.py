@@ -75,6 +75,8 @@ def test_parameters_and_degenerate_images(ctx):
         ctx.orb_detect_compute_batch(noise, 400, cap=100)
     with pytest.raises(VslamError):
         ctx.orb_detect_compute_batch(noise, params=OrbParams(400, 1.2, 9, 19, 20))
+    with pytest.raises(VslamError):                            # the sampling pattern reaches 18 px
+        ctx.orb_detect_compute_batch(noise, params=OrbParams(400, 1.2, 8, 18, 20))
 
 
 def test_compute_bow_vector_is_orb_then_transform(ctx):

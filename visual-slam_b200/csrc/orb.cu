@@ -519,9 +519,11 @@ int launch_orb(vslam_ctx* ctx, const uint8_t* images_dev, int count, int w, int 
                const vslam_orb_params* prm, int cap, OrbDeviceOut* out) {
   if (prm->nlevels < 1 || prm->nlevels > kMaxLevels) return vs_fail(ctx, VSLAM_E_LIMIT, "ORB: 1..8 pyramid levels");
   if (w >= 4096 || h >= 4096) return vs_fail(ctx, VSLAM_E_LIMIT, "ORB: images up to 4095 x 4095");
-  if (prm->nfeatures < 0 || prm->edge_threshold < 16 || prm->fast_threshold < 1 || prm->fast_threshold > 254 ||
+  // edge_threshold >= 19: the rotated sampling pattern reaches 18 px (13 * sqrt(2), rounded) and the levels carry no
+  // border here (OpenCV keeps 32 px of reflected, unblurred pixels around each level; the reference passes 19)
+  if (prm->nfeatures < 0 || prm->edge_threshold < 19 || prm->fast_threshold < 1 || prm->fast_threshold > 254 ||
       !(prm->scale_factor > 1.f))
-    return vs_fail(ctx, VSLAM_E_ARG, "ORB: nfeatures >= 0, edge_threshold >= 16 (patch radius), 1 <= fast_threshold <= 254, scale_factor > 1");
+    return vs_fail(ctx, VSLAM_E_ARG, "ORB: nfeatures >= 0, edge_threshold >= 19 (pattern reach), 1 <= fast_threshold <= 254, scale_factor > 1");
   OrbGeom g;
   memset(&g, 0, sizeof g);
   g.nlevels = prm->nlevels;
