@@ -405,9 +405,18 @@ __device__ __forceinline__ int reflect101(int p, int len) {
   return p;
 }
 
+// u8 -> f32 on the ALU/FMA pipes: the byte in the mantissa of 2^23, minus 2^23
+__device__ __forceinline__ float byte_f32(uint32_t word, int k) {
+  return __fsub_rn(__uint_as_float(__byte_perm(word, 0x4B000000u, 0x7540u + k)), 8388608.f);
+}
+
+// One CTA = 64 x 16 output pixels.  The input tile (22 rows x 72 columns, image x = x0 - 4 ...) is converted to float
+// once; interior tiles fetch it by aligned words, tiles that touch an image edge pixel by pixel through the reflection.
+// Row pass: 4 adjacent outputs per item from three float4 loads; column pass: 4 adjacent outputs per thread from
+// seven float4 loads, stored as one 32-bit word.
 __global__ void __launch_bounds__(256) orb_blur_kernel(const BlurParams p) {
-  __shared__ float s_img[kBlurTH + 6][kBlurTW + 8];
-  __shared__ float s_row[kBlurTH + 6][kBlurTW];
+  __shared__ __align__(16) float s_in[kBlurTH + 6][72];
+  __shared__ __align__(16) float s_row[kBlurTH + 6][kBlurTW];
   const int img = blockIdx.y;
   int l = 0;
   while (l + 1 < p.g.nlevels && (int)blockIdx.x >= p.tile_first[l + 1]) ++l;
@@ -415,32 +424,62 @@ __global__ void __launch_bounds__(256) orb_blur_kernel(const BlurParams p) {
   const int tx0 = (t % p.tiles_x[l]) * kBlurTW, ty0 = (t / p.tiles_x[l]) * kBlurTH;
   const int W = p.g.w[l], H = p.g.h[l], pitch = p.g.pitch[l];
   const uint8_t* base = p.pyr + (size_t)img * p.g.slab + p.g.off[l];
-  for (int i = threadIdx.x; i < (kBlurTH + 6) * (kBlurTW + 6); i += blockDim.x) {
-    const int yy = i / (kBlurTW + 6), xx = i % (kBlurTW + 6);
-    // u8 -> f32 once per tile pixel, on the ALU/FMA pipes: the byte in the mantissa of 2^23, minus 2^23
-    const uint32_t b = base[(size_t)reflect101(ty0 - 3 + yy, H) * pitch + reflect101(tx0 - 3 + xx, W)];
-    s_img[yy][xx] = __fsub_rn(__uint_as_float(0x4B000000u | b), 8388608.f);
+  const bool interior = tx0 >= 4 && tx0 + 67 < W && ty0 >= 3 && ty0 + kBlurTH + 2 < H;  // warp-uniform
+  if (interior) {
+    for (int i = threadIdx.x; i < (kBlurTH + 6) * 32; i += blockDim.x) {
+      const int yy = i >> 5, wx = i & 31;
+      if (wx >= 18) continue;
+      const uint32_t word = *reinterpret_cast<const uint32_t*>(base + (size_t)(ty0 - 3 + yy) * pitch + tx0 - 4 + 4 * wx);
+      *reinterpret_cast<float4*>(&s_in[yy][4 * wx]) =
+          make_float4(byte_f32(word, 0), byte_f32(word, 1), byte_f32(word, 2), byte_f32(word, 3));
+    }
+  } else {
+    for (int i = threadIdx.x; i < (kBlurTH + 6) * 72; i += blockDim.x) {
+      const int yy = i / 72, xx = i % 72;
+      const uint32_t b = base[(size_t)reflect101(ty0 - 3 + yy, H) * pitch + reflect101(tx0 - 4 + xx, W)];
+      s_in[yy][xx] = byte_f32(b, 0);
+    }
   }
   __syncthreads();
-  // RowFilter<uchar, float>: s = k[0] * p[0]; s += k[i] * p[i], left to right (fused)
-  for (int i = threadIdx.x; i < (kBlurTH + 6) * kBlurTW; i += blockDim.x) {
-    const int yy = i / kBlurTW, xx = i % kBlurTW;
-    float s = __fmul_rn(p.k7[0], s_img[yy][xx]);
+  // RowFilter<uchar, float>: s = k[0] * p[0]; s += k[i] * p[i], left to right (fused); output x reads inputs x-3..x+3
+  // = tile columns x + 1 .. x + 7
+  for (int i = threadIdx.x; i < (kBlurTH + 6) * 16; i += blockDim.x) {
+    const int yy = i >> 4, g = i & 15;
+    const float4 a = *reinterpret_cast<const float4*>(&s_in[yy][4 * g]);
+    const float4 b = *reinterpret_cast<const float4*>(&s_in[yy][4 * g + 4]);
+    const float4 c = *reinterpret_cast<const float4*>(&s_in[yy][4 * g + 8]);
+    const float in[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w};
+    float o[4];
 #pragma unroll
-    for (int q = 1; q < 7; ++q) s = __fmaf_rn(p.k7[q], s_img[yy][xx + q], s);
-    s_row[yy][xx] = s;
+    for (int j = 0; j < 4; ++j) {
+      float s = __fmul_rn(p.k7[0], in[j + 1]);
+#pragma unroll
+      for (int q = 1; q < 7; ++q) s = __fmaf_rn(p.k7[q], in[j + 1 + q], s);
+      o[j] = s;
+    }
+    *reinterpret_cast<float4*>(&s_row[yy][4 * g]) = make_float4(o[0], o[1], o[2], o[3]);
   }
   __syncthreads();
   // SymmColumnFilter: s = k[3] * r[0] + delta (0); s += k[3 + j] * (r[+j] + r[-j]); Cast<float, uchar> = cvRound, saturate
-  uint8_t* out = p.blur + (size_t)img * p.g.slab + p.g.off[l];
-  for (int i = threadIdx.x; i < kBlurTH * kBlurTW; i += blockDim.x) {
-    const int yy = i / kBlurTW, xx = i % kBlurTW;
-    const int gx = tx0 + xx, gy = ty0 + yy;
-    if (gx >= W || gy >= H) continue;
-    float s = __fmaf_rn(p.k7[3], s_row[yy + 3][xx], 0.f);
+  {
+    const int yy = threadIdx.x >> 4, g = threadIdx.x & 15;
+    const int gx = tx0 + 4 * g, gy = ty0 + yy;
+    if (gx < pitch && gy < H) {
+      float4 r[7];
 #pragma unroll
-    for (int j = 1; j <= 3; ++j) s = __fmaf_rn(p.k7[3 + j], __fadd_rn(s_row[yy + 3 + j][xx], s_row[yy + 3 - j][xx]), s);
-    out[(size_t)gy * pitch + gx] = (uint8_t)min(max(__float2int_rn(s), 0), 255);
+      for (int j = 0; j < 7; ++j) r[j] = *reinterpret_cast<const float4*>(&s_row[yy + j][4 * g]);
+      uint32_t word = 0;
+#pragma unroll
+      for (int cmp = 0; cmp < 4; ++cmp) {
+        const float v[7] = {(&r[0].x)[cmp], (&r[1].x)[cmp], (&r[2].x)[cmp], (&r[3].x)[cmp],
+                            (&r[4].x)[cmp], (&r[5].x)[cmp], (&r[6].x)[cmp]};
+        float s = __fmaf_rn(p.k7[3], v[3], 0.f);
+#pragma unroll
+        for (int j = 1; j <= 3; ++j) s = __fmaf_rn(p.k7[3 + j], __fadd_rn(v[3 + j], v[3 - j]), s);
+        word |= (uint32_t)min(max(__float2int_rn(s), 0), 255) << (8 * cmp);
+      }
+      *reinterpret_cast<uint32_t*>(p.blur + (size_t)img * p.g.slab + p.g.off[l] + (size_t)gy * pitch + gx) = word;
+    }
   }
 }
 
