@@ -574,23 +574,14 @@ int vslam_bow_transform_batch(vslam_ctx* ctx, vslam_bow_vocab* v, const uint8_t*
   return VSLAM_OK;
 }
 
-// visnav::compute_bow_vector (keypoints.h:243-254) for a batch: ORB (orb.cu) -> descent -> BowVector, all on the device
-int vslam_compute_bow_vector_batch(vslam_ctx* ctx, vslam_bow_vocab* v, const uint8_t* images, int count, int w, int h,
-                                   int pitch, size_t image_stride, const vslam_orb_params* prm, int levelsup,
-                                   uint32_t* bow_ids, double* bow_vals, int32_t* n_bow, int bow_cap, float* kp,
-                                   uint8_t* desc, int32_t* n_kp, uint32_t* feat_node, double* feat_weight, int cap) {
-  if (!ctx) return VSLAM_E_ARG;
-  if (!v || v->ctx != ctx || !images || !prm || count < 0 || w <= 0 || h <= 0 || pitch < w || cap <= 0 || bow_cap <= 0 ||
-      image_stride < (size_t)pitch * (h - 1) + w || (count > 0 && (!bow_ids || !bow_vals || !n_bow)))
-    return vs_fail(ctx, VSLAM_E_ARG, "bad compute_bow_vector arguments");
-  if (cap > kMaxFeatures) return vs_fail(ctx, VSLAM_E_LIMIT, "more than 8192 features in one image");
-  if (count == 0) return VSLAM_OK;
-  VS_CUDA(ctx, cudaSetDevice(ctx->device));
-  const size_t bytes = image_stride * (size_t)(count - 1) + (size_t)pitch * (h - 1) + w;
-  VS_CUDA(ctx, ctx->orb[6].reserve(bytes + 64));
-  VS_CUDA(ctx, cudaMemcpyAsync(ctx->orb[6].p, images, bytes, cudaMemcpyHostToDevice, ctx->stream));
+// One chunk of compute_bow_vector on images that are already on the device: ORB (orb.cu) -> descent -> BowVector, and
+// the downloads of its results, all queued on ctx->stream without waiting.  counts / status: DEVICE arrays of the chunk.
+static int bow_chunk(vslam_ctx* ctx, vslam_bow_vocab* v, const uint8_t* images_dev, int count, int w, int h, int pitch,
+                     size_t image_stride, const vslam_orb_params* prm, int levelsup, uint32_t* bow_ids, double* bow_vals,
+                     int32_t* n_bow, int bow_cap, float* kp, uint8_t* desc, uint32_t* feat_node, double* feat_weight,
+                     int cap, int32_t* counts, int32_t* status) {
   OrbDeviceOut o;
-  int rc = launch_orb(ctx, ctx->orb[6].as<uint8_t>(), count, w, h, pitch, image_stride, prm, cap, &o);
+  int rc = launch_orb(ctx, images_dev, count, w, h, pitch, image_stride, prm, cap, &o);
   if (rc) return rc;
   const int total = count * cap;
   const size_t o_node = up256((size_t)total * 4), o_w = o_node + up256((size_t)total * 4);
@@ -600,8 +591,7 @@ int vslam_compute_bow_vector_batch(vslam_ctx* ctx, vslam_bow_vocab* v, const uin
   VS_CUDA(ctx, v->cnt.reserve((size_t)count * 4));
   uint8_t* feat = v->feat.as<uint8_t>();
   uint8_t* bow = v->bow.as<uint8_t>();
-  const bool empty = v->n_words == 0;  // empty(): transform clears both vectors
-  if (!empty) {
+  if (v->n_words > 0) {
     VS_CUDA(ctx, cudaMemsetAsync(feat, 0, o_w + (size_t)total * 8, ctx->stream));
     DescendParams dp;
     dp.slot_desc = v->slot_desc.as<uint4>();
@@ -641,17 +631,74 @@ int vslam_compute_bow_vector_batch(vslam_ctx* ctx, vslam_bow_vocab* v, const uin
     VS_CUDA(ctx, cudaMemcpyAsync(bow_vals, bow + o_vals, (size_t)count * bow_cap * 8, cudaMemcpyDeviceToHost, ctx->stream));
     if (feat_node) VS_CUDA(ctx, cudaMemcpyAsync(feat_node, feat + o_node, (size_t)total * 4, cudaMemcpyDeviceToHost, ctx->stream));
     if (feat_weight) VS_CUDA(ctx, cudaMemcpyAsync(feat_weight, feat + o_w, (size_t)total * 8, cudaMemcpyDeviceToHost, ctx->stream));
-  } else {
-    for (int i = 0; i < count; ++i) n_bow[i] = 0;
-    if (feat_node) memset(feat_node, 0, (size_t)total * 4);
-    if (feat_weight) memset(feat_weight, 0, (size_t)total * 8);
   }
-  std::vector<int32_t> status((size_t)count), counts((size_t)count);
-  VS_CUDA(ctx, cudaMemcpyAsync(counts.data(), o.n_kp, (size_t)count * 4, cudaMemcpyDeviceToHost, ctx->stream));
-  VS_CUDA(ctx, cudaMemcpyAsync(status.data(), o.status, (size_t)count * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  // device to device: a download into the caller's pageable bookkeeping would stall the host until the chunk is done
+  VS_CUDA(ctx, cudaMemcpyAsync(counts, o.n_kp, (size_t)count * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+  VS_CUDA(ctx, cudaMemcpyAsync(status, o.status, (size_t)count * 4, cudaMemcpyDeviceToDevice, ctx->stream));
   if (kp) VS_CUDA(ctx, cudaMemcpyAsync(kp, o.kp, (size_t)total * 24, cudaMemcpyDeviceToHost, ctx->stream));
   if (desc) VS_CUDA(ctx, cudaMemcpyAsync(desc, o.desc, (size_t)total * 32, cudaMemcpyDeviceToHost, ctx->stream));
-  VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return VSLAM_OK;
+}
+
+// visnav::compute_bow_vector (keypoints.h:243-254) for a batch.  Large batches go through in chunks: the upload of
+// chunk c + 1 (copy stream) overlaps the kernels of chunk c (the workspaces are reused chunk after chunk in stream order).
+constexpr int kBowChunk = 128;
+
+int vslam_compute_bow_vector_batch(vslam_ctx* ctx, vslam_bow_vocab* v, const uint8_t* images, int count, int w, int h,
+                                   int pitch, size_t image_stride, const vslam_orb_params* prm, int levelsup,
+                                   uint32_t* bow_ids, double* bow_vals, int32_t* n_bow, int bow_cap, float* kp,
+                                   uint8_t* desc, int32_t* n_kp, uint32_t* feat_node, double* feat_weight, int cap) {
+  if (!ctx) return VSLAM_E_ARG;
+  if (!v || v->ctx != ctx || !images || !prm || count < 0 || w <= 0 || h <= 0 || pitch < w || cap <= 0 || bow_cap <= 0 ||
+      image_stride < (size_t)pitch * (h - 1) + w || (count > 0 && (!bow_ids || !bow_vals || !n_bow)))
+    return vs_fail(ctx, VSLAM_E_ARG, "bad compute_bow_vector arguments");
+  if (cap > kMaxFeatures) return vs_fail(ctx, VSLAM_E_LIMIT, "more than 8192 features in one image");
+  if (count == 0) return VSLAM_OK;
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t tail = (size_t)pitch * (h - 1) + w;  // bytes of the last image of a run
+  VS_CUDA(ctx, ctx->orb[6].reserve(image_stride * (size_t)(count - 1) + tail + 64));
+  uint8_t* staged = ctx->orb[6].as<uint8_t>();
+  std::vector<int32_t> status((size_t)count), counts((size_t)count);
+  VS_CUDA(ctx, v->q.reserve((size_t)count * 8 + 256));  // keypoint counts | status of the whole batch
+  int32_t* counts_dev = v->q.as<int32_t>();
+  int32_t* status_dev = counts_dev + count;
+  const int n_chunks = (count + kBowChunk - 1) / kBowChunk;
+  std::vector<cudaEvent_t> ev((size_t)n_chunks, nullptr);
+  int rc = VSLAM_OK;
+  VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the staging buffer may still be read by an earlier call
+  for (int c = 0; c < n_chunks && rc == VSLAM_OK; ++c) {
+    const int c0 = c * kBowChunk, cn = std::min(kBowChunk, count - c0);
+    cudaError_t e = cudaEventCreateWithFlags(&ev[c], cudaEventDisableTiming);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(staged + image_stride * c0, images + image_stride * c0, image_stride * (size_t)(cn - 1) + tail,
+                          cudaMemcpyHostToDevice, ctx->copy_stream[0]);
+    if (e == cudaSuccess) e = cudaEventRecord(ev[c], ctx->copy_stream[0]);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->stream, ev[c], 0);
+    if (e != cudaSuccess) {
+      ctx->err = std::string("compute_bow_vector upload: ") + cudaGetErrorString(e);
+      rc = VSLAM_E_CUDA;
+      break;
+    }
+    rc = bow_chunk(ctx, v, staged + image_stride * c0, cn, w, h, pitch, image_stride, prm, levelsup,
+                   bow_ids + (size_t)c0 * bow_cap, bow_vals + (size_t)c0 * bow_cap, n_bow + c0, bow_cap,
+                   kp ? kp + (size_t)c0 * cap * 6 : nullptr, desc ? desc + (size_t)c0 * cap * 32 : nullptr,
+                   feat_node ? feat_node + (size_t)c0 * cap : nullptr, feat_weight ? feat_weight + (size_t)c0 * cap : nullptr,
+                   cap, counts_dev + c0, status_dev + c0);
+  }
+  cudaError_t es = cudaStreamSynchronize(ctx->copy_stream[0]);
+  cudaError_t e2 = cudaStreamSynchronize(ctx->stream);
+  for (cudaEvent_t e : ev)
+    if (e) cudaEventDestroy(e);
+  if (rc) return rc;
+  VS_CUDA(ctx, es);
+  VS_CUDA(ctx, e2);
+  VS_CUDA(ctx, cudaMemcpy(counts.data(), counts_dev, (size_t)count * 4, cudaMemcpyDeviceToHost));
+  VS_CUDA(ctx, cudaMemcpy(status.data(), status_dev, (size_t)count * 4, cudaMemcpyDeviceToHost));
+  if (v->n_words == 0) {  // empty(): transform clears both vectors
+    for (int i = 0; i < count; ++i) n_bow[i] = 0;
+    if (feat_node) memset(feat_node, 0, (size_t)count * cap * 4);
+    if (feat_weight) memset(feat_weight, 0, (size_t)count * cap * 8);
+  }
   if (n_kp) memcpy(n_kp, counts.data(), (size_t)count * 4);
   rc = orb_check_status(ctx, counts.data(), status.data(), count, cap);
   if (rc) return rc;

@@ -617,16 +617,26 @@ int launch_orb(vslam_ctx* ctx, const uint8_t* images_dev, int count, int w, int 
   const size_t o_hist = ((size_t)count * kMaxLevels * 4 + 255) & ~(size_t)255;
   const size_t o_nkp = o_hist + (size_t)count * kMaxLevels * 256 * 4;
   const size_t o_status = o_nkp + (((size_t)count * 4 + 255) & ~(size_t)255);
-  const size_t o_pat = o_status + (((size_t)count * 4 + 255) & ~(size_t)255);
-  const size_t o_tab = o_pat + 1024;
-  VS_CUDA(ctx, b_misc.reserve(o_tab + tab.size() * 2 + 256));
+  VS_CUDA(ctx, b_misc.reserve(o_status + (size_t)count * 4 + 256));
+  // the sampling pattern and the resize tables stay on the device between calls with the same geometry
+  const size_t o_pat = 0, o_tab = 1024;
+  DevBuf& b_tab = ctx->orb[8];
+  int scale_bits;
+  memcpy(&scale_bits, &prm->scale_factor, 4);
+  const int key[4] = {w, h, g.nlevels, scale_bits};
+  const bool tables_stale = memcmp(key, ctx->orb_tab_key, sizeof key) != 0 || b_tab.bytes < o_tab + tab.size() * 2;
   VS_CUDA(ctx, b_kp.reserve((size_t)count * cap * 6 * 4));
   VS_CUDA(ctx, b_desc.reserve((size_t)count * cap * 32));
   VS_CUDA(ctx, ctx->orb[7].reserve((size_t)count * cap * 8));
   uint8_t* misc = b_misc.as<uint8_t>();
   cudaStream_t st = ctx->stream;
   VS_CUDA(ctx, cudaMemsetAsync(misc, 0, o_nkp, st));  // candidate counters and histograms
-  if (!tab.empty()) VS_CUDA(ctx, cudaMemcpyAsync(misc + o_tab, tab.data(), tab.size() * 2, cudaMemcpyHostToDevice, st));
+  if (tables_stale) {
+    VS_CUDA(ctx, cudaStreamSynchronize(st));
+    VS_CUDA(ctx, b_tab.reserve(o_tab + tab.size() * 2 + 256));
+    if (!tab.empty()) VS_CUDA(ctx, cudaMemcpy(b_tab.as<uint8_t>() + o_tab, tab.data(), tab.size() * 2, cudaMemcpyHostToDevice));
+  }
+  const uint8_t* tabs = b_tab.as<uint8_t>();
   // umax of the radius-15 disc (orb.cpp:860-878), 4 bits per row, and the sampling pattern (behind the resize tables)
   unsigned long long umax_packed = 0;
   {
@@ -645,7 +655,10 @@ int launch_orb(vslam_ctx* ctx, const uint8_t* images_dev, int count, int w, int 
   static const int8_t pattern[256][4] = {
 #include "rbrief_pattern.inc"
   };
-  VS_CUDA(ctx, cudaMemcpyAsync(misc + o_pat, pattern, sizeof pattern, cudaMemcpyHostToDevice, st));
+  if (tables_stale) {
+    VS_CUDA(ctx, cudaMemcpy(b_tab.as<uint8_t>() + o_pat, pattern, sizeof pattern, cudaMemcpyHostToDevice));
+    memcpy(ctx->orb_tab_key, key, sizeof key);
+  }
   uint8_t* pyr = b_pyr.as<uint8_t>();
   orb_copy_level0_kernel<<<dim3((w + 255) / 256, h, count), 256, 0, st>>>(images_dev, w, h, pitch, stride, g, pyr);
   ctx->launches += 1;
@@ -653,7 +666,7 @@ int launch_orb(vslam_ctx* ctx, const uint8_t* images_dev, int count, int w, int 
     if (g.w[l] == g.w[l - 1] && g.h[l] == g.h[l - 1])
       return vs_fail(ctx, VSLAM_E_LIMIT, "ORB: two pyramid levels of the same size");  // resize() would copy
     orb_resize_kernel<<<dim3((g.w[l] + 127) / 128, g.h[l], count), 128, 0, st>>>(
-        g, l, reinterpret_cast<const ushort2*>(misc + o_tab) + g.tab_off[l], pyr);
+        g, l, reinterpret_cast<const ushort2*>(tabs + o_tab) + g.tab_off[l], pyr);
     ctx->launches += 1;
   }
   VS_CUDA(ctx, cudaGetLastError());
@@ -707,7 +720,7 @@ int launch_orb(vslam_ctx* ctx, const uint8_t* images_dev, int count, int w, int 
   kp.n_kp = sp.n_kp;
   kp.desc = b_desc.as<uint8_t>();
   kp.rot = ctx->orb[7].as<float2>();
-  kp.pattern = reinterpret_cast<const char4*>(misc + o_pat);
+  kp.pattern = reinterpret_cast<const char4*>(tabs + o_pat);
   kp.umax = umax_packed;
   kp.cap = cap;
   orb_angle_kernel<<<dim3((cap + 7) / 8, count), 256, 0, st>>>(kp);
