@@ -3,7 +3,7 @@
 // images, for sm_100a.  SURVEY.md §8f-4, ORB half: the second detector the reference runs per keyframe, feeding the
 // vocabulary transform (bow.cu).
 //
-// Semantics (thirdparty/opencv/modules; every stage below was first restated on the CPU -- oracle/visnav_oracle_orb.c
+// Semantics (thirdparty/opencv/modules; every stage below was first restated on the CPU -- the test-only ORB restatement under oracle/
 // -- and pinned to cv2.ORB):
 //   pyramid      features2d/src/orb.cpp:1063-1130: level l is cvRound(size / 1.2^l), made from level l-1 by
 //                resize(INTER_LINEAR_EXACT): 8.8 fixed-point taps (imgproc/src/resize.cpp:733-771, :344-398, :691-731)
