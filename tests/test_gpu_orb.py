@@ -103,3 +103,24 @@ def test_compute_bow_vector_is_orb_then_transform(ctx):
     assert v.score(vecs[0], vs) > 1.3 * v.score(vecs[0], vecs[1])
     v.close()
     o.close()
+
+
+def test_row_pitch_and_image_stride_are_honoured(ctx):
+    """Images handed over with padding after every row and between images (pitch > w, stride > pitch * h)."""
+    import ctypes as C
+    w, h, pitch, count, nf, cap = 333, 250, 360, 3, 400, 1024
+    stride = pitch * h + 128
+    imgs = np.stack([wl.synth_image(40 + i, w, h) for i in range(count)])
+    buf = np.full(stride * count, 255, np.uint8)
+    for i in range(count):
+        buf[i * stride:i * stride + pitch * h].reshape(h, pitch)[:, :w] = imgs[i]
+    kp = np.zeros((count, cap, 6), np.float32)
+    desc = np.zeros((count, cap, 32), np.uint8)
+    n = np.zeros(count, np.int32)
+    prm = OrbParams(nf)
+    P = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    ctx._check(ctx.lib.vslam_orb_detect_compute_batch(ctx.h, P(buf), count, w, h, pitch, stride, C.byref(prm), P(kp), P(desc),
+                                                      P(n), cap))
+    for i in range(count):
+        okp, odesc = oo.orb_detect_compute(imgs[i], nf)
+        check_against(kp[i, :n[i]], desc[i, :n[i]], okp, odesc, i)
