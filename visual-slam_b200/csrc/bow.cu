@@ -222,8 +222,10 @@ __global__ void __launch_bounds__(kBowThreads) bow_vector_kernel(const BowVecPar
     // time (coalesced) and every lane runs the same chain of additions over them, fed by shuffles.
     const int lane = threadIdx.x;
     double norm = 0.0;
+    double next = lane < m ? vals[lane] : 0.0;
     for (int i0 = 0; i0 < m; i0 += 32) {
-      const double v = i0 + lane < m ? vals[i0 + lane] : 0.0;
+      const double v = next;
+      next = i0 + 32 + lane < m ? vals[i0 + 32 + lane] : 0.0;  // in flight while this chunk's chain runs
       const int cnt = min(32, m - i0);
       for (int j = 0; j < cnt; ++j) {
         const double x = __shfl_sync(0xFFFFFFFFu, v, j);

@@ -79,7 +79,7 @@ __global__ void orb_resize_kernel(OrbGeom g, int l, const ushort2* tab, uint8_t*
 }
 
 // ---- FAST-9/16 score + 3x3 non-maximum suppression + border filter -------------------------------------------------
-constexpr int kFastTW = 62, kFastTH = 16;                     // outputs per CTA
+constexpr int kFastTW = 62, kFastTH = 32;                     // outputs per CTA
 constexpr int kFastSW = kFastTW + 2, kFastSH = kFastTH + 2;   // score tile (1 px NMS halo): 64 wide = two lane passes
 constexpr int kFastIH = kFastTH + 8;                          // image tile rows: + 3 (ring) on every side
 constexpr int kFastIP = 80;                                   // image tile row pitch: 19 words + padding
@@ -239,79 +239,105 @@ __device__ void bitonic_asc_u32_blk(uint32_t* keys, int n) {
     }
 }
 
-__global__ void __launch_bounds__(1024) orb_select_kernel(const SelectParams p) {
+// One CTA per (level, image).  Warp j <= l derives level j's cut-off score and kept count from its histogram, so every
+// CTA knows where its level starts in the image's keypoint list without waiting for the levels before it.
+__global__ void __launch_bounds__(512) orb_select_kernel(const SelectParams p) {
   __shared__ uint32_t s_keys[kMaxLevelKp];
-  __shared__ int s_thr, s_cnt;
-  __shared__ uint32_t s_hist[256];
-  const int img = blockIdx.x;
-  int out = 0;
-  int status = 0;
-  for (int l = 0; l < p.g.nlevels; ++l) {
-    const uint32_t raw = p.cand_cnt[img * kMaxLevels + l];
-    const int n = (int)min(raw, (uint32_t)p.g.cand_cap[l]);
-    if (raw > (uint32_t)p.g.cand_cap[l]) status |= 1;
-    if (threadIdx.x < 256) s_hist[threadIdx.x] = p.hist[((size_t)img * kMaxLevels + l) * 256 + threadIdx.x];
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      // KeyPointsFilter::retainBest (keypoint.cpp:69-90): nothing to do unless there are more than n_points; then
-      // everything whose response reaches the n_points-th largest stays
-      const uint32_t* h = s_hist;
-      int thr = 0;
-      if (n > p.g.nper[l]) {
-        if (p.g.nper[l] == 0) {
-          thr = 256;
-        } else {
-          int acc = 0;
-          for (thr = 255; thr > 0; --thr) {
-            acc += (int)h[thr];
-            if (acc >= p.g.nper[l]) break;
+  __shared__ int s_thr[kMaxLevels], s_kept[kMaxLevels], s_cnt;
+  const int l = blockIdx.x, img = blockIdx.y;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_cnt = 0;
+  if (warp <= l) {
+    // KeyPointsFilter::retainBest (keypoint.cpp:69-90) for level `warp`: nothing to do unless there are more than
+    // n_points candidates; then everything whose response reaches the n_points-th largest stays
+    const int j = warp;
+    const uint32_t raw = p.cand_cnt[img * kMaxLevels + j];
+    const int n = (int)min(raw, (uint32_t)p.g.cand_cap[j]);
+    const int nper = p.g.nper[j];
+    int thr = 0, kept = n;
+    if (n > nper) {
+      if (nper == 0) {
+        thr = 256;
+        kept = 0;
+      } else {
+        const uint32_t* h = p.hist + ((size_t)img * kMaxLevels + j) * 256 + 8 * lane;  // this lane: scores 8*lane .. +7
+        int bins[8], mine = 0;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          bins[q] = (int)h[q];
+          mine += bins[q];
+        }
+        int suffix = mine;  // candidates with a score in this lane's bins or above
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const int o = __shfl_down_sync(0xFFFFFFFFu, suffix, d);
+          if (lane + d < 32) suffix += o;
+        }
+        const unsigned reach = __ballot_sync(0xFFFFFFFFu, suffix >= nper);
+        const int top = 31 - __clz(reach);  // the highest lane whose suffix reaches n_points (reach != 0: n > nper)
+        int acc = suffix - mine;
+        int t_found = 8 * lane, k_found = suffix;
+#pragma unroll
+        for (int q = 7; q >= 0; --q) {
+          acc += bins[q];
+          if (acc >= nper) {
+            t_found = 8 * lane + q;
+            k_found = acc;
+            break;
           }
         }
-      }
-      s_thr = thr;
-      s_cnt = 0;
-    }
-    __syncthreads();
-    const uint32_t thr = (uint32_t)s_thr;
-    const uint32_t* c = p.cand + (size_t)img * p.g.cand_total + p.g.cand_off[l];
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      const uint32_t key = c[i];
-      if ((key >> 24) >= thr) {
-        const int pos = atomicAdd(&s_cnt, 1);
-        if (pos < kMaxLevelKp) s_keys[pos] = (key << 8) | (key >> 24);  // y, x on top: raster order; score below
+        thr = __shfl_sync(0xFFFFFFFFu, t_found, top);
+        kept = __shfl_sync(0xFFFFFFFFu, k_found, top);
       }
     }
-    __syncthreads();
-    int m = s_cnt;
-    if (m > kMaxLevelKp) {
-      status |= 2;
-      m = kMaxLevelKp;
+    if (lane == 0) {
+      s_thr[j] = thr;
+      s_kept[j] = kept;
     }
-    int np2 = 32;
-    while (np2 < m) np2 <<= 1;
-    for (int i = m + threadIdx.x; i < np2; i += blockDim.x) s_keys[i] = 0xFFFFFFFFu;
-    __syncthreads();
-    bitonic_asc_u32_blk(s_keys, np2);
-    const float sc = p.g.scale[l];
-    for (int i = threadIdx.x; i < m; i += blockDim.x) {
-      const uint32_t k = s_keys[i];
-      const int x = (k >> 8) & 0xFFF, y = k >> 20;
-      if (out + i < p.cap) {
-        float* o = p.kp + ((size_t)img * p.cap + out + i) * 6;
-        o[0] = __fmul_rn((float)x, sc);   // allKeypoints[i].pt *= scale (orb.cpp:993-997)
-        o[1] = __fmul_rn((float)y, sc);
-        o[2] = __fmul_rn(31.f, sc);       // size = patchSize * scale (:907)
-        o[3] = 0.f;                       // angle: orb_angle_kernel
-        o[4] = (float)(k & 0xFF);
-        o[5] = (float)l;
-      }
+  }
+  __syncthreads();
+  int out = 0;
+  for (int j = 0; j < l; ++j) out += min(s_kept[j], kMaxLevelKp);
+  const uint32_t thr = (uint32_t)s_thr[l];
+  const uint32_t raw = p.cand_cnt[img * kMaxLevels + l];
+  const int n = (int)min(raw, (uint32_t)p.g.cand_cap[l]);
+  int status = raw > (uint32_t)p.g.cand_cap[l] ? 1 : 0;
+  const uint32_t* c = p.cand + (size_t)img * p.g.cand_total + p.g.cand_off[l];
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const uint32_t key = c[i];
+    if ((key >> 24) >= thr) {
+      const int pos = atomicAdd(&s_cnt, 1);
+      if (pos < kMaxLevelKp) s_keys[pos] = (key << 8) | (key >> 24);  // y, x on top: raster order; score below
     }
-    out += m;
-    __syncthreads();
+  }
+  __syncthreads();
+  int m = s_cnt;
+  if (m > kMaxLevelKp) {
+    status |= 2;
+    m = kMaxLevelKp;
+  }
+  int np2 = 32;
+  while (np2 < m) np2 <<= 1;
+  for (int i = m + threadIdx.x; i < np2; i += blockDim.x) s_keys[i] = 0xFFFFFFFFu;
+  __syncthreads();
+  bitonic_asc_u32_blk(s_keys, np2);
+  const float sc = p.g.scale[l];
+  for (int i = threadIdx.x; i < m; i += blockDim.x) {
+    const uint32_t k = s_keys[i];
+    const int x = (k >> 8) & 0xFFF, y = k >> 20;
+    if (out + i < p.cap) {
+      float* o = p.kp + ((size_t)img * p.cap + out + i) * 6;
+      o[0] = __fmul_rn((float)x, sc);   // allKeypoints[i].pt *= scale (orb.cpp:993-997)
+      o[1] = __fmul_rn((float)y, sc);
+      o[2] = __fmul_rn(31.f, sc);       // size = patchSize * scale (:907)
+      o[3] = 0.f;                       // angle: orb_angle_kernel
+      o[4] = (float)(k & 0xFF);
+      o[5] = (float)l;
+    }
   }
   if (threadIdx.x == 0) {
-    p.n_kp[img] = out;
-    p.status[img] = status;
+    if (l == p.g.nlevels - 1) p.n_kp[img] = out + m;
+    if (status) atomicOr(p.status + img, status);
   }
 }
 
@@ -630,7 +656,7 @@ int launch_orb(vslam_ctx* ctx, const uint8_t* images_dev, int count, int w, int 
   VS_CUDA(ctx, ctx->orb[7].reserve((size_t)count * cap * 8));
   uint8_t* misc = b_misc.as<uint8_t>();
   cudaStream_t st = ctx->stream;
-  VS_CUDA(ctx, cudaMemsetAsync(misc, 0, o_nkp, st));  // candidate counters and histograms
+  VS_CUDA(ctx, cudaMemsetAsync(misc, 0, o_status + (size_t)count * 4, st));  // candidate counters, histograms, counts, status
   if (tables_stale) {
     VS_CUDA(ctx, cudaStreamSynchronize(st));
     VS_CUDA(ctx, b_tab.reserve(o_tab + tab.size() * 2 + 256));
@@ -712,7 +738,7 @@ int launch_orb(vslam_ctx* ctx, const uint8_t* images_dev, int count, int w, int 
   sp.n_kp = reinterpret_cast<int32_t*>(misc + o_nkp);
   sp.status = reinterpret_cast<int32_t*>(misc + o_status);
   sp.cap = cap;
-  orb_select_kernel<<<count, 1024, 0, st>>>(sp);
+  orb_select_kernel<<<dim3(g.nlevels, count), 512, 0, st>>>(sp);
   KpParams kp;
   kp.g = g;
   kp.pyr = pyr;
