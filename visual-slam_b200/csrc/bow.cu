@@ -227,10 +227,18 @@ __global__ void __launch_bounds__(kBowThreads) bow_vector_kernel(const BowVecPar
       const double v = next;
       next = i0 + 32 + lane < m ? vals[i0 + 32 + lane] : 0.0;  // in flight while this chunk's chain runs
       const int cnt = min(32, m - i0);
-      for (int j = 0; j < cnt; ++j) {
-        const double x = __shfl_sync(0xFFFFFFFFu, v, j);
-        norm = p.norm_l2 ? __fma_rn(x, x, norm)  // fused, as the -march=native build of DBoW2
-                         : __dadd_rn(norm, fabs(x));
+      if (cnt == 32) {  // full chunk: unrolled, so the 32 shuffles are issued ahead of the chain of additions
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const double x = __shfl_sync(0xFFFFFFFFu, v, j);
+          norm = p.norm_l2 ? __fma_rn(x, x, norm)  // fused, as the -march=native build of DBoW2
+                           : __dadd_rn(norm, fabs(x));
+        }
+      } else {
+        for (int j = 0; j < cnt; ++j) {
+          const double x = __shfl_sync(0xFFFFFFFFu, v, j);
+          norm = p.norm_l2 ? __fma_rn(x, x, norm) : __dadd_rn(norm, fabs(x));
+        }
       }
     }
     if (p.norm_l2) norm = __dsqrt_rn(norm);
