@@ -49,6 +49,16 @@ def test_golden_cv2_orb(ctx):
     assert total_bits == 0   # observed; check_against states what would be tolerated
 
 
+@pytest.mark.parametrize("case", range(6))
+def test_golden_cv2_orb_other_parameters(ctx, case):
+    """cv2.ORB's own output at other scale factors, level counts, FAST and edge thresholds (orb_params.npz)."""
+    g = np.load(os.path.join(GOLD, "orb_params.npz"))
+    seed, w, h, nf, sf, nl, et, ft = g["cases"][case]
+    img = wl.synth_image(int(seed), int(w), int(h))
+    kp, desc, n = ctx.orb_detect_compute_batch(img[None], params=OrbParams(int(nf), float(sf), int(nl), int(et), int(ft)))
+    check_against(kp[0, :n[0]], desc[0, :n[0]], g["kp%d" % case], g["desc%d" % case], ("case", case))
+
+
 @pytest.mark.parametrize("w,h,nf,count", [(752, 480, 1500, 5), (640, 480, 700, 3), (321, 243, 200, 4), (1000, 700, 2000, 2),
                                           (130, 100, 500, 3), (60, 50, 100, 2)])
 def test_against_oracle(ctx, w, h, nf, count):

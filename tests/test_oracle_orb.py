@@ -39,6 +39,19 @@ def test_port_matches_golden_cv2_orb(name, nf):
     assert len(kp) >= nf     # ties at the cut-off score all stay (KeyPointsFilter::retainBest)
 
 
+@pytest.mark.parametrize("case", range(6))
+def test_port_matches_golden_cv2_orb_other_parameters(case):
+    """tests/golden/orb_params.npz (tools/make_golden.py orb_params): cv2.ORB at scale factors 1.1 ... 2.0, 1 ... 8
+    levels, FAST thresholds 5 ... 40, edge thresholds 19 / 25 / 31 on odd-sized images -- away from the reference's one
+    parameter set, which the entry point also accepts."""
+    g = np.load(os.path.join(GOLD, "orb_params.npz"))
+    seed, w, h, nf, sf, nl, et, ft = g["cases"][case]
+    img = wl.synth_image(int(seed), int(w), int(h))
+    kp, desc = canonical(*oo.orb_detect_compute(img, int(nf), int(nl), float(sf), int(et), int(ft)))
+    assert np.array_equal(kp.view(np.uint32), g["kp%d" % case].view(np.uint32))
+    assert np.array_equal(desc, g["desc%d" % case])
+
+
 def test_gaussian_kernel_is_cv2s():
     g = np.load(os.path.join(GOLD, "orb.npz"))
     assert np.array_equal(oo.gaussian_kernel7().view(np.uint32), g["k7"].view(np.uint32))

@@ -229,9 +229,34 @@ def orb():
     np.savez_compressed(os.path.join(OUT, "orb.npz"), **rec)
 
 
+ORB_PARAM_CASES = [  # (seed, w, h, nfeatures, scale, nlevels, edge, fast)
+    (2001, 333, 251, 300, 1.5, 4, 19, 10), (2002, 640, 200, 1000, 1.1, 8, 25, 20), (2003, 161, 123, 50, 2.0, 3, 19, 5),
+    (2004, 480, 360, 2500, 1.3, 6, 31, 40), (2005, 257, 511, 600, 1.2, 1, 19, 20), (2006, 97, 89, 300, 1.2, 8, 19, 7)]
+
+
+def orb_params():
+    """cv2.ORB away from the reference's parameter set (other scale factors, level counts, FAST thresholds, edge
+    thresholds, odd sizes, levels that come out empty): the entry point takes them, so the restatement is pinned there
+    too.  Images are workloads.synth_image(seed, w, h), not stored."""
+    rec = {"cases": np.array(ORB_PARAM_CASES, np.float64)}
+    for i, (seed, w, h, nf, sf, nl, et, ft) in enumerate(ORB_PARAM_CASES):
+        img = wl.synth_image(seed, w, h)
+        o = cv2.ORB_create(nf, sf, nl, et, 0, 2, cv2.ORB_FAST_SCORE, 31, ft)
+        kps, d = o.detectAndCompute(img, None)
+        d = np.zeros((0, 32), np.uint8) if d is None else d
+        order = sorted(range(len(kps)), key=lambda i: (kps[i].octave, kps[i].pt[1], kps[i].pt[0]))
+        rec["kp%d" % i] = np.array([[kps[j].pt[0], kps[j].pt[1], kps[j].size, kps[j].angle, kps[j].response,
+                                     kps[j].octave] for j in order], np.float32).reshape(-1, 6)
+        rec["desc%d" % i] = d[order]
+        print("orb_params", i, len(kps))
+    np.savez_compressed(os.path.join(OUT, "orb_params.npz"), **rec)
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "orb":
         orb()
+    elif len(sys.argv) > 1 and sys.argv[1] == "orb_params":
+        orb_params()
     elif len(sys.argv) > 1 and sys.argv[1] == "bow":
         bow()
     elif len(sys.argv) > 1 and sys.argv[1] == "landmarks":
@@ -250,3 +275,4 @@ if __name__ == "__main__":
         harris()
         bow()
         orb()
+        orb_params()

@@ -53,7 +53,9 @@ struct vslam_ctx {
   DevBuf d1, d2, pairs, mcnt, rowpart, colstat, jobs;
   DevBuf lm;  // vslam_match_landmarks staging
   DevBuf geo;  // geometry.cu staging (camera models, essential inliers, landmark projection)
-  DevBuf orb[9];  // orb.cu: pyramid, blurred pyramid, candidates, counters, keypoints, descriptors, staging, rotations, tables
+  // orb.cu: pyramid, blurred pyramid, candidates, counters, keypoints, descriptors, staging, rotations, tables, batch
+  // counts | status, the second keypoint / descriptor buffers (chunks alternate)
+  DevBuf orb[12];
   int orb_tab_key[4] = {0, 0, 0, 0};  // geometry the resize tables in orb[8] were built for (w, h, levels, scale bits)
   DevBuf pyr;  // vslam_pyramid_detect_describe_batch: levels 1.. of the chunk in flight
   void* pinned = nullptr;  // small pinned staging block for counts

@@ -772,6 +772,8 @@ int orb_check_status(vslam_ctx* ctx, const int32_t* n_kp, const int32_t* status,
   return VSLAM_OK;
 }
 
+constexpr int kOrbChunk = 128;
+
 extern "C" int vslam_orb_detect_compute_batch(vslam_ctx* ctx, const uint8_t* images, int count, int w, int h, int pitch,
                                               size_t image_stride, const vslam_orb_params* prm, float* kp, uint8_t* desc,
                                               int32_t* n_kp, int cap) {
@@ -781,17 +783,56 @@ extern "C" int vslam_orb_detect_compute_batch(vslam_ctx* ctx, const uint8_t* ima
     return vs_fail(ctx, VSLAM_E_ARG, "bad ORB arguments");
   if (count == 0) return VSLAM_OK;
   VS_CUDA(ctx, cudaSetDevice(ctx->device));
-  const size_t bytes = image_stride * (size_t)(count - 1) + (size_t)pitch * (h - 1) + w;
-  VS_CUDA(ctx, ctx->orb[6].reserve(bytes + 64));
-  VS_CUDA(ctx, cudaMemcpyAsync(ctx->orb[6].p, images, bytes, cudaMemcpyHostToDevice, ctx->stream));
-  OrbDeviceOut out;
-  int rc = launch_orb(ctx, ctx->orb[6].as<uint8_t>(), count, w, h, pitch, image_stride, prm, cap, &out);
+  // Chunks of kOrbChunk images: the upload of chunk c + 1 (copy stream 0) and the download of chunk c - 1's keypoints
+  // and descriptors (copy stream 1; the two output buffers alternate) overlap the kernels of chunk c.
+  const size_t tail = (size_t)pitch * (h - 1) + w;  // bytes of the last image of a run
+  VS_CUDA(ctx, ctx->orb[6].reserve(image_stride * (size_t)(count - 1) + tail + 64));
+  VS_CUDA(ctx, ctx->orb[9].reserve((size_t)count * 8 + 256));  // keypoint counts | status of the whole batch
+  uint8_t* staged = ctx->orb[6].as<uint8_t>();
+  int32_t* counts_dev = ctx->orb[9].as<int32_t>();
+  int32_t* status_dev = counts_dev + count;
+  const int n_chunks = (count + kOrbChunk - 1) / kOrbChunk;
+  std::vector<cudaEvent_t> ev((size_t)n_chunks * 3, nullptr);  // uploaded | computed | downloaded
+  int rc = VSLAM_OK;
+  cudaError_t e = cudaStreamSynchronize(ctx->stream);  // the staging buffer may still be read by an earlier call
+  for (int c = 0; c < n_chunks && rc == VSLAM_OK && e == cudaSuccess; ++c) {
+    const int c0 = c * kOrbChunk, cn = std::min(kOrbChunk, count - c0);
+    cudaEvent_t* evc = &ev[(size_t)c * 3];
+    for (int i = 0; i < 3 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&evc[i], cudaEventDisableTiming);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(staged + image_stride * c0, images + image_stride * c0, image_stride * (size_t)(cn - 1) + tail,
+                          cudaMemcpyHostToDevice, ctx->copy_stream[0]);
+    if (e == cudaSuccess) e = cudaEventRecord(evc[0], ctx->copy_stream[0]);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->stream, evc[0], 0);
+    if (c >= 2 && e == cudaSuccess) e = cudaStreamWaitEvent(ctx->stream, ev[(size_t)(c - 2) * 3 + 2], 0);  // its buffers are free again
+    if (e != cudaSuccess) break;
+    std::swap(ctx->orb[4], ctx->orb[10]);
+    std::swap(ctx->orb[5], ctx->orb[11]);
+    OrbDeviceOut out;
+    rc = launch_orb(ctx, staged + image_stride * c0, cn, w, h, pitch, image_stride, prm, cap, &out);
+    if (rc) break;
+    e = cudaMemcpyAsync(counts_dev + c0, out.n_kp, (size_t)cn * 4, cudaMemcpyDeviceToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(status_dev + c0, out.status, (size_t)cn * 4, cudaMemcpyDeviceToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(evc[1], ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->copy_stream[1], evc[1], 0);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(kp + (size_t)c0 * cap * 6, out.kp, (size_t)cn * cap * 24, cudaMemcpyDeviceToHost, ctx->copy_stream[1]);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(desc + (size_t)c0 * cap * 32, out.desc, (size_t)cn * cap * 32, cudaMemcpyDeviceToHost, ctx->copy_stream[1]);
+    if (e == cudaSuccess) e = cudaEventRecord(evc[2], ctx->copy_stream[1]);
+  }
+  const cudaError_t s0 = cudaStreamSynchronize(ctx->copy_stream[0]);
+  const cudaError_t s1 = cudaStreamSynchronize(ctx->stream);
+  const cudaError_t s2 = cudaStreamSynchronize(ctx->copy_stream[1]);
+  for (cudaEvent_t x : ev)
+    if (x) cudaEventDestroy(x);
   if (rc) return rc;
+  VS_CUDA(ctx, e);
+  VS_CUDA(ctx, s0);
+  VS_CUDA(ctx, s1);
+  VS_CUDA(ctx, s2);
   std::vector<int32_t> status((size_t)count);
-  VS_CUDA(ctx, cudaMemcpyAsync(n_kp, out.n_kp, (size_t)count * 4, cudaMemcpyDeviceToHost, ctx->stream));
-  VS_CUDA(ctx, cudaMemcpyAsync(status.data(), out.status, (size_t)count * 4, cudaMemcpyDeviceToHost, ctx->stream));
-  VS_CUDA(ctx, cudaMemcpyAsync(kp, out.kp, (size_t)count * cap * 24, cudaMemcpyDeviceToHost, ctx->stream));
-  VS_CUDA(ctx, cudaMemcpyAsync(desc, out.desc, (size_t)count * cap * 32, cudaMemcpyDeviceToHost, ctx->stream));
-  VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  VS_CUDA(ctx, cudaMemcpy(n_kp, counts_dev, (size_t)count * 4, cudaMemcpyDeviceToHost));
+  VS_CUDA(ctx, cudaMemcpy(status.data(), status_dev, (size_t)count * 4, cudaMemcpyDeviceToHost));
   return orb_check_status(ctx, n_kp, status.data(), count, cap);
 }
