@@ -61,6 +61,10 @@ typedef struct vslam_desc_store vslam_desc_store;
                                         spreads every job's columns over all SMs (latency of a single stereo
                                         pair); 0: always one CTA per job.  Results identical. */
 
+#define VSLAM_OPT_RESPONSE_BAND 6 /* output rows per box of the corner-response kernel.  0 (default): chosen per launch
+                                    (the whole image height when the batch fills the SMs, else bands of <= 64 rows);
+                                    >= 8: forced.  Results identical. */
+
 /* ---- context ------------------------------------------------------------------------ */
 int vslam_create(int device, vslam_ctx** out);
 void vslam_destroy(vslam_ctx* ctx);

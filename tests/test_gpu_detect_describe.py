@@ -7,7 +7,7 @@ import pytest
 
 import visnav_b200
 from visnav_b200 import workloads as wl
-from visnav_b200.keypoints import KeypointsData, VSLAM_OPT_FP_CONTRACT
+from visnav_b200.keypoints import KeypointsData, VSLAM_OPT_FP_CONTRACT, VSLAM_OPT_RESPONSE_BAND
 
 pytestmark = pytest.mark.gpu
 
@@ -27,6 +27,23 @@ def test_response_bit_exact(ctx, oracle_port, w, h):
     want = oracle_port.response(img)
     assert got.shape == want.shape
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), float((got != want).mean())
+
+
+@pytest.mark.parametrize("band", [8, 26, 29, 61, 100, 65535])
+@pytest.mark.parametrize("w,h", [(752, 480), (121, 97), (333, 131)])
+def test_response_box_heights(ctx, oracle_port, w, h, band):
+    """The response kernel streams a box through a two-chunk (2 x 32 rows) shared-memory ring; the box height is chosen
+    from the batch size (whole image height for a batch that fills the SMs).  Every height gives the same bits: chunk
+    boundaries at all phases of the row pipeline, reflected rows read from the previous chunk, one chunk only."""
+    img = _image(w, h, 5 + w + band)
+    want_map, want_xy = oracle_port.response(img), oracle_port.detect(img, 1500)
+    ctx.set_option(VSLAM_OPT_RESPONSE_BAND, band)
+    try:
+        got_map, got_xy = ctx.response(img), ctx.detect(img, 1500)
+    finally:
+        ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 0)
+    assert np.array_equal(got_map.view(np.uint32), want_map.view(np.uint32)), float((got_map != want_map).mean())
+    assert got_xy.shape == want_xy.shape and np.array_equal(got_xy, want_xy)
 
 
 @pytest.mark.parametrize("w,h", SIZES)

@@ -132,6 +132,7 @@ int vslam_set_option(vslam_ctx* ctx, int option, int value) {
   if (option == VSLAM_OPT_FP_CONTRACT) ctx->fp_contract = value != 0;
   else if (option == VSLAM_OPT_MATCH_CSA) ctx->match_csa = value != 0;
   else if (option == VSLAM_OPT_MATCH_SPLIT_SMALL) ctx->match_split_small = value != 0;
+  else if (option == VSLAM_OPT_RESPONSE_BAND && (value == 0 || (value >= 8 && value <= 65535))) ctx->resp_band = value;
   else if (option == VSLAM_OPT_BATCH_CHUNK && value >= 1 && value <= 4096) ctx->batch_chunk = value;
   else if (option == VSLAM_OPT_BATCH_DEPTH && value >= 1 && value <= vslam_ctx::kMaxBatchDepth) ctx->batch_depth = value;
   else return vs_fail(ctx, VSLAM_E_ARG, "unknown option");

@@ -44,6 +44,7 @@ struct vslam_ctx {
   int match_csa = 1;
   int harris_on = 0;       // goodFeaturesToTrack(useHarrisDetector): the reference passes false (keypoints.h:139)
   double harris_k = 0.04;  // cv::goodFeaturesToTrack's default k
+  int resp_band = 0;  // response kernel: forced box height (0 = chosen per launch)
   int match_split_small = 1;  // batches with fewer jobs than SMs/2: split every job's columns over CTAs
   long long launches = 0;
   float last_match_ms = 0.f;

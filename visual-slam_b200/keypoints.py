@@ -49,6 +49,7 @@ VSLAM_OPT_MATCH_CSA = 2
 VSLAM_OPT_BATCH_CHUNK = 3
 VSLAM_OPT_BATCH_DEPTH = 4
 VSLAM_OPT_MATCH_SPLIT_SMALL = 5
+VSLAM_OPT_RESPONSE_BAND = 6
 
 
 class VslamError(RuntimeError):
