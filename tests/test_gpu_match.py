@@ -49,6 +49,24 @@ def test_match_heavy_ties(ctx, oracle_port, seed):
     assert np.array_equal(ctx.best2(d1, d2), oracle_port.best2(d1, d2))
 
 
+def test_match_odd_parameters(ctx, oracle_port):
+    """Thresholds and ratios away from (70, 1.2): ratios below 1 (never reject), negative, huge and infinite ones
+    (reject everything but a zero best distance), thresholds above the largest distance and below zero; fused
+    (one CTA per job) and column-split kernels; weakly related, strongly related and identical sets."""
+    rng = np.random.default_rng(31)
+    for n1, n2, flips in [(700, 650, 20), (1500, 1400, 45), (300, 5000, 30), (200, 180, 0), (64, 64, 100)]:
+        d2 = wl.random_descriptors(n2, n1)
+        d1 = wl.random_descriptors(n1, n2 + 1)
+        k = min(n1, n2)
+        d1[:k] = wl.flip_bits(d2[rng.permutation(n2)[:k]], flips, rng) if flips else d2[rng.permutation(n2)[:k]]
+        for thr, ratio in [(70, 1.2), (70, 0.5), (70, 0.0), (70, -3.0), (70, 1e9), (70, float("inf")), (1, 1.2),
+                           (50, 3.7), (256, 1.2), (257, 1.2), (1000, 20.0), (128, 2.0), (-5, 1.2)]:
+            got = ctx.match(d1, d2, thr, ratio)
+            want = oracle_port.match(d1, d2, thr, ratio)
+            assert np.array_equal(got, want), (n1, n2, flips, thr, ratio, len(got), len(want))
+        assert np.array_equal(ctx.best2(d1, d2), oracle_port.best2(d1, d2))
+
+
 def test_match_extremes(ctx, oracle_port):
     z = np.zeros((5, 8), np.uint32)
     f = np.full((7, 8), 0xFFFFFFFF, np.uint32)
