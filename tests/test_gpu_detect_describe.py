@@ -55,6 +55,19 @@ def test_detect_ordered_equal(ctx, oracle_port, w, h, nf):
     assert got.shape == want.shape and np.array_equal(got, want)
 
 
+def test_response_full_height_1080p(ctx, oracle_port):
+    """A 1080-row box: 34 chunks through the ring, 16 boxes across (config 5 geometry)."""
+    img = _image(1920, 1080, 123)
+    ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 65535)
+    try:
+        got_map, got_xy = ctx.response(img), ctx.detect(img, 4000)
+    finally:
+        ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 0)
+    want_map = oracle_port.response(img)
+    assert np.array_equal(got_map.view(np.uint32), want_map.view(np.uint32))
+    assert np.array_equal(got_xy, oracle_port.detect(img, 4000))
+
+
 def test_detect_strongest_subset_paths(ctx, oracle_port):
     """1080p images have ~24 k candidates above the threshold: the select kernel decides on the strongest
     8192 in shared memory when they yield num_features corners (4000) and must fall back to the complete
