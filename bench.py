@@ -310,6 +310,19 @@ def run_ours(args):
         "gpu_launches": int(launches), "clocks": clocks,
         "results": {"mean_keypoints": float(res["n_kp"].mean()), "mean_matches": float(res["n_matches"].mean())},
     }
+    # The matcher against the integer-popcount roofline north_star names (8 popc.b32 per 256-bit distance;
+    # the kernel's carry-save adders turn them into 4 real POPCs, so the fraction may exceed 1).  Peak = the
+    # register-only POPC microbenchmark of the library, run now on this GPU.
+    kp = res["n_kp"].astype(np.int64).reshape(-1, 2)
+    n_dist = float((kp[:, 0] * kp[:, 1]).sum())
+    popc_peak = ctx.popc_peak()
+    match_ms = float(stage_ms[4])
+    line["roofline_match"] = {"kernel": "match_fused_kernel (all-pairs Hamming + best/second + ratio + mutual check)",
+                              "bound": "popc", "unit": "popc.b32/s", "achieved": 8.0 * n_dist / (match_ms * 1e-3),
+                              "peak": popc_peak, "peak_source": "vslam_popc_peak microbenchmark, this run",
+                              "frac": 8.0 * n_dist / (match_ms * 1e-3) / popc_peak,
+                              "distances_per_s": n_dist / (match_ms * 1e-3), "ms_per_launch": match_ms,
+                              "distances_per_launch": n_dist}
     if not args.no_cpu_baseline and world == 1:
         cores = os.cpu_count() or 1
         sample = min(16 * cores, n_distinct)      # ~15-25 s of CPU work (73 ms per pair and core)
