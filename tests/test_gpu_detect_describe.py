@@ -55,6 +55,20 @@ def test_detect_ordered_equal(ctx, oracle_port, w, h, nf):
     assert got.shape == want.shape and np.array_equal(got, want)
 
 
+def test_response_ring_bottom_alignments(ctx, oracle_port):
+    """Every position of the last image row inside a 32-row chunk: the reflected rows h-2, h-3 that rows h, h+1 read
+    sit in the same chunk or in the previous one (the other half of the ring)."""
+    ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 65535)
+    try:
+        for h in list(range(56, 72)) + list(range(88, 100)):
+            img = _image(150, h, 900 + h)
+            got, want = ctx.response(img), oracle_port.response(img)
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), h
+            assert np.array_equal(ctx.detect(img, 500), oracle_port.detect(img, 500)), h
+    finally:
+        ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 0)
+
+
 def test_response_full_height_1080p(ctx, oracle_port):
     """A 1080-row box: 34 chunks through the ring, 16 boxes across (config 5 geometry)."""
     img = _image(1920, 1080, 123)
