@@ -33,10 +33,10 @@ UNIT = "stereo pairs/s"
 # 1500 x 8 B corner list it ultimately yields
 RESP_BYTES_PER_IMAGE = W_IMG * H_IMG + NUM_FEATURES * 8
 # DRAM traffic of the response kernel per image, from the ncu --set full capture of the same kernel
-# at the bench's own launch size (profiles/r1v_response_raw.txt: dram__bytes_read.sum 1.446291 GB +
-# dram__bytes_write.sum 138.02 MB for 4000 images): the image is read once (1.00x its size), the rest is the
+# at the bench's own launch size (profiles/r1x_response_raw.txt: dram__bytes_read.sum 1.444258 GB +
+# dram__bytes_write.sum 136.05 MB for 4000 images): the image is read once (1.00x its size), the rest is the
 # candidate list.
-RESP_DRAM_BYTES_PER_IMAGE = (1.446291e9 + 138.018304e6) / 4000
+RESP_DRAM_BYTES_PER_IMAGE = (1.444258e9 + 136.047616e6) / 4000
 
 
 def parse():
@@ -301,7 +301,7 @@ def run_ours(args):
         "roofline": {"kernel": "response_kernel (Sobel+cov+box+min-eig+local-max, TMA tiles)", "bound": "hbm",
                      "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": RESP_DRAM_BYTES_PER_IMAGE * 2 * n_pairs,
-                     "traffic_source": "ncu --set full, profiles/r1v_response_raw.txt (per image x images per launch)",
+                     "traffic_source": "ncu --set full, profiles/r1x_response_raw.txt (per image x images per launch)",
                      "ms_per_launch": resp_ms, "algorithmic_bytes_per_launch": RESP_BYTES_PER_IMAGE * 2 * n_pairs},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "timing": "CUDA events around the synchronous C-ABI calls (rank-0 host wall clock: %.1f ms/step)"
