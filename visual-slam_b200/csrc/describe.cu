@@ -131,7 +131,7 @@ __device__ __forceinline__ void rotate_pair(double c, double s, char4 q, double&
 }
 
 template <bool kContract>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 8) orient_describe_kernel(const DescribeParams p) {
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 6) orient_describe_kernel(const DescribeParams p) {
   __shared__ __align__(16) unsigned char patch_all[kWarpsPerCta][2][kPatchRows * kPatchPitch];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int img = blockIdx.y;
