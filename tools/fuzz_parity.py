@@ -7,7 +7,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 import oracle, visnav_b200
 from visnav_b200 import workloads as wl
-from visnav_b200.keypoints import DescStore
+from visnav_b200.keypoints import DescStore, VSLAM_OPT_RESPONSE_BAND
 
 budget = float(os.environ.get("FUZZ_SECONDS", "60"))
 seed = int(os.environ.get("FUZZ_SEED", "1"))
@@ -21,6 +21,8 @@ while time.time() < t_end and len(stats["failures"]) < 5:
     it += 1
     kind = it % 4
     w, h = int(rng.integers(40, 1300)), int(rng.integers(40, 900))
+    # box height of the response kernel: chosen by the library, the whole image, or anything in between
+    ctx.set_option(VSLAM_OPT_RESPONSE_BAND, [0, 65535, int(rng.integers(8, 300))][it % 3])
     if kind == 0:
         img = wl.synth_image(int(rng.integers(0, 1 << 30)), w, h)
     elif kind == 1:
