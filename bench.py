@@ -37,6 +37,7 @@ RESP_BYTES_PER_IMAGE = W_IMG * H_IMG + NUM_FEATURES * 8
 # dram__bytes_write.sum 136.05 MB for 4000 images): the image is read once (1.00x its size), the rest is the
 # candidate list.
 RESP_DRAM_BYTES_PER_IMAGE = (1.444258e9 + 136.047616e6) / 4000
+CPU_GFTT_IMPL = "?"
 
 
 def parse():
@@ -116,6 +117,12 @@ def cpu_pairs_per_s(pairs, n_threads, budget_s=20.0):
     kind = "reference"
     if lib is None:
         lib, kind = oracle.load_oracle(), "port"
+    elif not lib.has_opencv:
+        kind = "reference+port"      # reference functions, goodFeaturesToTrack = C restatement (OpenCV not built)
+    else:
+        lib.set_num_threads(1)       # one OpenCV thread per worker: the workers are the parallelism
+    global CPU_GFTT_IMPL
+    CPU_GFTT_IMPL = lib.gftt_impl
 
     t0 = time.perf_counter()
     deadline = t0 + budget_s
@@ -186,9 +193,10 @@ def run_reference(args):
         t_tot += time.perf_counter() - t0
         n_tot += done
     v = n_tot / t_tot
-    sample_txt = ("%d synthetic 752x480 stereo pairs per step on %d host threads; angles/descriptors/matching are the "
-                  "reference's own functions compiled from keypoints.h (oracle/_ref), goodFeaturesToTrack is the C "
-                  "restatement pinned to cv2 (vendored OpenCV needs cmake -> unbuildable by rule)" % (sample, cores))
+    sample_txt = ("%d synthetic 752x480 stereo pairs per step on %d host threads (one pair per thread at a time, "
+                  "cv::setNumThreads(1)); detectKeypoints/computeAngles/computeDescriptors/matchDescriptors are the "
+                  "reference's own functions compiled from keypoints.h (oracle/_ref); cv::goodFeaturesToTrack = %s"
+                  % (sample, cores, CPU_GFTT_IMPL))
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / max(args.steps, 1), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32/f64/u32 (cpu)", "data": "synthetic",
@@ -329,7 +337,7 @@ def run_ours(args):
         v, done, kind = cpu_pairs_per_s(distinct[:sample], cores, budget_s=20.0)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
                                 "sample": "%d of the same synthetic pairs on %d host threads (reference functions from "
-                                          "keypoints.h in oracle/_ref; gftt = C restatement pinned to cv2)" % (done, cores)}
+                                          "keypoints.h in oracle/_ref; cv::goodFeaturesToTrack = %s)" % (done, cores, CPU_GFTT_IMPL)}
     emit(line)
     if dist is not None:
         dist.destroy_process_group()

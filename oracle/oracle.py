@@ -75,6 +75,46 @@ class Oracle:
             lib.vso_best2.restype = None
             lib.vso_best2.argtypes = [_u32p, C.c_int, _u32p, C.c_int, _i32p]
 
+        self.gftt_impl = "port (C restatement vso_gftt)"
+        if kind == "reference" and hasattr(lib, "ref_gftt_impl"):
+            lib.ref_gftt_impl.restype = C.c_char_p
+            self.gftt_impl = lib.ref_gftt_impl().decode()
+        self.has_opencv = kind == "reference" and hasattr(lib, "ref_gftt")
+        if self.has_opencv:
+            lib.ref_set_use_optimized.restype = None
+            lib.ref_set_use_optimized.argtypes = [C.c_int]
+            lib.ref_set_num_threads.restype = None
+            lib.ref_set_num_threads.argtypes = [C.c_int]
+            lib.ref_gftt.restype = C.c_int
+            lib.ref_gftt.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, C.c_int,
+                                     C.c_double, _f32p, C.c_int]
+            lib.ref_corner_response.restype = None
+            lib.ref_corner_response.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, _f32p]
+
+    # --- the reference's vendored OpenCV (only in oracle/_ref/libvisnav_ref.so built with it) -----------
+    def set_use_optimized(self, on):
+        """cv::setUseOptimized of the vendored build: False = scalar dispatch (the bit-exact pin)."""
+        self.lib.ref_set_use_optimized(int(bool(on)))
+
+    def set_num_threads(self, n):
+        self.lib.ref_set_num_threads(int(n))
+
+    def cv_gftt(self, img, max_corners, quality=0.01, min_distance=8.0, block_size=3, harris=False, k=0.04):
+        """cv::goodFeaturesToTrack of the vendored OpenCV (featureselect.cpp:382-548)."""
+        img, w, h, pitch = _img(img)
+        cap = max_corners if max_corners > 0 else w * h
+        xy = np.empty((cap, 2), np.float32)
+        n = self.lib.ref_gftt(_p(img, _u8p), w, h, pitch, max_corners, quality, min_distance, block_size, int(harris), k,
+                              _p(xy, _f32p), cap)
+        return xy[:min(n, cap)].copy()
+
+    def cv_response(self, img, block_size=3, ksize=3, harris=False, k=0.04):
+        """cv::cornerMinEigenVal / cv::cornerHarris of the vendored OpenCV."""
+        img, w, h, pitch = _img(img)
+        out = np.empty((h, w), np.float32)
+        self.lib.ref_corner_response(_p(img, _u8p), w, h, pitch, block_size, ksize, int(harris), k, _p(out, _f32p))
+        return out
+
     def set_harris(self, on, k=0.04):
         """goodFeaturesToTrack(useHarrisDetector, k) for the restatement's detection functions (port only)."""
         self.lib.vso_set_harris(int(bool(on)), float(k))

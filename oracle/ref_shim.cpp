@@ -11,10 +11,12 @@
 // product that is never committed -- and this file supplies the few types the
 // extract needs.  No reference source lives in this repository.
 //
-// cv::goodFeaturesToTrack: the vendored OpenCV needs its cmake-generated headers
-// and dispatch files to build, so it is treated as unbuildable here.
-// The shim routes the reference's call (keypoints.h:138-139) to the C restatement
-// vso_gftt, which is pinned separately against cv2 (tests/golden/gftt_*.npz).
+// cv::goodFeaturesToTrack: with -DVSO_REF_WITH_OPENCV (the default whenever oracle/build_opencv.sh
+// produced the static libraries) the reference's call (keypoints.h:138-139) reaches the reference's OWN
+// vendored OpenCV 4.7.0-dev (thirdparty/opencv, modules core + imgproc, built where it lies by its own
+// cmake files into a scratch directory; featureselect.cpp:382-548) -- the stock code path, AVX2/FMA
+// dispatch and all.  Without the define (no cmake, no /root/reference) the call is routed to the C
+// restatement vso_gftt and ref_gftt_impl() says so; bench.py then labels the arm "reference+port".
 #include <bitset>
 #include <cmath>
 #include <cstddef>
@@ -51,6 +53,11 @@ struct Vector2d {
 };
 }  // namespace Eigen
 
+#ifdef VSO_REF_WITH_OPENCV
+#include <opencv2/core.hpp>
+#include <opencv2/core/utility.hpp>
+#include <opencv2/imgproc.hpp>
+#else
 #define CV_8U 0
 namespace cv {
 struct Point2f { float x, y; };
@@ -72,6 +79,7 @@ inline void goodFeaturesToTrack(const Mat& image, std::vector<Point2f>& pts, int
   for (int i = 0; i < n; i++) pts.push_back(Point2f{xy[2 * i], xy[2 * i + 1]});
 }
 }  // namespace cv
+#endif
 
 // Mirrors visnav::KeypointsData (include/visnav/common_types.h:111-122).
 namespace visnav {
@@ -142,5 +150,41 @@ int ref_match(const uint32_t* d1, int n1, const uint32_t* d2, int n2, int thresh
   for (int i = 0; i < m && i < cap; i++) { pairs[2 * i] = matches[i].first; pairs[2 * i + 1] = matches[i].second; }
   return m;
 }
+
+// Which goodFeaturesToTrack this library runs (bench.py / tests label the CPU arm with it).
+const char* ref_gftt_impl(void) {
+#ifdef VSO_REF_WITH_OPENCV
+  return "opencv " CV_VERSION " (the reference's vendored thirdparty/opencv: core+imgproc static, no IPP/TBB)";
+#else
+  return "port (C restatement vso_gftt; vendored OpenCV not built)";
+#endif
+}
+
+#ifdef VSO_REF_WITH_OPENCV
+// cv::setUseOptimized / cv::setNumThreads of the vendored build: the scalar dispatch is the bit-exact pin of
+// the response map, the default (AVX2/FMA) dispatch is what a stock build of the reference executes.
+void ref_set_use_optimized(int on) { cv::setUseOptimized(on != 0); }
+void ref_set_num_threads(int n) { cv::setNumThreads(n); }
+
+// cv::goodFeaturesToTrack alone (featureselect.cpp:382-548): xy[cap][2] float, returns the count.
+int ref_gftt(const uint8_t* img, int w, int h, int pitch, int max_corners, double quality, double min_distance,
+             int block_size, int use_harris, double k, float* xy, int cap) {
+  cv::Mat image(h, w, CV_8U, const_cast<uint8_t*>(img), (size_t)pitch);
+  std::vector<cv::Point2f> pts;
+  cv::goodFeaturesToTrack(image, pts, max_corners, quality, min_distance, cv::noArray(), block_size, use_harris != 0, k);
+  int n = (int)pts.size();
+  for (int i = 0; i < n && i < cap; i++) { xy[2 * i] = pts[i].x; xy[2 * i + 1] = pts[i].y; }
+  return n;
+}
+
+// cv::cornerMinEigenVal / cv::cornerHarris (corner.cpp:237-322, 700-760): the response map gftt thresholds.
+void ref_corner_response(const uint8_t* img, int w, int h, int pitch, int block_size, int ksize, int use_harris,
+                         double k, float* out) {
+  cv::Mat image(h, w, CV_8U, const_cast<uint8_t*>(img), (size_t)pitch);
+  cv::Mat dst(h, w, CV_32F, out);
+  if (use_harris) cv::cornerHarris(image, dst, block_size, ksize, k);
+  else cv::cornerMinEigenVal(image, dst, block_size, ksize);
+}
+#endif
 
 }  // extern "C"
