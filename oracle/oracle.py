@@ -72,6 +72,8 @@ class Oracle:
             lib.vso_gftt.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, _f32p, C.c_int]
             lib.vso_set_harris.restype = None
             lib.vso_set_harris.argtypes = [C.c_int, C.c_double]
+            lib.vso_set_box_direct.restype = None
+            lib.vso_set_box_direct.argtypes = [C.c_int]
             lib.vso_best2.restype = None
             lib.vso_best2.argtypes = [_u32p, C.c_int, _u32p, C.c_int, _i32p]
 
@@ -114,6 +116,10 @@ class Oracle:
         out = np.empty((h, w), np.float32)
         self.lib.ref_corner_response(_p(img, _u8p), w, h, pitch, block_size, ksize, int(harris), k, _p(out, _f32p))
         return out
+
+    def set_box_direct(self, on):
+        """0: OpenCV's running column sum in the box filter (default); 1: direct three-row sum (port only)."""
+        self.lib.vso_set_box_direct(int(bool(on)))
 
     def set_harris(self, on, k=0.04):
         """goodFeaturesToTrack(useHarrisDetector, k) for the restatement's detection functions (port only)."""

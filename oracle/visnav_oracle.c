@@ -65,6 +65,9 @@ static inline int r101(int i, int n) {
 static int g_harris_on = 0;
 static double g_harris_k = 0.04;
 void vso_set_harris(int on, double k) { g_harris_on = on; g_harris_k = k; }
+/* 0 (default): OCV's running column sum; 1: direct three-row sum (see the column pass in vso_response). */
+static int g_box_direct = 0;
+void vso_set_box_direct(int on) { g_box_direct = on; }
 
 int vso_response(const uint8_t* img, int w, int h, int pitch, float* lam) {
   if (!img || !lam || w <= 0 || h <= 0 || pitch < w) return -1;
@@ -116,15 +119,38 @@ int vso_response(const uint8_t* img, int w, int h, int pitch, float* lam) {
         rs[((size_t)y * w + x) * 3 + k] = v;
       }
     }
+  /* Column pass of the box filter.  OCV's ColumnSum<double,float> (box_filter.simd.hpp:189-262) keeps ONE running
+   * sum per column and channel: SUM = 0 + R(-1) + R(0) before the first row (:206-216, rows reflected), then per
+   * output row y:  s0 = SUM + R(y+1);  D = (float)s0;  SUM = s0 - R(y-1)  (:248-262).  Where one of these double
+   * additions is inexact the residue travels down the column, so the result can differ in the last bit from the
+   * direct three-row sum (R(y-1) + R(y)) + R(y+1) -- which vso_set_box_direct(1) selects instead (what a row-banded
+   * evaluation computes; tests bound the difference). */
+  double* SUM = (double*)malloc((size_t)w * 3 * sizeof(double));
+  if (!SUM) { free(rdx); free(rdy); free(cov); free(rs); return -2; }
+  {
+    const double* r_m1 = rs + (size_t)r101(-1, h) * w * 3;
+    for (size_t i = 0; i < (size_t)w * 3; i++) {
+      double v = 0.0;
+      v = v + r_m1[i];
+      v = v + rs[i];
+      SUM[i] = v;
+    }
+  }
   for (int y = 0; y < h; y++) {
     int ym = r101(y - 1, h), yp = r101(y + 1, h);
     for (int x = 0; x < w; x++) {
       float abc[3];
       for (int k = 0; k < 3; k++) {
-        double v = rs[((size_t)ym * w + x) * 3 + k];
-        v = v + rs[((size_t)y * w + x) * 3 + k];
-        v = v + rs[((size_t)yp * w + x) * 3 + k];
-        abc[k] = (float)v;
+        if (g_box_direct) {
+          double v = rs[((size_t)ym * w + x) * 3 + k];
+          v = v + rs[((size_t)y * w + x) * 3 + k];
+          v = v + rs[((size_t)yp * w + x) * 3 + k];
+          abc[k] = (float)v;
+        } else {
+          double s0 = SUM[(size_t)x * 3 + k] + rs[((size_t)yp * w + x) * 3 + k];
+          abc[k] = (float)s0;
+          SUM[(size_t)x * 3 + k] = s0 - rs[((size_t)ym * w + x) * 3 + k];
+        }
       }
       if (g_harris_on) {
         const size_t i = (size_t)y * w + x;
@@ -155,7 +181,7 @@ int vso_response(const uint8_t* img, int w, int h, int pitch, float* lam) {
       lam[(size_t)y * w + x] = p - q;
     }
   }
-  free(rdx); free(rdy); free(cov); free(rs);
+  free(rdx); free(rdy); free(cov); free(rs); free(SUM);
   return 0;
 }
 
