@@ -64,6 +64,11 @@ typedef struct vslam_desc_store vslam_desc_store;
 #define VSLAM_OPT_RESPONSE_BAND 6 /* output rows per box of the corner-response kernel.  0 (default): chosen per launch
                                     (the whole image height when the batch fills the SMs, else bands of <= 64 rows);
                                     >= 8: forced.  Results identical. */
+#define VSLAM_OPT_MATCH_MMA 7 /* 1 (default): batches of matching jobs that fill the GPU (stereo plans / vslam_stereo_batch
+                                 chunks, vslam_match_batch) compute the Hamming matrix on the tensor cores (tcgen05.mma
+                                 kind::i8 on descriptors expanded to signed bytes: dot = 256 - 2 * hamming, exact);
+                                 0: the POPC kernels; 2: the tensor cores for every batch, however small (tests).
+                                 Results identical. */
 
 /* ---- context ------------------------------------------------------------------------ */
 int vslam_create(int device, vslam_ctx** out);
@@ -342,6 +347,9 @@ int vslam_event_elapsed_ms(vslam_ctx* ctx, int slot_a, int slot_b, float* ms);
 /* Register-only POPC throughput microbenchmark: popc.b32 instructions per second (thread
  * level) sustained over all SMs -- the measured denominator of the matching roofline. */
 int vslam_popc_peak(vslam_ctx* ctx, double* popc_per_s);
+/* 1 if a bounded pipeline wait of the tensor-core matcher ever ran out in this process (a bug, never in a correct
+ * run: the job then reports count -2 instead of hanging the GPU), 0 if not, < 0 on a CUDA error. */
+int vslam_debug_mma_timeouts(vslam_ctx* ctx);
 
 #ifdef __cplusplus
 }

@@ -132,6 +132,7 @@ int vslam_set_option(vslam_ctx* ctx, int option, int value) {
   if (option == VSLAM_OPT_FP_CONTRACT) ctx->fp_contract = value != 0;
   else if (option == VSLAM_OPT_MATCH_CSA) ctx->match_csa = value != 0;
   else if (option == VSLAM_OPT_MATCH_SPLIT_SMALL) ctx->match_split_small = value != 0;
+  else if (option == VSLAM_OPT_MATCH_MMA && value >= 0 && value <= 2) ctx->match_mma = value;
   else if (option == VSLAM_OPT_RESPONSE_BAND && (value == 0 || (value >= 8 && value <= 65535))) ctx->resp_band = value;
   else if (option == VSLAM_OPT_BATCH_CHUNK && value >= 1 && value <= 4096) ctx->batch_chunk = value;
   else if (option == VSLAM_OPT_BATCH_DEPTH && value >= 1 && value <= vslam_ctx::kMaxBatchDepth) ctx->batch_depth = value;
@@ -501,6 +502,14 @@ int vslam_popc_peak(vslam_ctx* ctx, double* popc_per_s) {
   return launch_popc_peak(ctx, popc_per_s);
 }
 
+int vslam_debug_mma_timeouts(vslam_ctx* ctx) {
+  if (!ctx) return VSLAM_E_ARG;
+  VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  int flag = 0;
+  if (match_mma_timeouts(&flag)) return vs_fail(ctx, VSLAM_E_CUDA, "cannot read the matcher's timeout flag");
+  return flag;
+}
+
 }  // extern "C"
 
 // ---- stereo plan --------------------------------------------------------------------------------------
@@ -510,6 +519,7 @@ struct vslam_stereo_plan {
   int w = 0, h = 0, max_pairs = 0, cap = 0;
   DevImages im{};
   DevBuf images, xy, ang, desc, nkp, matches, nmatch, jobs;
+  DevBuf descx;  // the descriptors as 256 signed bytes each: operands of the tensor-core matcher (match_mma.cu)
   DevBuf cand, candcnt, imgmax, selws;
   DevBuf mrow, mcol;            // scratch of the small-batch column-split matcher (plans run on their own streams)
   DevBuf inliers, ninl, epiws;  // optional fused findInliersEssential stage (vslam_stereo_plan_set_epipolar)
@@ -529,7 +539,7 @@ void vslam_stereo_plan_destroy(vslam_stereo_plan* plan) {
   cudaDeviceSynchronize();
   DevBuf* bufs[] = {&plan->images, &plan->xy, &plan->ang, &plan->desc, &plan->nkp, &plan->matches, &plan->nmatch,
                     &plan->jobs, &plan->cand, &plan->candcnt, &plan->imgmax, &plan->selws, &plan->inliers,
-                    &plan->ninl, &plan->epiws, &plan->mrow, &plan->mcol};
+                    &plan->ninl, &plan->epiws, &plan->mrow, &plan->mcol, &plan->descx};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 6; ++i)
     if (plan->ev[i]) cudaEventDestroy(plan->ev[i]);
@@ -636,9 +646,26 @@ int vslam_stereo_plan_run(vslam_stereo_plan* plan, int count, int num_features, 
     rc = launch_orient_describe(ctx, plan->im, nimg, plan->xy.as<double>(), plan->nkp.as<int32_t>(), plan->cap,
                                 rotate ? 1 : 0, plan->ang.as<double>(), plan->desc.as<uint32_t>());
   cudaEventRecord(plan->ev[3], ctx->stream);
-  if (!rc)
-    rc = launch_match_jobs(ctx, plan->jobs.as<MatchJob>(), count, plan->cap, plan->cap, match_threshold,
-                           match_dist_2_best, plan->cap, &plan->mrow, &plan->mcol);
+  if (!rc) {
+    // enough jobs to fill the GPU with one CTA per SM: Hamming matrix on the tensor cores; else the POPC kernels
+    // (whose column-split path spreads a few jobs over all SMs)
+    if ((ctx->match_mma == 2 || (ctx->match_mma && 2 * count >= ctx->num_sms)) && match_mma_fits(plan->cap, plan->cap)) {
+      const long long rows = (long long)nimg * plan->cap;
+      if (!plan->descx.p) {
+        VS_CUDA(ctx, plan->descx.reserve((size_t)2 * plan->max_pairs * plan->cap * 256));
+        VS_CUDA(ctx, cudaMemsetAsync(plan->descx.p, 0, plan->descx.bytes, ctx->stream));
+      }
+      rc = launch_expand_desc(ctx, plan->desc.as<uint32_t>(), rows, plan->cap, plan->nkp.as<int32_t>(),
+                              plan->descx.as<uint8_t>());
+      const MatchExpanded x = {plan->desc.as<uint32_t>(), plan->descx.as<uint8_t>(), rows};
+      if (!rc)
+        rc = launch_match_jobs_mma(ctx, plan->jobs.as<MatchJob>(), count, plan->cap, plan->cap, match_threshold,
+                                   match_dist_2_best, plan->cap, x, x);
+    } else {
+      rc = launch_match_jobs(ctx, plan->jobs.as<MatchJob>(), count, plan->cap, plan->cap, match_threshold,
+                             match_dist_2_best, plan->cap, &plan->mrow, &plan->mcol);
+    }
+  }
   cudaEventRecord(plan->ev[4], ctx->stream);
   if (!rc && plan->epi_on) {
     // matching_utils.h:63-88 on the matcher's device output: left corners of pair k are image 2k, right 2k+1
@@ -941,6 +968,8 @@ int vslam_pyramid_detect_describe_batch(vslam_ctx* ctx, const uint8_t* images, i
 struct vslam_desc_store {
   vslam_ctx* ctx = nullptr;
   DevBuf desc, offsets, counts;
+  DevBuf descx;               // descriptors as signed bytes (tensor-core matcher), rows [0, expanded) are current
+  int64_t expanded = 0;
   int n_sets = 0;
   int max_count = 0;
   // host mirrors, so that sets can be appended (vslam_desc_store_append) without reading the device back
@@ -971,6 +1000,7 @@ void vslam_desc_store_destroy(vslam_desc_store* s) {
   cudaSetDevice(s->ctx->device);
   cudaDeviceSynchronize();
   s->desc.release();
+  s->descx.release();
   s->offsets.release();
   s->counts.release();
   delete s;
@@ -1055,6 +1085,16 @@ int vslam_match_batch(vslam_ctx* ctx, const vslam_desc_store* s, const int32_t* 
   VS_CUDA(ctx, ctx->jobs.reserve((size_t)chunk * (sizeof(MatchJob) + 8)));
   MatchJob* jobs_dev = ctx->jobs.as<MatchJob>();
   int32_t* ji_dev = reinterpret_cast<int32_t*>(jobs_dev + chunk);
+  // batches that fill the GPU run on the tensor cores: bring the signed-byte copy of the store up to date first
+  const bool use_mma = (ctx->match_mma == 2 || (ctx->match_mma && 2 * n_jobs >= ctx->num_sms)) && match_mma_fits(s->max_count, s->max_count) && s->total > 0;
+  if (use_mma && s->expanded < s->total) {
+    vslam_desc_store* ms = const_cast<vslam_desc_store*>(s);
+    VS_CUDA(ctx, grow_preserve(ms->descx, (size_t)(s->total + 1) * 256, (size_t)s->expanded * 256));
+    const int rc = launch_expand_desc(ctx, s->desc.as<uint32_t>() + (size_t)s->expanded * 8, s->total - s->expanded, 1, nullptr,
+                                      ms->descx.as<uint8_t>() + (size_t)s->expanded * 256);
+    if (rc) return rc;
+    ms->expanded = s->total;
+  }
   float total_ms = 0.f;
   for (int c0 = 0; c0 < n_jobs; c0 += chunk) {
     const int nc = n_jobs - c0 < chunk ? n_jobs - c0 : chunk;
@@ -1063,7 +1103,14 @@ int vslam_match_batch(vslam_ctx* ctx, const vslam_desc_store* s, const int32_t* 
     int rc = launch_build_store_jobs(ctx, ji_dev, nc, s->desc.as<uint32_t>(), s->offsets.as<int64_t>(),
                                      s->counts.as<int32_t>(), s->n_sets, ctx->pairs.as<int32_t>(),
                                      ctx->mcnt.as<int32_t>(), cap, jobs_dev);
-    if (!rc) rc = launch_match_jobs(ctx, jobs_dev, nc, s->max_count, s->max_count, threshold, dist_2_best, cap);
+    if (!rc) {
+      if (use_mma) {
+        const MatchExpanded x = {s->desc.as<uint32_t>(), s->descx.as<uint8_t>(), (long long)s->total};
+        rc = launch_match_jobs_mma(ctx, jobs_dev, nc, s->max_count, s->max_count, threshold, dist_2_best, cap, x, x);
+      } else {
+        rc = launch_match_jobs(ctx, jobs_dev, nc, s->max_count, s->max_count, threshold, dist_2_best, cap);
+      }
+    }
     if (rc) return rc;
     VS_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
     if (matches) VS_CUDA(ctx, cudaMemcpyAsync(matches + (size_t)c0 * cap * 2, ctx->pairs.p, (size_t)nc * per_job, cudaMemcpyDeviceToHost, ctx->stream));

@@ -46,12 +46,14 @@ struct vslam_ctx {
   double harris_k = 0.04;  // cv::goodFeaturesToTrack's default k
   int resp_band = 0;  // response kernel: forced box height (0 = chosen per launch)
   int match_split_small = 1;  // batches with fewer jobs than SMs/2: split every job's columns over CTAs
+  int match_mma = 1;          // batches with at least SMs/2 jobs: Hamming matrix on the tensor cores (match_mma.cu)
   long long launches = 0;
   float last_match_ms = 0.f;
   // scratch for the single-call entry points
   DevBuf img, xy, ang, desc, cnt, lam;
   DevBuf cand, candcnt, imgmax, selws;
   DevBuf d1, d2, pairs, mcnt, rowpart, colstat, jobs;
+  DevBuf d1x, d2x;  // expanded (signed byte) copies of d1 / d2 for the tensor-core matcher
   DevBuf lm;  // vslam_match_landmarks staging
   DevBuf geo;  // geometry.cu staging (camera models, essential inliers, landmark projection)
   // orb.cu: pyramid, blurred pyramid, candidates, counters, keypoints, descriptors, staging, rotations, tables, batch
@@ -140,6 +142,22 @@ int launch_build_store_jobs(vslam_ctx* ctx, const int32_t* jobs_i2, int n_jobs, 
                             const int64_t* offsets, const int32_t* counts, int n_sets, int32_t* pairs,
                             int32_t* out_counts, int cap, MatchJob* out);
 int launch_popc_peak(vslam_ctx* ctx, double* popc_per_s);
+// match_mma.cu: the same jobs with the Hamming matrix on the tensor cores (tcgen05.mma kind::i8).  The jobs' d1 / d2
+// must point into the packed arrays x1.packed / x2.packed; `expanded` holds those arrays' descriptors as 256 signed
+// bytes each (launch_expand_desc), row r = the descriptor at packed + 8 r.
+struct MatchExpanded {
+  const uint32_t* packed;
+  const uint8_t* expanded;
+  long long rows;
+};
+bool match_mma_fits(int max_n1, int max_n2);
+// rows_per_set / n_valid: optional (n_valid may be nullptr): only the first n_valid[set] rows of every set of
+// rows_per_set rows are expanded (the describe stage's fixed-stride slabs)
+int launch_expand_desc(vslam_ctx* ctx, const uint32_t* desc, long long rows, int rows_per_set, const int32_t* n_valid,
+                       uint8_t* expanded);
+int launch_match_jobs_mma(vslam_ctx* ctx, const MatchJob* jobs_dev, int n_jobs, int max_n1, int max_n2, int threshold,
+                          double ratio, int cap, const MatchExpanded& x1, const MatchExpanded& x2);
+int match_mma_timeouts(int* flag);
 // pyramid.cu: dst level = 2x2 rounded mean of src (dst.w = src.w / 2, dst.h = src.h / 2)
 int launch_pyr_down(vslam_ctx* ctx, const DevImages& src, const DevImages& dst, int count);
 // orb.cu: cv::ORB front end on images already on the device; outputs stay on the device

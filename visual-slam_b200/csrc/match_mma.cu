@@ -1,0 +1,514 @@
+// match_mma.cu -- matchDescriptors with the all-pairs Hamming matrix on the 5th-generation tensor cores (sm_100a).
+//
+// Semantics: visnav::matchDescriptors + isPQiffQP (reference include/visnav/keypoints.h:323-369, 278-313), the same
+// predicate match.cu implements on the integer pipes (see its header): T(q, D) = (m1, a1, m2), threshold, ratio test,
+// mutual check, matches in ascending first index.
+//
+// The distance matrix is an exact integer contraction: with every descriptor bit b stored as the signed byte 2b - 1,
+//     dot(sa, sb) = #equal bits - #different bits = 256 - 2 * hamming(a, b),
+// which tcgen05.mma kind::i8 (s8 x s8 -> s32, K = 256 = 8 instructions of K = 32) computes without rounding.  Measured
+// (tools/probes/umma_hamming.cu, profiles/r2a_umma_hamming_probe.jsonl): 8.3e12 distances/s for the MMA alone, against
+// 6.6e11 for the POPC kernel of match.cu, 2.0e12 for mma.sync u8 and 8.2e11 for mma.sync b1 and.popc.
+//
+// Layout: descriptors are EXPANDED once per set to 256 signed bytes (expand_desc_kernel; the describe stage's output is
+// expanded right behind it, a keyframe store at append time).  One CTA owns one job (one matchDescriptors call) at a
+// time, persistent over the batch, warp-specialised:
+//   warp 8  (one lane)  TMA producer: 128-descriptor operand tiles ([2 K halves][128 rows][128 B], 128-byte swizzle,
+//                       K-major) -- kGroup tiles of desc1 stay resident while the tiles of desc2 stream through a ring
+//   warp 9  (one lane)  MMA issuer: per (desc1 tile, desc2 tile) TWO 128 x 128 products into one TMEM stage,
+//                       D1 = A * B^T (rows = desc1) and D2 = B * A^T (rows = desc2): both directions of the reference's
+//                       test become ROW statistics, so no reduction ever crosses threads
+//   warps 0-3 / 4-7     epilogue of D1 / D2: thread = one TMEM lane = one matrix row; tcgen05.ld 32 columns at a time;
+//                       two distances per register as 16-bit keys (hamming << 7 | column) built by two IMADs on the FMA
+//                       pipe, (min, second min) kept with VIMNMX.U16x2 (3 ALU instructions per TWO distances); per tile
+//                       the pair is widened to the 32-bit keys of match.cu and merged into the row's running
+//                       statistics in shared memory
+// Two TMEM stages (2 x 256 columns = the whole TMEM) let the MMA of the next tile pair run under the epilogue of the
+// current one.  The ratio test, the mutual check and the ordered compaction run in the same CTA on the epilogue warps
+// while the producer / MMA warps already work on the next job.
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int kTile = 128;                 // descriptors per operand tile = UMMA M = UMMA N
+constexpr int kHalfBytes = kTile * 128;    // one K half of a tile: [128 rows][128 B]
+constexpr int kTileBytes = 2 * kHalfBytes; // 32 KB
+constexpr int kGroup = 2;                  // desc1 tiles resident per pass over desc2
+constexpr int kBStages = 3;                // ring of desc2 tiles
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = (kEpiWarps + 2) * 32;
+constexpr uint32_t kShift = 20;            // 32-bit key = distance << 20 | index (as in match.cu)
+constexpr uint32_t kIdxMask = (1u << kShift) - 1;
+constexpr uint32_t kSent = 256u << kShift;
+constexpr int kMaxIndex = 1 << kShift;
+constexpr uint32_t kSpinLimit = 1u << 26;
+
+__device__ int g_mma_timeout;  // a bounded wait ran out (never in a correct run): read by vslam_debug_mma_timeouts
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// Bounded wait.  A wait that runs out (a pipeline bug; never in a correct run) raises the CTA's fail flag and the global
+// one; every later wait of the CTA then returns at once, all roles keep walking their loops (so that every barrier is
+// still reached by everybody) and the job's result is reported as an error instead of hanging the GPU.
+__device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, volatile int* fail) {
+  uint32_t ok = 0;
+  for (uint32_t it = 0; it < kSpinLimit; ++it) {
+    if ((it & 1023u) == 1023u && *fail) return false;
+    asm volatile(
+        "{\n.reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (ok) return true;
+  }
+  *fail = 1;
+  atomicExch(&g_mma_timeout, 1);
+  return false;
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* tm, void* dst, uint64_t* bar, int x, int y) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+          smem_u32(dst)),
+      "l"(tm), "r"(x), "r"(y), "r"(smem_u32(bar))
+      : "memory");
+}
+// K-major operand in shared memory under the 128-byte swizzle TMA wrote: rows 128 B apart, 8-row groups 1024 B apart
+// (SmemDescriptor: start >> 4 | LBO(unused) 1 << 16 | SBO 64 << 32 | version 1 << 46 | SWIZZLE_128B 2 << 61).
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+  return (uint64_t)((saddr >> 4) & 0x3FFF) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::i8: D s32 (2 << 4), A / B signed 8 bit (1 << 7, 1 << 10), both K-major, N >> 3 at bit 17, M >> 4 at bit 24
+constexpr uint32_t kIdesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kTile >> 3) << 17) | ((uint32_t)(kTile >> 4) << 24);
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t accumulate) {
+  asm volatile(
+      "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n}\n" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(kIdesc), "r"(accumulate), "r"(0u)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,"
+      "%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+        "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+        "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+        "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory"); }
+
+// ---- expansion: bit b of a descriptor -> signed byte 2b - 1 (0x01 / 0xFF) -------------------------------------------
+// One thread per (descriptor, 16-bit group): one 16-byte store.  rows_per_set / n_valid (optional): descriptors are
+// stored in sets of rows_per_set rows of which only the first n_valid[set] exist (the describe stage's slabs).
+__global__ void expand_desc_kernel(const uint32_t* __restrict__ desc, long long rows, int rows_per_set,
+                                   const int32_t* __restrict__ n_valid, uint8_t* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= rows * 16) return;
+  const long long d = i >> 4;
+  const int g = (int)(i & 15);
+  if (n_valid) {
+    const long long set = d / rows_per_set;
+    if ((int)(d - set * rows_per_set) >= n_valid[set]) return;
+  }
+  const uint32_t bits = (desc[d * 8 + (g >> 1)] >> ((g & 1) * 16)) & 0xFFFFu;
+  uint32_t w[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const uint32_t nib = (bits >> (4 * q)) & 0xFu;
+    const uint32_t b = (nib * 0x00204081u) & 0x01010101u;  // bit k of the nibble -> byte k (0 / 1)
+    w[q] = b | ((b ^ 0x01010101u) * 0xFFu);                // 1 -> 0x01, 0 -> 0xFF
+  }
+  reinterpret_cast<uint4*>(out)[i] = make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+struct MmaParams {
+  const MatchJob* jobs;
+  int n_jobs;
+  const uint32_t* base1;  // packed descriptor arrays the jobs' d1 / d2 point into; row r of the expanded array under
+  const uint32_t* base2;  // tmap1 / tmap2 is the descriptor at base + 8 r
+  int threshold;
+  double ratio;
+  int cap;
+  int max_n1, max_n2;
+};
+
+struct MmaSmem {
+  uint8_t a[kGroup][kTileBytes];
+  uint8_t b[kBStages][kTileBytes];
+  uint64_t a_full, a_empty;
+  uint64_t b_full[kBStages], b_empty[kBStages];
+  uint64_t t_full[2], t_empty[2];
+  uint32_t tmem_base;
+  int warp_sums[kEpiWarps];
+  int running;
+  int fail;
+};
+
+__device__ __forceinline__ bool passes(uint32_t m1, uint32_t m2, int threshold, double ratio) {
+  // keypoints.h:355-357: best1_d >= threshold -> no; best2_d < best1_d * dist_2_best -> no.
+  if ((int)m1 >= threshold) return false;
+  return !((double)(int)m2 < __dmul_rn((double)(int)m1, ratio));
+}
+
+// (min, second min) of one matrix row over the nvalid first columns of a 128-column TMEM tile, as 16-bit keys
+// hamming << 7 | column, two columns per register.  acc = dot = 256 - 2 hamming, so key = (256 - dot) << 6 | column:
+// for the column pair (c, c + 1):  P = dot_c * -64 + dot_c1 * (-64 << 16) + ((16384 + c) | (16384 + c + 1) << 16).
+__device__ __forceinline__ void fold_tile(uint32_t taddr, int nvalid, uint32_t& k1, uint32_t& k2) {
+  uint32_t p1 = 0xFFFFFFFFu, p2 = 0xFFFFFFFFu;
+  const int mlo = -64, mhi = -(64 << 16);
+#pragma unroll 1
+  for (int c0 = 0; c0 < kTile; c0 += 32) {
+    if (c0 >= nvalid) break;  // warp-uniform
+    uint32_t v[32];
+    tmem_ld32(taddr + c0, v);
+    tmem_ld_wait();
+    if (c0 + 32 <= nvalid) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 2) {
+        const uint32_t cst = (uint32_t)(16384 + j) | ((uint32_t)(16384 + j + 1) << 16);
+        uint32_t key = (uint32_t)((int)v[j + 1] * mhi + (int)(cst + (uint32_t)c0 * 0x00010001u));
+        key = (uint32_t)((int)v[j] * mlo + (int)key);
+        const uint32_t tmax = __vmaxu2(p1, key);
+        p1 = __vminu2(p1, key);
+        p2 = __vminu2(p2, tmax);
+      }
+    } else {
+      const int nv = nvalid - c0;  // 1..31 valid columns in this chunk
+#pragma unroll
+      for (int j = 0; j < 32; j += 2) {
+        const uint32_t cst = (uint32_t)(16384 + j) | ((uint32_t)(16384 + j + 1) << 16);
+        uint32_t key = (uint32_t)((int)v[j + 1] * mhi + (int)(cst + (uint32_t)c0 * 0x00010001u));
+        key = (uint32_t)((int)v[j] * mlo + (int)key);
+        key |= (j >= nv ? 0x0000FFFFu : 0u) | (j + 1 >= nv ? 0xFFFF0000u : 0u);
+        const uint32_t tmax = __vmaxu2(p1, key);
+        p1 = __vminu2(p1, key);
+        p2 = __vminu2(p2, tmax);
+      }
+    }
+  }
+  // the two smallest of the even-column list (low halves) and the odd-column list (high halves)
+  const uint32_t a1 = p1 & 0xFFFFu, b1 = p1 >> 16, a2 = p2 & 0xFFFFu, b2 = p2 >> 16;
+  k1 = min(a1, b1);
+  k2 = min(max(a1, b1), min(a2, b2));
+}
+
+// 16-bit tile key -> 32-bit key of match.cu: distance << 20 | (tile base + column)
+__device__ __forceinline__ uint32_t widen_key(uint32_t k16, uint32_t base) {
+  return ((k16 >> 7) << kShift) + base + (k16 & 127u);
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+    match_mma_kernel(const __grid_constant__ CUtensorMap tmap1, const __grid_constant__ CUtensorMap tmap2, const MmaParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  MmaSmem& s = *reinterpret_cast<MmaSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint2* rs = reinterpret_cast<uint2*>(&s + 1);  // [max_n1] row statistics T(d1[i], desc2)
+  uint2* cs = rs + p.max_n1;                     // [max_n2] column statistics T(d2[j], desc1)
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    mbar_init(&s.a_full, 1);
+    mbar_init(&s.a_empty, 1);
+    for (int i = 0; i < kBStages; ++i) {
+      mbar_init(&s.b_full[i], 1);
+      mbar_init(&s.b_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s.t_full[i], 1);
+      mbar_init(&s.t_empty[i], kEpiWarps);
+    }
+    s.running = 0;
+    s.fail = 0;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kEpiWarps + 1) {  // the MMA warp owns the TMEM allocation: 512 columns = two stages of (D1 | D2)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s.tmem_base)), "n"(512)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s.tmem_base;
+
+  // Pipeline positions, each role advancing the ones it uses: desc1 groups, desc2 tiles, tile pairs.  After a failed
+  // wait (fail flag) every role still walks the same loops -- waits return at once, work is skipped -- so that the
+  // barriers below are reached by everybody.
+  uint32_t a_it = 0, b_it = 0, t_it = 0;
+  volatile int* fail = &s.fail;
+  for (int jb = blockIdx.x; jb < p.n_jobs; jb += gridDim.x) {
+    const MatchJob job = p.jobs[jb];
+    const int n1 = job.n1p ? *job.n1p : job.n1;
+    const int n2 = job.n2p ? *job.n2p : job.n2;
+    const bool valid = n1 > 0 && n2 > 0 && n1 <= p.max_n1 && n2 <= p.max_n2;  // uniform over the CTA
+    if (!valid) {
+      if (threadIdx.x == 0) *job.count = (n1 > p.max_n1 || n2 > p.max_n2) ? -1 : 0;
+      continue;
+    }
+    const int nA = (n1 + kTile - 1) / kTile, nB = (n2 + kTile - 1) / kTile;
+    const int row1 = (int)((job.d1 - p.base1) >> 3), row2 = (int)((job.d2 - p.base2) >> 3);
+
+    if (warp == kEpiWarps) {
+      // ================= TMA producer =================
+      if (lane == 0) {
+        for (int g0 = 0; g0 < nA; g0 += kGroup) {
+          const int ng = min(kGroup, nA - g0);
+          bool ok = true;
+          if (a_it > 0) ok = mbar_wait(&s.a_empty, (a_it - 1) & 1, fail);
+          if (ok) {
+            mbar_expect_tx(&s.a_full, ng * kTileBytes);
+            for (int t = 0; t < ng; ++t)
+              for (int hk = 0; hk < 2; ++hk)
+                tma_load_2d(&tmap1, s.a[t] + hk * kHalfBytes, &s.a_full, hk * 128, row1 + (g0 + t) * kTile);
+          }
+          ++a_it;
+          for (int b = 0; b < nB; ++b) {
+            const int st = b_it % kBStages;
+            if (b_it >= kBStages) ok = mbar_wait(&s.b_empty[st], ((b_it / kBStages) - 1) & 1, fail);
+            if (ok) {
+              mbar_expect_tx(&s.b_full[st], kTileBytes);
+              for (int hk = 0; hk < 2; ++hk)
+                tma_load_2d(&tmap2, s.b[st] + hk * kHalfBytes, &s.b_full[st], hk * 128, row2 + b * kTile);
+            }
+            ++b_it;
+          }
+        }
+      }
+      __syncwarp();
+    } else if (warp == kEpiWarps + 1) {
+      // ================= MMA issuer =================
+      if (lane == 0) {
+        for (int g0 = 0; g0 < nA; g0 += kGroup) {
+          const int ng = min(kGroup, nA - g0);
+          bool ok = mbar_wait(&s.a_full, a_it & 1, fail);
+          for (int b = 0; b < nB; ++b) {
+            const int st = b_it % kBStages;
+            ok = mbar_wait(&s.b_full[st], (b_it / kBStages) & 1, fail) && ok;
+            tc_fence_after();
+            for (int t = 0; t < ng; ++t) {
+              const int ts = t_it & 1;
+              if (t_it >= 2) ok = mbar_wait(&s.t_empty[ts], ((t_it >> 1) - 1) & 1, fail) && ok;
+              tc_fence_after();
+              if (ok) {
+                const uint32_t sa = smem_u32(s.a[t]), sb = smem_u32(s.b[st]);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {  // D1[i][j] = dot(desc1 row i, desc2 row j)
+                  const uint32_t off = (k >> 2) * kHalfBytes + (k & 3) * 32;
+                  umma_i8(tmem + ts * 256, umma_desc_sw128(sa + off), umma_desc_sw128(sb + off), k > 0);
+                }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {  // D2[j][i]: the same operands with the roles swapped
+                  const uint32_t off = (k >> 2) * kHalfBytes + (k & 3) * 32;
+                  umma_i8(tmem + ts * 256 + kTile, umma_desc_sw128(sb + off), umma_desc_sw128(sa + off), k > 0);
+                }
+                umma_commit(&s.t_full[ts]);
+              }
+              ++t_it;
+            }
+            if (ok) umma_commit(&s.b_empty[st]);  // arrives when the MMAs that read this desc2 tile are done
+            ++b_it;
+          }
+          if (ok) umma_commit(&s.a_empty);
+          ++a_it;
+        }
+      }
+      __syncwarp();
+    } else {
+      // ================= epilogue: warps 0-3 rows of D1, warps 4-7 rows of D2 =================
+      const int et = threadIdx.x;  // 0..255
+      for (int i = et; i < n1; i += kEpiWarps * 32) rs[i] = make_uint2(kSent, kSent);
+      for (int j = et; j < n2; j += kEpiWarps * 32) cs[j] = make_uint2(kSent, kSent);
+      epi_barrier();
+      const bool d2 = warp >= 4;
+      const int q = warp & 3;
+      for (int g0 = 0; g0 < nA; g0 += kGroup) {
+        const int ng = min(kGroup, nA - g0);
+        for (int b = 0; b < nB; ++b) {
+          for (int t = 0; t < ng; ++t) {
+            const int ts = t_it & 1;
+            const bool ok = mbar_wait(&s.t_full[ts], (t_it >> 1) & 1, fail);
+            tc_fence_after();
+            const int i0 = (g0 + t) * kTile, j0 = b * kTile;
+            // my row of the tile, the columns that exist, and where the row's statistics live
+            const int row = (d2 ? j0 : i0) + q * 32 + lane;
+            const int nrows = d2 ? n2 : n1;
+            const int nvalid = d2 ? min(kTile, n1 - i0) : min(kTile, n2 - j0);
+            const uint32_t cbase = d2 ? i0 : j0;
+            if (ok && q * 32 < (d2 ? n2 - j0 : n1 - i0)) {  // warp-uniform: the warp holds at least one real row
+              uint32_t k1, k2;
+              fold_tile(tmem + ((uint32_t)(q * 32) << 16) + ts * 256 + (d2 ? kTile : 0), nvalid, k1, k2);
+              if (row < nrows) {
+                uint2* sp = (d2 ? cs : rs) + row;
+                uint2 acc = *sp;
+                const uint32_t w1 = widen_key(k1, cbase), w2 = widen_key(k2, cbase);
+                const uint32_t hi = max(acc.x, w1);
+                acc.x = min(acc.x, w1);
+                acc.y = min(min(acc.y, w2), hi);
+                *sp = acc;
+              }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s.t_empty[ts]);
+            ++t_it;
+          }
+        }
+      }
+      epi_barrier();
+      const bool good = *fail == 0;  // read behind the barrier: the same for all epilogue warps
+      // ---- ratio test both ways, mutual check, compaction in ascending row order (as match_fused_kernel) ----
+      if (good) {
+        for (int base = 0; base < n1; base += kEpiWarps * 32) {
+          const int i = base + et;
+          bool hit = false;
+          int j = 0;
+          if (i < n1) {
+            const uint2 R = rs[i];
+            if (passes(R.x >> kShift, R.y >> kShift, p.threshold, p.ratio)) {
+              j = R.x & kIdxMask;
+              const uint2 C = cs[j];
+              hit = passes(C.x >> kShift, C.y >> kShift, p.threshold, p.ratio) && (int)(C.x & kIdxMask) == i;
+            }
+          }
+          const unsigned bal = __ballot_sync(0xFFFFFFFFu, hit);
+          if (lane == 0) s.warp_sums[warp] = __popc(bal);
+          epi_barrier();
+          int off = s.running, tot = 0;
+          for (int w = 0; w < kEpiWarps; ++w) {
+            if (w < warp) off += s.warp_sums[w];
+            tot += s.warp_sums[w];
+          }
+          const int pos = off + __popc(bal & ((1u << lane) - 1));
+          if (hit && pos < p.cap) {
+            job.pairs[2 * pos] = i;
+            job.pairs[2 * pos + 1] = j;
+          }
+          epi_barrier();
+          if (et == 0) s.running += tot;
+          epi_barrier();
+        }
+        if (et == 0) {
+          *job.count = s.running;
+          s.running = 0;
+        }
+      } else if (et == 0) {
+        *job.count = -2;  // pipeline failure (see mbar_wait)
+      }
+      epi_barrier();
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kEpiWarps + 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512) : "memory");
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+// 2-D map over an expanded descriptor array [rows][256 B], box = one K half of an operand tile (128 B x 128 rows)
+int make_desc_tmap(vslam_ctx* ctx, const uint8_t* expanded, long long rows, CUtensorMap* tm) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return vs_fail(ctx, VSLAM_E_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  const cuuint64_t dims[2] = {256, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {256};
+  const cuuint32_t box[2] = {128, (cuuint32_t)kTile};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t*>(expanded), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[128];
+    snprintf(buf, sizeof buf, "cuTensorMapEncodeTiled (descriptors) failed: %d", (int)r);
+    return vs_fail(ctx, VSLAM_E_CUDA, buf);
+  }
+  return VSLAM_OK;
+}
+
+}  // namespace
+
+size_t match_mma_smem_bytes(int max_n1, int max_n2) {
+  return sizeof(MmaSmem) + 1024 + (size_t)(max_n1 + max_n2) * sizeof(uint2);
+}
+
+bool match_mma_fits(int max_n1, int max_n2) {
+  return match_mma_smem_bytes(max_n1, max_n2) <= 227 * 1024 && max_n1 <= kMaxIndex && max_n2 <= kMaxIndex;
+}
+
+int launch_expand_desc(vslam_ctx* ctx, const uint32_t* desc, long long rows, int rows_per_set, const int32_t* n_valid,
+                       uint8_t* expanded) {
+  if (rows <= 0) return VSLAM_OK;
+  const long long threads = rows * 16;
+  const long long blocks = (threads + 255) / 256;
+  if (blocks > 0x7FFFFFFFLL) return vs_fail(ctx, VSLAM_E_LIMIT, "descriptor array too large for one expansion launch");
+  expand_desc_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(desc, rows, rows_per_set, n_valid, expanded);
+  ctx->launches++;
+  VS_CUDA(ctx, cudaGetLastError());
+  return VSLAM_OK;
+}
+
+int launch_match_jobs_mma(vslam_ctx* ctx, const MatchJob* jobs_dev, int n_jobs, int max_n1, int max_n2, int threshold,
+                          double ratio, int cap, const MatchExpanded& x1, const MatchExpanded& x2) {
+  if (n_jobs <= 0) return VSLAM_OK;
+  if (!match_mma_fits(max_n1, max_n2)) return vs_fail(ctx, VSLAM_E_LIMIT, "job too large for the tensor-core matcher");
+  if (x1.rows > 0x7FFFFFFFLL || x2.rows > 0x7FFFFFFFLL) return vs_fail(ctx, VSLAM_E_LIMIT, "descriptor array beyond 2^31 rows");
+  CUtensorMap tm1, tm2;
+  int rc = make_desc_tmap(ctx, x1.expanded, x1.rows, &tm1);
+  if (!rc) rc = make_desc_tmap(ctx, x2.expanded, x2.rows, &tm2);
+  if (rc) return rc;
+  MmaParams p;
+  p.jobs = jobs_dev;
+  p.n_jobs = n_jobs;
+  p.base1 = x1.packed;
+  p.base2 = x2.packed;
+  p.threshold = threshold;
+  p.ratio = ratio;
+  p.cap = cap;
+  p.max_n1 = max_n1;
+  p.max_n2 = max_n2;
+  const size_t smem = match_mma_smem_bytes(max_n1, max_n2);
+  VS_CUDA(ctx, cudaFuncSetAttribute(match_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int grid = n_jobs < ctx->num_sms ? n_jobs : ctx->num_sms;
+  match_mma_kernel<<<grid, kThreads, smem, ctx->stream>>>(tm1, tm2, p);
+  ctx->launches++;
+  VS_CUDA(ctx, cudaGetLastError());
+  return VSLAM_OK;
+}
+
+int match_mma_timeouts(int* flag) {
+  return cudaMemcpyFromSymbol(flag, g_mma_timeout, sizeof(int)) == cudaSuccess ? 0 : -1;
+}

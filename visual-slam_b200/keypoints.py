@@ -42,6 +42,7 @@ ABI_SYMBOLS = [
     "vslam_bow_vocab_create", "vslam_bow_vocab_load_text", "vslam_bow_vocab_destroy", "vslam_bow_vocab_info",
     "vslam_bow_transform_batch", "vslam_bow_score", "vslam_bow_db_create", "vslam_bow_db_destroy", "vslam_bow_db_add",
     "vslam_bow_db_size", "vslam_bow_db_query", "vslam_orb_detect_compute_batch", "vslam_compute_bow_vector_batch",
+    "vslam_debug_mma_timeouts",
 ]
 
 VSLAM_OPT_FP_CONTRACT = 1
@@ -50,6 +51,7 @@ VSLAM_OPT_BATCH_CHUNK = 3
 VSLAM_OPT_BATCH_DEPTH = 4
 VSLAM_OPT_MATCH_SPLIT_SMALL = 5
 VSLAM_OPT_RESPONSE_BAND = 6
+VSLAM_OPT_MATCH_MMA = 7
 
 
 class VslamError(RuntimeError):
@@ -147,6 +149,7 @@ def load_library():
     L.vslam_last_match_ms.argtypes = [vp]
     L.vslam_last_match_ms.restype = C.c_float
     L.vslam_popc_peak.argtypes = [vp, C.POINTER(d)]
+    L.vslam_debug_mma_timeouts.argtypes = [vp]
     L.vslam_event_record.argtypes = [vp, i]
     L.vslam_event_elapsed_ms.argtypes = [vp, i, i, C.POINTER(C.c_float)]
     L.vslam_set_harris.argtypes = [vp, i, d]
@@ -432,6 +435,10 @@ class Context:
 
     def last_match_ms(self):
         return float(self.lib.vslam_last_match_ms(self.h))
+
+    def mma_timeouts(self):
+        """1 if the tensor-core matcher ever hit a pipeline timeout in this process (a bug), else 0."""
+        return int(self.lib.vslam_debug_mma_timeouts(self.h))
 
     def popc_peak(self):
         v = C.c_double(0)
