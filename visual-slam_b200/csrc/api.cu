@@ -642,25 +642,26 @@ int vslam_stereo_plan_run(vslam_stereo_plan* plan, int count, int num_features, 
                          plan->xy.as<double>(), plan->nkp.as<int32_t>(), plan->cap);
     cudaEventRecord(plan->ev[2], ctx->stream);
   }
+  // enough jobs to fill the GPU with one CTA per SM: Hamming matrix on the tensor cores (the describe kernel then also
+  // writes every descriptor as 256 signed bytes, the matcher's operand format); else the POPC kernels, whose
+  // column-split path spreads a few jobs over all SMs
+  const bool mma = (ctx->match_mma == 2 || (ctx->match_mma && 2 * count >= ctx->num_sms)) && match_mma_fits(plan->cap, plan->cap);
+  if (!rc && mma && !plan->descx.p) {  // first tensor-core run of this plan (no early return: ctx->stream is swapped)
+    if (plan->descx.reserve((size_t)2 * plan->max_pairs * plan->cap * 256) != cudaSuccess ||
+        cudaMemsetAsync(plan->descx.p, 0, plan->descx.bytes, ctx->stream) != cudaSuccess)
+      rc = vs_fail(ctx, VSLAM_E_CUDA, "plan: cannot allocate the signed-byte descriptor slab");
+  }
   if (!rc)
     rc = launch_orient_describe(ctx, plan->im, nimg, plan->xy.as<double>(), plan->nkp.as<int32_t>(), plan->cap,
-                                rotate ? 1 : 0, plan->ang.as<double>(), plan->desc.as<uint32_t>());
+                                rotate ? 1 : 0, plan->ang.as<double>(), plan->desc.as<uint32_t>(),
+                                mma ? plan->descx.as<uint8_t>() : nullptr);
   cudaEventRecord(plan->ev[3], ctx->stream);
   if (!rc) {
-    // enough jobs to fill the GPU with one CTA per SM: Hamming matrix on the tensor cores; else the POPC kernels
-    // (whose column-split path spreads a few jobs over all SMs)
-    if ((ctx->match_mma == 2 || (ctx->match_mma && 2 * count >= ctx->num_sms)) && match_mma_fits(plan->cap, plan->cap)) {
+    if (mma) {
       const long long rows = (long long)nimg * plan->cap;
-      if (!plan->descx.p) {
-        VS_CUDA(ctx, plan->descx.reserve((size_t)2 * plan->max_pairs * plan->cap * 256));
-        VS_CUDA(ctx, cudaMemsetAsync(plan->descx.p, 0, plan->descx.bytes, ctx->stream));
-      }
-      rc = launch_expand_desc(ctx, plan->desc.as<uint32_t>(), rows, plan->cap, plan->nkp.as<int32_t>(),
-                              plan->descx.as<uint8_t>());
       const MatchExpanded x = {plan->desc.as<uint32_t>(), plan->descx.as<uint8_t>(), rows};
-      if (!rc)
-        rc = launch_match_jobs_mma(ctx, plan->jobs.as<MatchJob>(), count, plan->cap, plan->cap, match_threshold,
-                                   match_dist_2_best, plan->cap, x, x);
+      rc = launch_match_jobs_mma(ctx, plan->jobs.as<MatchJob>(), count, plan->cap, plan->cap, match_threshold,
+                                 match_dist_2_best, plan->cap, x, x);
     } else {
       rc = launch_match_jobs(ctx, plan->jobs.as<MatchJob>(), count, plan->cap, plan->cap, match_threshold,
                              match_dist_2_best, plan->cap, &plan->mrow, &plan->mcol);

@@ -114,7 +114,8 @@ int launch_select(vslam_ctx* ctx, const DevImages& im, int count, const DetectWo
 // describe.cu
 int launch_orient_describe(vslam_ctx* ctx, const DevImages& im, int count, const double* xy,
                            const int32_t* n_kp, int cap, int mode_angles /*0: zero, 1: compute, 2: given*/,
-                           double* angles, uint32_t* desc /*nullable*/);
+                           double* angles, uint32_t* desc /*nullable*/,
+                           uint8_t* descx = nullptr /*optional [count][cap][256]: descriptors as signed bytes*/);
 // match.cu
 struct MatchJob {
   const uint32_t* d1;

@@ -45,6 +45,7 @@ struct DescribeParams {
   int mode_angles;       // 0: zero, 1: compute, 2: given in `angles`
   double* angles;        // [count][cap]
   uint32_t* desc;        // [count][cap][8] or null
+  uint8_t* descx;        // optional [count][cap][256]: every bit b as the signed byte 2b - 1 (operands of match_mma.cu)
   int contract;
 };
 
@@ -255,7 +256,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) orient_describe_kernel(c
       patch_wait<0>();
     }
     const unsigned char* centre = patch + kReach * kPatchPitch + off;
-    uint32_t my_word = 0;
+    uint32_t my_word = 0, my_xword = 0;
     int fmin = 1;  // smallest fixed-point fraction seen: 0 <=> some coordinate needs the exact round()
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
@@ -267,6 +268,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) orient_describe_kernel(c
       const int va = centre[yai * kPatchPitch + xai], vb = centre[ybi * kPatchPitch + xbi];
       const uint32_t word = __ballot_sync(0xFFFFFFFFu, va < vb);
       if (lane == k) my_word = word;
+      if ((lane >> 2) == k) my_xword = word;
     }
     if (__any_sync(0xFFFFFFFFu, fmin == 0)) {
       // a coordinate within 2^-21 of a halfway point (practically never): redo the keypoint with round()
@@ -278,9 +280,18 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) orient_describe_kernel(c
         const int va = centre[yai * kPatchPitch + xai], vb = centre[ybi * kPatchPitch + xbi];
         const uint32_t word = __ballot_sync(0xFFFFFFFFu, va < vb);
         if (lane == k) my_word = word;
+        if ((lane >> 2) == k) my_xword = word;
       }
     }
     if (lane < 8) p.desc[(slot0 + i) * 8 + lane] = my_word;
+    if (p.descx) {
+      // lane l expands bits [8l, 8l + 8) = byte (l & 3) of word l >> 2 to eight signed bytes (1 -> 0x01, 0 -> 0xFF):
+      // one coalesced 256-byte row per keypoint
+      const uint32_t bits = (my_xword >> (8 * (lane & 3))) & 0xFFu;
+      const uint32_t b0 = ((bits & 0xFu) * 0x00204081u) & 0x01010101u, b1 = ((bits >> 4) * 0x00204081u) & 0x01010101u;
+      reinterpret_cast<uint2*>(p.descx + (slot0 + i) * 256)[lane] =
+          make_uint2(b0 | ((b0 ^ 0x01010101u) * 0xFFu), b1 | ((b1 ^ 0x01010101u) * 0xFFu));
+    }
     __syncwarp();  // every lane is done with this buffer before it is refilled
   }
 #undef STAGE
@@ -290,12 +301,12 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) orient_describe_kernel(c
 
 int launch_orient_describe(vslam_ctx* ctx, const DevImages& im, int count, const double* xy,
                            const int32_t* n_kp, int cap, int mode_angles, double* angles,
-                           uint32_t* desc) {
+                           uint32_t* desc, uint8_t* descx) {
   if (count <= 0 || cap <= 0) return VSLAM_OK;
   DescribeParams p;
   p.base = im.base; p.w = im.w; p.h = im.h; p.pitch = im.pitch; p.stride = im.stride;
   p.xy = xy; p.n_kp = n_kp; p.cap = cap; p.mode_angles = mode_angles;
-  p.angles = angles; p.desc = desc; p.contract = ctx->fp_contract;
+  p.angles = angles; p.desc = desc; p.descx = desc ? descx : nullptr; p.contract = ctx->fp_contract;
   const int per_cta = kWarpsPerCta * 32;
   if (count > 65535) return vs_fail(ctx, VSLAM_E_LIMIT, "more than 65535 images in one describe launch");
   dim3 grid((cap + per_cta - 1) / per_cta, count);

@@ -45,6 +45,17 @@ constexpr uint32_t kSent = 256u << kShift;
 constexpr int kMaxIndex = 1 << kShift;
 constexpr uint32_t kSpinLimit = 1u << 26;
 
+#ifdef VSLAM_MMA_PROFILE
+// cycle counters of CTA 0 (build with -DVSLAM_MMA_PROFILE; read with vslam_debug_mma_clocks):
+// 0 MMA total, 1 MMA wait a_full, 2 wait b_full, 3 wait t_empty, 4 issue; 8 epi total, 9 wait t_full, 10 fold, 11 finalize,
+// 12 tile pairs; 16.. the same epilogue counters for warp 4
+__device__ long long g_mma_clk[32];
+#define MMA_T0() const long long t0_ = clock64()
+#define MMA_ACC(slot) do { if (blockIdx.x == 0) g_mma_clk[slot] += clock64() - t0_; } while (0)
+#else
+#define MMA_T0() do { } while (0)
+#define MMA_ACC(slot) do { } while (0)
+#endif
 __device__ int g_mma_timeout;  // a bounded wait ran out (never in a correct run): read by vslam_debug_mma_timeouts
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -171,43 +182,57 @@ __device__ __forceinline__ bool passes(uint32_t m1, uint32_t m2, int threshold, 
   return !((double)(int)m2 < __dmul_rn((double)(int)m1, ratio));
 }
 
-// (min, second min) of one matrix row over the nvalid first columns of a 128-column TMEM tile, as 16-bit keys
-// hamming << 7 | column, two columns per register.  acc = dot = 256 - 2 hamming, so key = (256 - dot) << 6 | column:
-// for the column pair (c, c + 1):  P = dot_c * -64 + dot_c1 * (-64 << 16) + ((16384 + c) | (16384 + c + 1) << 16).
-__device__ __forceinline__ void fold_tile(uint32_t taddr, int nvalid, uint32_t& k1, uint32_t& k2) {
-  uint32_t p1 = 0xFFFFFFFFu, p2 = 0xFFFFFFFFu;
+// One 32-column chunk of a row into two independent (min, second min) chains of packed 16-bit keys (columns 0-15 of
+// the chunk -> chain a, 16-31 -> chain b: the serial min/max dependency is what bounds a warp here).
+// acc = dot = 256 - 2 hamming, key16 = (256 - dot) << 6 | column; for the column pair (c, c + 1):
+//   P = dot_c * -64 + dot_c1 * (-64 << 16) + ((16384 + c) | (16384 + c + 1) << 16)      (two IMADs, FMA pipe)
+template <bool kMasked>
+__device__ __forceinline__ void fold_chunk(const uint32_t (&v)[32], int c0, int nv, uint32_t& p1a, uint32_t& p2a,
+                                           uint32_t& p1b, uint32_t& p2b) {
   const int mlo = -64, mhi = -(64 << 16);
-#pragma unroll 1
-  for (int c0 = 0; c0 < kTile; c0 += 32) {
-    if (c0 >= nvalid) break;  // warp-uniform
-    uint32_t v[32];
-    tmem_ld32(taddr + c0, v);
-    tmem_ld_wait();
-    if (c0 + 32 <= nvalid) {
+  const uint32_t cb = (uint32_t)c0 * 0x00010001u;
 #pragma unroll
-      for (int j = 0; j < 32; j += 2) {
-        const uint32_t cst = (uint32_t)(16384 + j) | ((uint32_t)(16384 + j + 1) << 16);
-        uint32_t key = (uint32_t)((int)v[j + 1] * mhi + (int)(cst + (uint32_t)c0 * 0x00010001u));
-        key = (uint32_t)((int)v[j] * mlo + (int)key);
-        const uint32_t tmax = __vmaxu2(p1, key);
-        p1 = __vminu2(p1, key);
-        p2 = __vminu2(p2, tmax);
-      }
+  for (int j = 0; j < 32; j += 2) {
+    const uint32_t cst = (uint32_t)(16384 + j) | ((uint32_t)(16384 + j + 1) << 16);
+    uint32_t key = (uint32_t)((int)v[j + 1] * mhi + (int)(cst + cb));
+    key = (uint32_t)((int)v[j] * mlo + (int)key);
+    if (kMasked) key |= (j >= nv ? 0x0000FFFFu : 0u) | (j + 1 >= nv ? 0xFFFF0000u : 0u);  // nv = valid columns of the chunk
+    if (j < 16) {
+      const uint32_t tmax = __vmaxu2(p1a, key);
+      p1a = __vminu2(p1a, key);
+      p2a = __vminu2(p2a, tmax);
     } else {
-      const int nv = nvalid - c0;  // 1..31 valid columns in this chunk
-#pragma unroll
-      for (int j = 0; j < 32; j += 2) {
-        const uint32_t cst = (uint32_t)(16384 + j) | ((uint32_t)(16384 + j + 1) << 16);
-        uint32_t key = (uint32_t)((int)v[j + 1] * mhi + (int)(cst + (uint32_t)c0 * 0x00010001u));
-        key = (uint32_t)((int)v[j] * mlo + (int)key);
-        key |= (j >= nv ? 0x0000FFFFu : 0u) | (j + 1 >= nv ? 0xFFFF0000u : 0u);
-        const uint32_t tmax = __vmaxu2(p1, key);
-        p1 = __vminu2(p1, key);
-        p2 = __vminu2(p2, tmax);
-      }
+      const uint32_t tmax = __vmaxu2(p1b, key);
+      p1b = __vminu2(p1b, key);
+      p2b = __vminu2(p2b, tmax);
     }
   }
-  // the two smallest of the even-column list (low halves) and the odd-column list (high halves)
+}
+
+// (min, second min) of one matrix row over the nvalid first columns of a 128-column TMEM tile, as 16-bit keys
+// hamming << 7 | column.  The load of the next chunk is in flight while the current one is folded.
+__device__ __forceinline__ void fold_tile(uint32_t taddr, int nvalid, uint32_t& k1, uint32_t& k2) {
+  uint32_t p1a = 0xFFFFFFFFu, p2a = 0xFFFFFFFFu, p1b = 0xFFFFFFFFu, p2b = 0xFFFFFFFFu;
+  uint32_t va[32], vb[32];
+  const int nch = (nvalid + 31) >> 5;  // 1..4 chunks hold a real column (warp-uniform)
+  tmem_ld32(taddr, va);
+#pragma unroll
+  for (int c = 0; c < kTile / 32; c += 2) {
+    if (c < nch) {
+      tmem_ld_wait();
+      if (c + 1 < nch) tmem_ld32(taddr + (c + 1) * 32, vb);
+      if ((c + 1) * 32 <= nvalid) fold_chunk<false>(va, c * 32, 32, p1a, p2a, p1b, p2b);
+      else fold_chunk<true>(va, c * 32, nvalid - c * 32, p1a, p2a, p1b, p2b);
+    }
+    if (c + 1 < nch) {
+      tmem_ld_wait();
+      if (c + 2 < nch) tmem_ld32(taddr + (c + 2) * 32, va);
+      if ((c + 2) * 32 <= nvalid) fold_chunk<false>(vb, (c + 1) * 32, 32, p1a, p2a, p1b, p2b);
+      else fold_chunk<true>(vb, (c + 1) * 32, nvalid - (c + 1) * 32, p1a, p2a, p1b, p2b);
+    }
+  }
+  // merge the two chains, then the even-column list (low halves) with the odd-column list (high halves)
+  const uint32_t p1 = __vminu2(p1a, p1b), p2 = __vminu2(__vmaxu2(p1a, p1b), __vminu2(p2a, p2b));
   const uint32_t a1 = p1 & 0xFFFFu, b1 = p1 >> 16, a2 = p2 & 0xFFFFu, b2 = p2 >> 16;
   k1 = min(a1, b1);
   k2 = min(max(a1, b1), min(a2, b2));
@@ -300,15 +325,17 @@ __global__ void __launch_bounds__(kThreads, 1)
       if (lane == 0) {
         for (int g0 = 0; g0 < nA; g0 += kGroup) {
           const int ng = min(kGroup, nA - g0);
-          bool ok = mbar_wait(&s.a_full, a_it & 1, fail);
+          bool ok;
+          { MMA_T0(); ok = mbar_wait(&s.a_full, a_it & 1, fail); MMA_ACC(1); }
           for (int b = 0; b < nB; ++b) {
             const int st = b_it % kBStages;
-            ok = mbar_wait(&s.b_full[st], (b_it / kBStages) & 1, fail) && ok;
+            { MMA_T0(); ok = mbar_wait(&s.b_full[st], (b_it / kBStages) & 1, fail) && ok; MMA_ACC(2); }
             tc_fence_after();
             for (int t = 0; t < ng; ++t) {
               const int ts = t_it & 1;
-              if (t_it >= 2) ok = mbar_wait(&s.t_empty[ts], ((t_it >> 1) - 1) & 1, fail) && ok;
+              { MMA_T0(); if (t_it >= 2) ok = mbar_wait(&s.t_empty[ts], ((t_it >> 1) - 1) & 1, fail) && ok; MMA_ACC(3); }
               tc_fence_after();
+              MMA_T0();
               if (ok) {
                 const uint32_t sa = smem_u32(s.a[t]), sb = smem_u32(s.b[st]);
 #pragma unroll
@@ -323,6 +350,7 @@ __global__ void __launch_bounds__(kThreads, 1)
                 }
                 umma_commit(&s.t_full[ts]);
               }
+              MMA_ACC(4);
               ++t_it;
             }
             if (ok) umma_commit(&s.b_empty[st]);  // arrives when the MMAs that read this desc2 tile are done
@@ -346,8 +374,10 @@ __global__ void __launch_bounds__(kThreads, 1)
         for (int b = 0; b < nB; ++b) {
           for (int t = 0; t < ng; ++t) {
             const int ts = t_it & 1;
-            const bool ok = mbar_wait(&s.t_full[ts], (t_it >> 1) & 1, fail);
+            bool ok;
+            { MMA_T0(); ok = mbar_wait(&s.t_full[ts], (t_it >> 1) & 1, fail); if (lane == 0 && q == 0) MMA_ACC(d2 ? 17 : 9); }
             tc_fence_after();
+            MMA_T0();
             const int i0 = (g0 + t) * kTile, j0 = b * kTile;
             // my row of the tile, the columns that exist, and where the row's statistics live
             const int row = (d2 ? j0 : i0) + q * 32 + lane;
@@ -370,11 +400,13 @@ __global__ void __launch_bounds__(kThreads, 1)
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&s.t_empty[ts]);
+            if (lane == 0 && q == 0) MMA_ACC(d2 ? 18 : 10);
             ++t_it;
           }
         }
       }
       epi_barrier();
+      MMA_T0();
       const bool good = *fail == 0;  // read behind the barrier: the same for all epilogue warps
       // ---- ratio test both ways, mutual check, compaction in ascending row order (as match_fused_kernel) ----
       if (good) {
@@ -415,6 +447,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         *job.count = -2;  // pipeline failure (see mbar_wait)
       }
       epi_barrier();
+      if (et == 0) MMA_ACC(11);
     }
   }
 
@@ -508,6 +541,17 @@ int launch_match_jobs_mma(vslam_ctx* ctx, const MatchJob* jobs_dev, int n_jobs, 
   VS_CUDA(ctx, cudaGetLastError());
   return VSLAM_OK;
 }
+
+#ifdef VSLAM_MMA_PROFILE
+extern "C" int vslam_debug_mma_clocks(long long* out32, int reset) {
+  if (cudaMemcpyFromSymbol(out32, g_mma_clk, sizeof(long long) * 32) != cudaSuccess) return -1;
+  if (reset) {
+    long long z[32] = {};
+    if (cudaMemcpyToSymbol(g_mma_clk, z, sizeof z) != cudaSuccess) return -1;
+  }
+  return 0;
+}
+#endif
 
 int match_mma_timeouts(int* flag) {
   return cudaMemcpyFromSymbol(flag, g_mma_timeout, sizeof(int)) == cudaSuccess ? 0 : -1;

@@ -93,7 +93,8 @@ class Epipolar(C.Structure):
 
 
 def lib_path():
-    return os.path.join(_HERE, "csrc", "libvisnav_b200.so")
+    # VSLAM_LIB: another build of the same library (profiling variants of tools/probes); never a different implementation
+    return os.environ.get("VSLAM_LIB") or os.path.join(_HERE, "csrc", "libvisnav_b200.so")
 
 
 _lib = None
