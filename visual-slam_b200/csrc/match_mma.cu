@@ -15,9 +15,11 @@
 // time, persistent over the batch, warp-specialised:
 //   warp 8  (one lane)  TMA producer: 128-descriptor operand tiles ([2 K halves][128 rows][128 B], 128-byte swizzle,
 //                       K-major) -- kGroup tiles of desc1 stay resident while the tiles of desc2 stream through a ring
-//   warp 9  (one lane)  MMA issuer: per (desc1 tile, desc2 tile) TWO 128 x 128 products into one TMEM stage,
+//   warps 9, 10 (one lane each)  MMA issuers, one per TMEM stage: per (desc1 tile, desc2 tile) TWO 128 x 128 products,
 //                       D1 = A * B^T (rows = desc1) and D2 = B * A^T (rows = desc2): both directions of the reference's
-//                       test become ROW statistics, so no reduction ever crosses threads
+//                       test become ROW statistics, so no reduction ever crosses threads.  Two issuers because a
+//                       tcgen05.mma issue blocks on the pipe's short queue: a single thread's barrier waits then sit
+//                       between its MMAs (measured: pipe 45 % busy); with two, one waits while the other multiplies
 //   warps 0-3 / 4-7     epilogue of D1 / D2: thread = one TMEM lane = one matrix row; tcgen05.ld 32 columns at a time;
 //                       two distances per register as 16-bit keys (hamming << 7 | column) built by two IMADs on the FMA
 //                       pipe, (min, second min) kept with VIMNMX.U16x2 (3 ALU instructions per TWO distances); per tile
@@ -38,7 +40,8 @@ constexpr int kTileBytes = 2 * kHalfBytes; // 32 KB
 constexpr int kGroup = 2;                  // desc1 tiles resident per pass over desc2
 constexpr int kBStages = 3;                // ring of desc2 tiles
 constexpr int kEpiWarps = 8;
-constexpr int kThreads = (kEpiWarps + 2) * 32;
+constexpr int kMmaWarps = 2;               // one MMA-issuing warp per TMEM stage (see the kernel's header)
+constexpr int kThreads = (kEpiWarps + 1 + kMmaWarps) * 32;
 constexpr uint32_t kShift = 20;            // 32-bit key = distance << 20 | index (as in match.cu)
 constexpr uint32_t kIdxMask = (1u << kShift) - 1;
 constexpr uint32_t kSent = 256u << kShift;
@@ -50,11 +53,23 @@ constexpr uint32_t kSpinLimit = 1u << 26;
 // 0 MMA total, 1 MMA wait a_full, 2 wait b_full, 3 wait t_empty, 4 issue; 8 epi total, 9 wait t_full, 10 fold, 11 finalize,
 // 12 tile pairs; 16.. the same epilogue counters for warp 4
 __device__ long long g_mma_clk[32];
+// per tile pair of CTA 0 (first 256): clock64 at 0 MMA issue start, 1 issue end (commit), 2 + w: epilogue warp w done
+// (arrived on t_empty), 10: warp 0 saw t_full, 11: warp 4 saw t_full
+__device__ long long g_mma_trace[256][12];
+#define MMA_TRACE(pair, k) do { if ((pair) < 256) s.prof_trace[pair][k] = clock64(); } while (0)
+// the counters live in shared memory while the kernel runs (a global read-modify-write per event would put ~700
+// cycles on the MMA thread's critical path -- measured) and are dumped by CTA 0 at the end
+#if VSLAM_MMA_PROFILE >= 2  // trace only: the accumulating counters cost a shared-memory read-modify-write per event
+#define MMA_T0() do { } while (0)
+#define MMA_ACC(slot) do { } while (0)
+#else
 #define MMA_T0() const long long t0_ = clock64()
-#define MMA_ACC(slot) do { if (blockIdx.x == 0) g_mma_clk[slot] += clock64() - t0_; } while (0)
+#define MMA_ACC(slot) do { s.prof_clk[slot] += clock64() - t0_; } while (0)
+#endif
 #else
 #define MMA_T0() do { } while (0)
 #define MMA_ACC(slot) do { } while (0)
+#define MMA_TRACE(pair, k) do { } while (0)
 #endif
 __device__ int g_mma_timeout;  // a bounded wait ran out (never in a correct run): read by vslam_debug_mma_timeouts
 
@@ -162,6 +177,9 @@ struct MmaParams {
   double ratio;
   int cap;
   int max_n1, max_n2;
+  // -64 and -64 << 16: the multipliers that turn two accumulators into a packed key pair (fold_chunk).  Kernel
+  // parameters rather than literals: as literals ptxas re-materialises them with a MOV in front of every second IMAD
+  int key_mul_lo, key_mul_hi;
 };
 
 struct MmaSmem {
@@ -174,6 +192,10 @@ struct MmaSmem {
   int warp_sums[kEpiWarps];
   int running;
   int fail;
+#ifdef VSLAM_MMA_PROFILE
+  long long prof_clk[32];
+  long long prof_trace[256][12];
+#endif
 };
 
 __device__ __forceinline__ bool passes(uint32_t m1, uint32_t m2, int threshold, double ratio) {
@@ -182,54 +204,72 @@ __device__ __forceinline__ bool passes(uint32_t m1, uint32_t m2, int threshold, 
   return !((double)(int)m2 < __dmul_rn((double)(int)m1, ratio));
 }
 
+// Folds two packed keys into a (min, second min) pair of packed lists: 5 min/max per TWO registers (= four distances):
+//   lo = min(x, y), hi = max(x, y);  m1' = min(m1, lo);  m2' = min3(m2, max(m1, lo), hi)
+__device__ __forceinline__ void fold2(uint32_t x, uint32_t y, uint32_t& m1, uint32_t& m2) {
+  const uint32_t lo = __vminu2(x, y), hi = __vmaxu2(x, y);
+  const uint32_t t = __vmaxu2(m1, lo);
+  m1 = __vminu2(m1, lo);
+  m2 = __vimin3_u16x2(m2, t, hi);
+}
+
 // One 32-column chunk of a row into two independent (min, second min) chains of packed 16-bit keys (columns 0-15 of
 // the chunk -> chain a, 16-31 -> chain b: the serial min/max dependency is what bounds a warp here).
 // acc = dot = 256 - 2 hamming, key16 = (256 - dot) << 6 | column; for the column pair (c, c + 1):
 //   P = dot_c * -64 + dot_c1 * (-64 << 16) + ((16384 + c) | (16384 + c + 1) << 16)      (two IMADs, FMA pipe)
 template <bool kMasked>
-__device__ __forceinline__ void fold_chunk(const uint32_t (&v)[32], int c0, int nv, uint32_t& p1a, uint32_t& p2a,
-                                           uint32_t& p1b, uint32_t& p2b) {
-  const int mlo = -64, mhi = -(64 << 16);
+__device__ __forceinline__ void fold_chunk(const uint32_t (&v)[32], int c0, int nv, int mlo, int mhi, uint32_t& p1a,
+                                           uint32_t& p2a, uint32_t& p1b, uint32_t& p2b) {
   const uint32_t cb = (uint32_t)c0 * 0x00010001u;
+  uint32_t key[16];
 #pragma unroll
   for (int j = 0; j < 32; j += 2) {
     const uint32_t cst = (uint32_t)(16384 + j) | ((uint32_t)(16384 + j + 1) << 16);
-    uint32_t key = (uint32_t)((int)v[j + 1] * mhi + (int)(cst + cb));
-    key = (uint32_t)((int)v[j] * mlo + (int)key);
-    if (kMasked) key |= (j >= nv ? 0x0000FFFFu : 0u) | (j + 1 >= nv ? 0xFFFF0000u : 0u);  // nv = valid columns of the chunk
-    if (j < 16) {
-      const uint32_t tmax = __vmaxu2(p1a, key);
-      p1a = __vminu2(p1a, key);
-      p2a = __vminu2(p2a, tmax);
-    } else {
-      const uint32_t tmax = __vmaxu2(p1b, key);
-      p1b = __vminu2(p1b, key);
-      p2b = __vminu2(p2b, tmax);
-    }
+    uint32_t k = (uint32_t)((int)v[j + 1] * mhi + (int)(cst + cb));
+    k = (uint32_t)((int)v[j] * mlo + (int)k);
+    if (kMasked) k |= (j >= nv ? 0x0000FFFFu : 0u) | (j + 1 >= nv ? 0xFFFF0000u : 0u);  // nv = valid columns of the chunk
+    key[j >> 1] = k;
   }
+#pragma unroll
+  for (int i = 0; i < 8; i += 2) fold2(key[i], key[i + 1], p1a, p2a);
+#pragma unroll
+  for (int i = 8; i < 16; i += 2) fold2(key[i], key[i + 1], p1b, p2b);
 }
 
 // (min, second min) of one matrix row over the nvalid first columns of a 128-column TMEM tile, as 16-bit keys
-// hamming << 7 | column.  The load of the next chunk is in flight while the current one is folded.
-__device__ __forceinline__ void fold_tile(uint32_t taddr, int nvalid, uint32_t& k1, uint32_t& k2) {
+// hamming << 7 | column.  All of the row's loads are issued before the first one is consumed: a TMEM load behind a
+// running MMA takes several hundred cycles (measured: a warp that loaded chunk by chunk spent 2/3 of its time waiting).
+__device__ __forceinline__ void fold_tile(uint32_t taddr, int nvalid, int mlo, int mhi, uint32_t& k1, uint32_t& k2) {
   uint32_t p1a = 0xFFFFFFFFu, p2a = 0xFFFFFFFFu, p1b = 0xFFFFFFFFu, p2b = 0xFFFFFFFFu;
-  uint32_t va[32], vb[32];
+  uint32_t v0[32], v1[32], v2[32], v3[32];
   const int nch = (nvalid + 31) >> 5;  // 1..4 chunks hold a real column (warp-uniform)
-  tmem_ld32(taddr, va);
-#pragma unroll
-  for (int c = 0; c < kTile / 32; c += 2) {
-    if (c < nch) {
-      tmem_ld_wait();
-      if (c + 1 < nch) tmem_ld32(taddr + (c + 1) * 32, vb);
-      if ((c + 1) * 32 <= nvalid) fold_chunk<false>(va, c * 32, 32, p1a, p2a, p1b, p2b);
-      else fold_chunk<true>(va, c * 32, nvalid - c * 32, p1a, p2a, p1b, p2b);
-    }
-    if (c + 1 < nch) {
-      tmem_ld_wait();
-      if (c + 2 < nch) tmem_ld32(taddr + (c + 2) * 32, va);
-      if ((c + 2) * 32 <= nvalid) fold_chunk<false>(vb, (c + 1) * 32, 32, p1a, p2a, p1b, p2b);
-      else fold_chunk<true>(vb, (c + 1) * 32, nvalid - (c + 1) * 32, p1a, p2a, p1b, p2b);
-    }
+  tmem_ld32(taddr, v0);
+  if (nch > 1) tmem_ld32(taddr + 32, v1);
+  if (nch > 2) tmem_ld32(taddr + 64, v2);
+  if (nch > 3) tmem_ld32(taddr + 96, v3);
+  tmem_ld_wait();
+  if (nvalid == kTile) {
+    // the common case as ONE basic block: the scheduler can run the key IMADs (FMA pipe) of one chunk under the min/max
+    // (ALU pipe) of another -- both pipes issue every other cycle, and two warps share a scheduler
+    fold_chunk<false>(v0, 0, 32, mlo, mhi, p1a, p2a, p1b, p2b);
+    fold_chunk<false>(v1, 32, 32, mlo, mhi, p1a, p2a, p1b, p2b);
+    fold_chunk<false>(v2, 64, 32, mlo, mhi, p1a, p2a, p1b, p2b);
+    fold_chunk<false>(v3, 96, 32, mlo, mhi, p1a, p2a, p1b, p2b);
+  } else {
+  if (nvalid >= 32) fold_chunk<false>(v0, 0, 32, mlo, mhi, p1a, p2a, p1b, p2b);
+  else fold_chunk<true>(v0, 0, nvalid, mlo, mhi, p1a, p2a, p1b, p2b);
+  if (nch > 1) {
+    if (nvalid >= 64) fold_chunk<false>(v1, 32, 32, mlo, mhi, p1a, p2a, p1b, p2b);
+    else fold_chunk<true>(v1, 32, nvalid - 32, mlo, mhi, p1a, p2a, p1b, p2b);
+  }
+  if (nch > 2) {
+    if (nvalid >= 96) fold_chunk<false>(v2, 64, 32, mlo, mhi, p1a, p2a, p1b, p2b);
+    else fold_chunk<true>(v2, 64, nvalid - 64, mlo, mhi, p1a, p2a, p1b, p2b);
+  }
+  if (nch > 3) {
+    if (nvalid >= 128) fold_chunk<false>(v3, 96, 32, mlo, mhi, p1a, p2a, p1b, p2b);
+    else fold_chunk<true>(v3, 96, nvalid - 96, mlo, mhi, p1a, p2a, p1b, p2b);
+  }
   }
   // merge the two chains, then the even-column list (low halves) with the odd-column list (high halves)
   const uint32_t p1 = __vminu2(p1a, p1b), p2 = __vminu2(__vmaxu2(p1a, p1b), __vminu2(p2a, p2b));
@@ -253,10 +293,10 @@ __global__ void __launch_bounds__(kThreads, 1)
 
   if (threadIdx.x == 0) {
     mbar_init(&s.a_full, 1);
-    mbar_init(&s.a_empty, 1);
+    mbar_init(&s.a_empty, kMmaWarps);  // both MMA warps commit to the operand barriers, whether or not they had a tile
     for (int i = 0; i < kBStages; ++i) {
       mbar_init(&s.b_full[i], 1);
-      mbar_init(&s.b_empty[i], 1);
+      mbar_init(&s.b_empty[i], kMmaWarps);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&s.t_full[i], 1);
@@ -264,6 +304,9 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
     s.running = 0;
     s.fail = 0;
+#ifdef VSLAM_MMA_PROFILE
+    for (int i = 0; i < 32; ++i) s.prof_clk[i] = 0;
+#endif
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == kEpiWarps + 1) {  // the MMA warp owns the TMEM allocation: 512 columns = two stages of (D1 | D2)
@@ -279,7 +322,7 @@ __global__ void __launch_bounds__(kThreads, 1)
   // Pipeline positions, each role advancing the ones it uses: desc1 groups, desc2 tiles, tile pairs.  After a failed
   // wait (fail flag) every role still walks the same loops -- waits return at once, work is skipped -- so that the
   // barriers below are reached by everybody.
-  uint32_t a_it = 0, b_it = 0, t_it = 0;
+  uint32_t a_it = 0, b_it = 0, t_it = 0, t_it1 = 0;  // (t_it1: the epilogue's count for stage 1)
   volatile int* fail = &s.fail;
   for (int jb = blockIdx.x; jb < p.n_jobs; jb += gridDim.x) {
     const MatchJob job = p.jobs[jb];
@@ -320,8 +363,12 @@ __global__ void __launch_bounds__(kThreads, 1)
         }
       }
       __syncwarp();
-    } else if (warp == kEpiWarps + 1) {
-      // ================= MMA issuer =================
+    } else if (warp > kEpiWarps) {
+      // ================= MMA issuers: warp kEpiWarps + 1 + t multiplies the group's tile t into TMEM stage t =========
+      // A tcgen05.mma issue blocks while the tensor pipe's short queue is full, so one issuing thread serialises its own
+      // barrier waits (a try_wait costs it ~300 cycles, measured) with the MMAs: the pipe idled 55 % of the time.  With
+      // one issuer per stage, the waits of one run under the MMAs of the other.
+      const int t = warp - kEpiWarps - 1;
       if (lane == 0) {
         for (int g0 = 0; g0 < nA; g0 += kGroup) {
           const int ng = min(kGroup, nA - g0);
@@ -330,30 +377,33 @@ __global__ void __launch_bounds__(kThreads, 1)
           for (int b = 0; b < nB; ++b) {
             const int st = b_it % kBStages;
             { MMA_T0(); ok = mbar_wait(&s.b_full[st], (b_it / kBStages) & 1, fail) && ok; MMA_ACC(2); }
-            tc_fence_after();
-            for (int t = 0; t < ng; ++t) {
-              const int ts = t_it & 1;
-              { MMA_T0(); if (t_it >= 2) ok = mbar_wait(&s.t_empty[ts], ((t_it >> 1) - 1) & 1, fail) && ok; MMA_ACC(3); }
+            if (t < ng) {
+              MMA_TRACE(2 * t_it + t, 4);
+              { MMA_T0(); if (t_it >= 1) ok = mbar_wait(&s.t_empty[t], (t_it - 1) & 1, fail) && ok; MMA_ACC(3); }
+              MMA_TRACE(2 * t_it + t, 5);
               tc_fence_after();
               MMA_T0();
+              MMA_TRACE(2 * t_it + t, 0);
               if (ok) {
                 const uint32_t sa = smem_u32(s.a[t]), sb = smem_u32(s.b[st]);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {  // D1[i][j] = dot(desc1 row i, desc2 row j)
                   const uint32_t off = (k >> 2) * kHalfBytes + (k & 3) * 32;
-                  umma_i8(tmem + ts * 256, umma_desc_sw128(sa + off), umma_desc_sw128(sb + off), k > 0);
+                  umma_i8(tmem + t * 256, umma_desc_sw128(sa + off), umma_desc_sw128(sb + off), k > 0);
                 }
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {  // D2[j][i]: the same operands with the roles swapped
                   const uint32_t off = (k >> 2) * kHalfBytes + (k & 3) * 32;
-                  umma_i8(tmem + ts * 256 + kTile, umma_desc_sw128(sb + off), umma_desc_sw128(sa + off), k > 0);
+                  umma_i8(tmem + t * 256 + kTile, umma_desc_sw128(sb + off), umma_desc_sw128(sa + off), k > 0);
                 }
-                umma_commit(&s.t_full[ts]);
+                MMA_TRACE(2 * t_it + t, 6);
+                umma_commit(&s.t_full[t]);
               }
               MMA_ACC(4);
-              ++t_it;
+              MMA_TRACE(2 * t_it + t, 1);
+              ++t_it;  // uses of this warp's stage
             }
-            if (ok) umma_commit(&s.b_empty[st]);  // arrives when the MMAs that read this desc2 tile are done
+            if (ok) umma_commit(&s.b_empty[st]);  // arrives when this warp's MMAs that read the desc2 tile are done
             ++b_it;
           }
           if (ok) umma_commit(&s.a_empty);
@@ -373,11 +423,13 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int ng = min(kGroup, nA - g0);
         for (int b = 0; b < nB; ++b) {
           for (int t = 0; t < ng; ++t) {
-            const int ts = t_it & 1;
+            const int ts = t;  // stage = index of the desc1 tile in its group
+            const uint32_t use = t ? t_it1 : t_it;  // uses of the stage so far
             bool ok;
-            { MMA_T0(); ok = mbar_wait(&s.t_full[ts], (t_it >> 1) & 1, fail); if (lane == 0 && q == 0) MMA_ACC(d2 ? 17 : 9); }
+            { MMA_T0(); ok = mbar_wait(&s.t_full[ts], use & 1, fail); if (lane == 0 && q == 0) MMA_ACC(d2 ? 17 : 9); }
             tc_fence_after();
             MMA_T0();
+            if (lane == 0 && q == 0) MMA_TRACE(2 * use + t, d2 ? 11 : 10);
             const int i0 = (g0 + t) * kTile, j0 = b * kTile;
             // my row of the tile, the columns that exist, and where the row's statistics live
             const int row = (d2 ? j0 : i0) + q * 32 + lane;
@@ -386,7 +438,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             const uint32_t cbase = d2 ? i0 : j0;
             if (ok && q * 32 < (d2 ? n2 - j0 : n1 - i0)) {  // warp-uniform: the warp holds at least one real row
               uint32_t k1, k2;
-              fold_tile(tmem + ((uint32_t)(q * 32) << 16) + ts * 256 + (d2 ? kTile : 0), nvalid, k1, k2);
+              fold_tile(tmem + ((uint32_t)(q * 32) << 16) + ts * 256 + (d2 ? kTile : 0), nvalid, p.key_mul_lo, p.key_mul_hi, k1, k2);
               if (row < nrows) {
                 uint2* sp = (d2 ? cs : rs) + row;
                 uint2 acc = *sp;
@@ -401,7 +453,8 @@ __global__ void __launch_bounds__(kThreads, 1)
             __syncwarp();
             if (lane == 0) mbar_arrive(&s.t_empty[ts]);
             if (lane == 0 && q == 0) MMA_ACC(d2 ? 18 : 10);
-            ++t_it;
+            if (lane == 0 && q == 0) MMA_TRACE(2 * use + t, d2 ? 3 : 2);
+            if (t) ++t_it1; else ++t_it;
           }
         }
       }
@@ -453,6 +506,12 @@ __global__ void __launch_bounds__(kThreads, 1)
 
   tc_fence_before();
   __syncthreads();
+#ifdef VSLAM_MMA_PROFILE
+  if (blockIdx.x == 0) {
+    for (int i = threadIdx.x; i < 32; i += kThreads) g_mma_clk[i] += s.prof_clk[i];
+    for (int i = threadIdx.x; i < 256 * 12; i += kThreads) g_mma_trace[i / 12][i % 12] = s.prof_trace[i / 12][i % 12];
+  }
+#endif
   if (warp == kEpiWarps + 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512) : "memory");
   }
@@ -533,6 +592,8 @@ int launch_match_jobs_mma(vslam_ctx* ctx, const MatchJob* jobs_dev, int n_jobs, 
   p.cap = cap;
   p.max_n1 = max_n1;
   p.max_n2 = max_n2;
+  p.key_mul_lo = -64;
+  p.key_mul_hi = -(64 << 16);
   const size_t smem = match_mma_smem_bytes(max_n1, max_n2);
   VS_CUDA(ctx, cudaFuncSetAttribute(match_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int grid = n_jobs < ctx->num_sms ? n_jobs : ctx->num_sms;
@@ -543,6 +604,9 @@ int launch_match_jobs_mma(vslam_ctx* ctx, const MatchJob* jobs_dev, int n_jobs, 
 }
 
 #ifdef VSLAM_MMA_PROFILE
+extern "C" int vslam_debug_mma_trace(long long* out3072) {
+  return cudaMemcpyFromSymbol(out3072, g_mma_trace, sizeof(long long) * 3072) == cudaSuccess ? 0 : -1;
+}
 extern "C" int vslam_debug_mma_clocks(long long* out32, int reset) {
   if (cudaMemcpyFromSymbol(out32, g_mma_clk, sizeof(long long) * 32) != cudaSuccess) return -1;
   if (reset) {
