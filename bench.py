@@ -32,11 +32,29 @@ UNIT = "stereo pairs/s"
 # algorithmic bytes per image of the dominant kernel (response): the u8 image read once + the
 # 1500 x 8 B corner list it ultimately yields
 RESP_BYTES_PER_IMAGE = W_IMG * H_IMG + NUM_FEATURES * 8
-# DRAM traffic of the response kernel per image, from the ncu --set full capture of the same kernel
-# at the bench's own launch size (profiles/r1x_response_raw.txt: dram__bytes_read.sum 1.444258 GB +
-# dram__bytes_write.sum 136.05 MB for 4000 images): the image is read once (1.00x its size), the rest is the
-# candidate list.
-RESP_DRAM_BYTES_PER_IMAGE = (1.444258e9 + 136.047616e6) / 4000
+# algorithmic bytes per keypoint of the describe kernel: the 37 x 37 patch both functions can touch + xy, angle,
+# descriptor
+DESC_BYTES_PER_KP = 37 * 37 + 48
+# int8 tensor peak for the matcher's roofline: tcgen05.mma kind::i8 alone, whole chip, measured by
+# tools/probes/umma_hamming.cu on this pool's B200 (profiles/r2a_umma_hamming_probe.jsonl: 4236 TOPS; nominal 4500)
+INT8_TOPS_MEASURED = 4236.2e12
+
+
+def kernel_traffic(name):
+    """DRAM traffic per unit of a kernel from the ncu --set full capture under profiles/<name>_traffic.json
+    (tools/ncu_summary.py traffic).  The record carries the sha256 of the kernel's source file at capture time: a
+    capture of an older version of the kernel is reported, but marked stale."""
+    import hashlib
+    path = os.path.join(ROOT, "profiles", name + "_traffic.json")
+    try:
+        rec = json.load(open(path))
+        cur = hashlib.sha256(open(os.path.join(ROOT, rec["source"]), "rb").read()).hexdigest()
+        return rec["dram_bytes_per_unit"], {"traffic_source": "ncu --set full, profiles/%s_traffic.json (%s, per unit x units per launch)"
+                                            % (name, rec.get("report", "?")), "traffic_stale": cur != rec["source_sha256"]}
+    except Exception as e:   # no capture committed: say so instead of inventing a number
+        return None, {"traffic_source": "no capture (%s)" % type(e).__name__, "traffic_stale": True}
+
+
 CPU_GFTT_IMPL = "?"
 
 
@@ -49,6 +67,7 @@ def parse():
     ap.add_argument("--pairs", type=int, default=PAIRS_PER_GPU, help="pairs per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0: min(steps, 5)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the config 3 / 4 / 5 lines")
     return ap.parse_args()
 
 
@@ -207,6 +226,61 @@ def run_reference(args):
     emit(line)
 
 
+def extra_configs(ctx, rank, world, dist, popc_peak):
+    """BASELINE configs 3, 4 and 5 on the driver-run line (a few hundred ms of GPU time each, not part of `value`):
+      c3  loop-closure verification sample: 40 keyframes x 1500 descriptors, all 780 pairs through vslam_match_batch
+      c4  relocalisation query: 1500 x 200 000 through vslam_match
+      c5  1920x1080 / 4000 features, single scale, 148 resident stereo pairs per GPU (sharded by pair over the ranks)
+    Kernel times by CUDA events inside the library (vslam_last_match_ms / plan stage events); max over ranks."""
+    from visnav_b200 import workloads as wl
+    from visnav_b200.keypoints import DescStore, StereoPlan
+    out = {}
+    kf = wl.keyframe_descriptors(40, 1500, 25)
+    store = DescStore(ctx, kf)
+    jobs = wl.keyframe_pair_jobs(40)
+    best = 1e9
+    for _ in range(4):
+        _, counts = ctx.match_batch(store, jobs, THRESH, RATIO, want_matches=False)
+        best = min(best, ctx.last_match_ms())
+    store.close()
+    d3 = len(jobs) * 1500.0 * 1500.0
+    q, db = wl.reloc_query()
+    best4 = 1e9
+    for _ in range(4):
+        m4 = ctx.match(q, db, THRESH, RATIO)
+        best4 = min(best4, ctx.last_match_ms())
+    n5 = 148
+    base5 = wl.synth_stereo_batch(4, 1920, 1080, first=4 * rank)
+    imgs5 = np.ascontiguousarray(base5[np.arange(n5) % 4])
+    plan5 = StereoPlan(ctx, 1920, 1080, n5, 4000)
+    plan5.upload(imgs5)
+    for _ in range(3):
+        plan5.run(n5, 4000, True, THRESH, RATIO)
+        ms5 = [float(v) for v in plan5.last_ms()]
+    r5 = plan5.download(n5)
+    plan5.close()
+    t = [best, best4, ms5[0]]
+    if dist is not None:
+        import torch
+        tt = torch.tensor(t, dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t = [float(v) for v in tt]
+    out["c3_sample"] = {"workload": "configs[2] sample: 780 matchDescriptors jobs of 1500 x 1500 per GPU (40 keyframes, all pairs)",
+                        "ms": t[0], "jobs_per_s": world * len(jobs) / (t[0] * 1e-3),
+                        "distances_per_s": world * d3 / (t[0] * 1e-3),
+                        "int8_frac_of_measured_peak": 512 * d3 / (t[0] * 1e-3) / INT8_TOPS_MEASURED,
+                        "popc_equivalent_frac": 8 * d3 / (t[0] * 1e-3) / popc_peak, "mean_matches": float(counts.mean())}
+    out["c4"] = {"workload": "configs[3]: 1500 queries x 200000 map descriptors, one vslam_match call (replicas across GPUs)",
+                 "ms": t[1], "distances_per_s": 1500 * 200000.0 / (t[1] * 1e-3),
+                 "popc_equivalent_frac": 8 * 1500 * 200000.0 / (t[1] * 1e-3) / popc_peak, "matches": int(len(m4))}
+    out["c5_single_scale"] = {"workload": "configs[4], single scale: %d resident 1920x1080 stereo pairs per GPU, 4000 features, "
+                                          "sharded by pair over %d GPU(s)" % (n5, world),
+                              "ms": t[2], "pairs_per_s": world * n5 / (t[2] * 1e-3),
+                              "stage_ms": {"response": ms5[1], "select": ms5[2], "describe": ms5[3], "match": ms5[4]},
+                              "mean_keypoints": float(r5["n_kp"].mean()), "mean_matches": float(r5["n_matches"].mean())}
+    return out
+
+
 def run_ours(args):
     rank, world, local = dist_env()
     import visnav_b200
@@ -285,6 +359,10 @@ def run_ours(args):
         t = torch.tensor([t_ms, t_e2e], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         t_ms, t_e2e = float(t[0]), float(t[1])
+    # configs 3 / 4 / 5 run on every rank (their times are reduced over the ranks); the main plan's 9 GB are freed first
+    plan.close()
+    popc_peak = ctx.popc_peak()
+    extras = None if args.no_extras else extra_configs(ctx, rank, world, dist, popc_peak)
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -296,6 +374,8 @@ def run_ours(args):
     peak, peak_src = peaks()
     resp_ms = float(stage_ms[1])
     achieved = RESP_BYTES_PER_IMAGE * 2 * n_pairs / (resp_ms * 1e-3) / 1e9
+    resp_traffic, resp_tinfo = kernel_traffic("response")
+    desc_traffic, desc_tinfo = kernel_traffic("describe")
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": t_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -308,8 +388,7 @@ def run_ours(args):
         "stage_ms": {"response": stage_ms[1], "select": stage_ms[2], "describe": stage_ms[3], "match": stage_ms[4]},
         "roofline": {"kernel": "response_kernel (Sobel+cov+box+min-eig+local-max, TMA tiles)", "bound": "hbm",
                      "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": RESP_DRAM_BYTES_PER_IMAGE * 2 * n_pairs,
-                     "traffic_source": "ncu --set full, profiles/r1x_response_raw.txt (per image x images per launch)",
+                     "traffic": None if resp_traffic is None else resp_traffic * 2 * n_pairs, **resp_tinfo,
                      "ms_per_launch": resp_ms, "algorithmic_bytes_per_launch": RESP_BYTES_PER_IMAGE * 2 * n_pairs},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "timing": "CUDA events around the synchronous C-ABI calls (rank-0 host wall clock: %.1f ms/step)"
@@ -318,19 +397,38 @@ def run_ours(args):
         "gpu_launches": int(launches), "clocks": clocks,
         "results": {"mean_keypoints": float(res["n_kp"].mean()), "mean_matches": float(res["n_matches"].mean())},
     }
-    # The matcher against the integer-popcount roofline north_star names (8 popc.b32 per 256-bit distance;
-    # the kernel's carry-save adders turn them into 4 real POPCs, so the fraction may exceed 1).  Peak = the
-    # register-only POPC microbenchmark of the library, run now on this GPU.
     kp = res["n_kp"].astype(np.int64).reshape(-1, 2)
     n_dist = float((kp[:, 0] * kp[:, 1]).sum())
-    popc_peak = ctx.popc_peak()
+    n_kp_total = float(res["n_kp"].sum())
+    # describe kernel: 24-28 % of the step.  Classified HBM by SURVEY 8d (bytes per keypoint x keypoints / time); the
+    # patches are L2 hits (DRAM reads ~ the image once), so the honest statement is "compute-bound, far below the HBM
+    # roof", and the fraction says how far
+    desc_ms = float(stage_ms[3])
+    desc_achieved = DESC_BYTES_PER_KP * n_kp_total / (desc_ms * 1e-3) / 1e9
+    line["roofline_describe"] = {"kernel": "orient_describe_kernel (moments + atan2 + rBRIEF, cp.async patch cache)",
+                                 "bound": "hbm", "achieved": desc_achieved, "peak": peak, "peak_source": peak_src,
+                                 "unit": "GB/s", "frac": desc_achieved / peak,
+                                 "traffic": None if desc_traffic is None else desc_traffic * 2 * n_pairs, **desc_tinfo,
+                                 "ms_per_launch": desc_ms, "algorithmic_bytes_per_launch": DESC_BYTES_PER_KP * n_kp_total,
+                                 "note": "ALU-pipe-bound in practice (DESIGN.md 4.3); patch bytes come from L2"}
+    # matcher: the Hamming matrix is an int8 contraction on the tensor cores (match_mma.cu), 256 MAC = 512 int8 ops per
+    # distance; the kernel multiplies every tile pair twice (rows = desc1 and rows = desc2), so the executed ops are 2x the
+    # algorithmic ones.  Peak = the measured tcgen05 kind::i8 rate.  The POPC figure north_star names (8 popc.b32 per
+    # distance) stays beside it for continuity: the POPC pipe no longer carries this work.
     match_ms = float(stage_ms[4])
-    line["roofline_match"] = {"kernel": "match_fused_kernel (all-pairs Hamming + best/second + ratio + mutual check)",
-                              "bound": "popc", "unit": "popc.b32/s", "achieved": 8.0 * n_dist / (match_ms * 1e-3),
-                              "peak": popc_peak, "peak_source": "vslam_popc_peak microbenchmark, this run",
-                              "frac": 8.0 * n_dist / (match_ms * 1e-3) / popc_peak,
+    ops = 512.0 * n_dist / (match_ms * 1e-3)
+    line["roofline_match"] = {"kernel": "match_mma_kernel (tcgen05.mma kind::i8 Hamming matrix + best/second + ratio + mutual check)",
+                              "bound": "tensor", "unit": "int8 op/s", "achieved": ops, "peak": INT8_TOPS_MEASURED,
+                              "peak_source": "tcgen05.mma kind::i8 alone, profiles/r2a_umma_hamming_probe.jsonl (nominal 4.5e15)",
+                              "frac": ops / INT8_TOPS_MEASURED, "frac_executed": 2 * ops / INT8_TOPS_MEASURED,
                               "distances_per_s": n_dist / (match_ms * 1e-3), "ms_per_launch": match_ms,
-                              "distances_per_launch": n_dist}
+                              "distances_per_launch": n_dist,
+                              "popc_equivalent": {"unit": "popc.b32/s", "algorithmic_8_per_distance": 8.0 * n_dist / (match_ms * 1e-3),
+                                                  "popc_peak_measured": popc_peak,
+                                                  "frac": 8.0 * n_dist / (match_ms * 1e-3) / popc_peak,
+                                                  "real_popc_issued_per_distance": 0}}
+    if extras is not None:
+        line["configs"] = extras
     if not args.no_cpu_baseline and world == 1:
         cores = os.cpu_count() or 1
         sample = min(16 * cores, n_distinct)      # ~15-25 s of CPU work (73 ms per pair and core)

@@ -201,8 +201,11 @@ void vslam_desc_store_destroy(vslam_desc_store* s);
  * set index; earlier indices stay valid.  Amortised O(count): the device buffers grow geometrically. */
 int vslam_desc_store_append(vslam_desc_store* s, const uint32_t* desc, int count, int* set_index);
 int vslam_desc_store_size(const vslam_desc_store* s);
-/* jobs: n_jobs x 2 int32 (set index of descriptors_1, set index of descriptors_2).
- * Outputs: matches [n_jobs][cap][2], n_matches [n_jobs] (host; either may be NULL). */
+/* jobs: n_jobs x 2 int32 (set index of descriptors_1, set index of descriptors_2); an index outside the store is
+ * VSLAM_E_ARG.  Outputs: matches [n_jobs][cap][2], n_matches [n_jobs] (host; either may be NULL).  n_matches holds
+ * the FULL count of every job; when one exceeds cap its list holds the first cap pairs and the call returns
+ * VSLAM_E_CAPACITY (as vslam_match does) after all jobs have run -- pass cap >= the largest set to rule that out.
+ * With n_matches == NULL the counts cannot be checked: the caller vouches for cap. */
 int vslam_match_batch(vslam_ctx* ctx, const vslam_desc_store* s, const int32_t* jobs, int n_jobs,
                       int threshold, double dist_2_best, int32_t* matches, int32_t* n_matches,
                       int cap);

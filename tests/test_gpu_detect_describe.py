@@ -149,6 +149,15 @@ def test_detect_strongest_subset_paths(ctx, oracle_port):
         assert np.array_equal(ctx.detect(noise, nf), oracle_port.detect(noise, nf)), nf
 
 
+def test_detect_4k_image(ctx, oracle_port):
+    """3840 x 2160: 129 600 minDistance cells, more than the select kernel's shared-memory table holds -- the whole
+    selection runs on the global workspace.  goodFeaturesToTrack has no image-size limit."""
+    img = _image(3840, 2160, 4)
+    for nf in (1500, 20000):
+        got, want = ctx.detect(img, nf), oracle_port.detect(img, nf)
+        assert got.shape == want.shape and np.array_equal(got, want), nf
+
+
 def test_detect_special_images(ctx, oracle_port):
     flat = np.full((120, 160), 77, np.uint8)              # constant: no response anywhere
     assert len(ctx.detect(flat, 100)) == 0 == len(oracle_port.detect(flat, 100))

@@ -4,6 +4,9 @@ import os
 import numpy as np
 import pytest
 
+import visnav_b200  # noqa: F401  (puts the package directory on the path)
+from visnav_b200 import workloads as wl
+
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
@@ -97,3 +100,28 @@ def test_harris_option_vs_opencv(ctx, oracle_port):
         oracle_port.set_harris(False)
     g2 = _load("gftt_161x123")
     assert np.array_equal(ctx.response(g2["img"]).view(np.uint32), g2["lam_unopt"].view(np.uint32))
+
+
+def test_response_large_fixture(ctx):
+    """Benchmark-size response maps against the reference's vendored OpenCV (tests/golden/response_large.npz, scalar
+    dispatch): the full-height kernel (what batches that fill the GPU run) reproduces the map bit for bit -- compared by
+    sha256 -- and both kernel modes return OpenCV's ordered corners."""
+    import hashlib
+    from visnav_b200.keypoints import VSLAM_OPT_RESPONSE_BAND
+    g = np.load(os.path.join(GOLD, "response_large.npz"))
+    for key in g["names"]:
+        w, h, seed = int(key.split("x")[0]), int(key.split("x")[1].split("_")[0]), int(key.split("_")[1])
+        img = wl.synth_image(seed, w, h)
+        if hashlib.sha256(img.tobytes()).digest() != g[key + "_img_sha"].tobytes():
+            pytest.skip("the synthetic image generator no longer reproduces the fixture images")
+        nf = 1500 if w == 752 else 4000
+        border = lambda c: c[(c[:, 0] >= 19) & (c[:, 0] < w - 19) & (c[:, 1] >= 19) & (c[:, 1] < h - 19)]
+        want = border(g[key + "_corners_scalar"]).astype(np.float64)
+        assert np.array_equal(ctx.detect(img, nf), want), key          # banded launch (single image)
+        ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 65535)
+        try:
+            lam = ctx.response(img)
+            assert hashlib.sha256(lam.tobytes()).digest() == g[key + "_lam_sha"].tobytes(), key
+            assert np.array_equal(ctx.detect(img, nf), want), key
+        finally:
+            ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 0)

@@ -211,3 +211,38 @@ def test_desc_store_append(ctx, oracle_port):
             want = oracle_port.match(sets[a], sets[b], 70, 1.2)
             assert c == len(want) and np.array_equal(m[:c], want), (k, a, b)
     store.close()
+
+
+def test_config4_full_size_equals_oracle(ctx, oracle_port):
+    """BASELINE config 4 at full size (1500 x 200 000) against the CPU oracle directly: the (best, index, second best)
+    triple of every query and the match list -- bit-exact.  (The oracle needs ~1 s.)"""
+    q, db = wl.reloc_query()
+    assert np.array_equal(ctx.best2(q, db), oracle_port.best2(q, db))
+    for thr, ratio in [(70, 1.2), (90, 1.05)]:
+        assert np.array_equal(ctx.match(q, db, thr, ratio), oracle_port.match(q, db, thr, ratio)), (thr, ratio)
+
+
+def test_config3_sampled_jobs_equal_oracle(ctx, oracle_port):
+    """BASELINE config 3 shape (keyframes of 1500 descriptors, 25 flipped bits, all unordered pairs): 60 keyframes =
+    1770 jobs through vslam_match_batch (tensor-core path: the batch fills the GPU), 240 of them compared with the
+    oracle's match lists, the rest by count against the POPC kernels."""
+    from visnav_b200.keypoints import VSLAM_OPT_MATCH_MMA
+    kf = wl.keyframe_descriptors(60, 1500, 25)
+    store = DescStore(ctx, kf)
+    jobs = wl.keyframe_pair_jobs(60)
+    try:
+        matches, counts = ctx.match_batch(store, jobs, 70, 1.2)
+        ctx.set_option(VSLAM_OPT_MATCH_MMA, 0)
+        try:
+            _, counts_popc = ctx.match_batch(store, jobs, 70, 1.2, want_matches=False)
+        finally:
+            ctx.set_option(VSLAM_OPT_MATCH_MMA, 1)
+    finally:
+        store.close()
+    assert np.array_equal(counts, counts_popc) and counts.min() > 1000
+    rng = np.random.default_rng(12)
+    for k in rng.choice(len(jobs), 240, replace=False):
+        i, j = jobs[k]
+        want = oracle_port.match(kf[i], kf[j], 70, 1.2)
+        assert counts[k] == len(want) and np.array_equal(matches[k][:counts[k]], want), (i, j)
+    assert ctx.mma_timeouts() == 0

@@ -6,6 +6,9 @@ import os
 import numpy as np
 import pytest
 
+import visnav_b200  # noqa: F401  (puts the package directory on the path)
+from visnav_b200 import workloads as wl
+
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
@@ -169,3 +172,40 @@ def test_harris_option_matches_opencv(oracle_port):
     # off again: the min-eigenvalue fixture still holds
     g2 = np.load(os.path.join(GOLD, "gftt_161x123.npz"))
     assert np.array_equal(oracle_port.response(g2["img"]).view(np.uint32), g2["lam_unopt"].view(np.uint32))
+
+
+def test_response_large_matches_vendored_opencv(oracle_port, oracle_ref):
+    """tests/golden/response_large.npz: cv::cornerMinEigenVal of the reference's vendored OpenCV (scalar dispatch) at the
+    benchmark sizes, as sha256 of the float bits, and its goodFeaturesToTrack corners.  The restatement (running column
+    sum, box_filter.simd.hpp:206-262) reproduces the map bit for bit and the ordered corners; the direct three-row sum
+    does not on the images the fixture marks."""
+    import hashlib
+    g = np.load(os.path.join(GOLD, "response_large.npz"))
+    n_direct = 0
+    for key in g["names"]:
+        w, h, seed = int(key.split("x")[0]), int(key.split("x")[1].split("_")[0]), int(key.split("_")[1])
+        img = wl.synth_image(seed, w, h)
+        if hashlib.sha256(img.tobytes()).digest() != g[key + "_img_sha"].tobytes():
+            pytest.skip("the synthetic image generator no longer reproduces the fixture images")
+        lam = oracle_port.response(img)
+        assert hashlib.sha256(lam.tobytes()).digest() == g[key + "_lam_sha"].tobytes(), key
+        nf = 1500 if w == 752 else 4000
+        assert np.array_equal(oracle_port.gftt(img, nf), g[key + "_corners_scalar"]), key
+        # default (AVX2/FMA) dispatch: the same corner SET; the order may differ where responses tie in the last bit
+        assert set(map(tuple, g[key + "_corners_default"])) == set(map(tuple, g[key + "_corners_scalar"]))
+        if int(g[key + "_n_direct_sum_differs"]):
+            oracle_port.set_box_direct(1)
+            try:
+                d = oracle_port.response(img)
+            finally:
+                oracle_port.set_box_direct(0)
+            nd = int((d.view(np.uint32) != lam.view(np.uint32)).sum())
+            assert nd == int(g[key + "_n_direct_sum_differs"])
+            n_direct += nd
+        if oracle_ref is not None and oracle_ref.has_opencv and h <= 480:     # live, where the vendored build exists
+            oracle_ref.set_use_optimized(False)
+            try:
+                assert np.array_equal(oracle_ref.cv_response(img).view(np.uint32), lam.view(np.uint32))
+            finally:
+                oracle_ref.set_use_optimized(True)
+    assert n_direct > 0

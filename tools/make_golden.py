@@ -252,8 +252,54 @@ def orb_params():
     np.savez_compressed(os.path.join(OUT, "orb_params.npz"), **rec)
 
 
+def response_large():
+    """Response maps at the benchmark sizes (752x480, 1920x1080) from the reference's OWN vendored OpenCV
+    (oracle/_ref/libvisnav_ref.so links thirdparty/opencv core+imgproc): cv::cornerMinEigenVal under the scalar
+    dispatch (cv::setUseOptimized(false)) as sha256 of the float32 bits -- the maps themselves would be 1.4 / 8 MB
+    each -- plus the ordered goodFeaturesToTrack corners under both dispatches.  The images are the seeded synthetic
+    ones; their sha256 is stored so that a drifting generator is told apart from a drifting kernel.  The 1080p seeds
+    are ones where OpenCV's running column sum and a direct three-row sum differ (what the fixture exists to pin)."""
+    import hashlib
+    ref = oracle.load_ref()
+    assert ref is not None and ref.has_opencv, "oracle/_ref must be built against the vendored OpenCV"
+    port = oracle.load_oracle()
+    ref.set_num_threads(1)
+    rec = {}
+    names = []
+    for (w, h, seed, nf) in [(752, 480, 1234, 1500), (752, 480, 1, 1500), (1920, 1080, 300, 4000), (1920, 1080, 301, 4000),
+                             (1920, 1080, 302, 4000), (1920, 1080, 303, 4000)]:
+        img = wl.synth_image(seed, w, h)
+        key = "%dx%d_%d" % (w, h, seed)
+        names.append(key)
+        ref.set_use_optimized(False)
+        lam = ref.cv_response(img)
+        c_scalar = ref.cv_gftt(img, nf)
+        ref.set_use_optimized(True)
+        lam_def = ref.cv_response(img)
+        c_default = ref.cv_gftt(img, nf)
+        port.set_box_direct(1)
+        lam_direct = port.response(img)
+        port.set_box_direct(0)
+        rec[key + "_img_sha"] = np.frombuffer(hashlib.sha256(img.tobytes()).digest(), np.uint8)
+        rec[key + "_lam_sha"] = np.frombuffer(hashlib.sha256(lam.tobytes()).digest(), np.uint8)
+        rec[key + "_lam_max"] = np.float32(lam.max())
+        rec[key + "_corners_scalar"] = c_scalar
+        rec[key + "_corners_default"] = c_default
+        rec[key + "_n_direct_sum_differs"] = np.int32((lam.view(np.uint32) != lam_direct.view(np.uint32)).sum())
+        rec[key + "_n_default_dispatch_differs"] = np.int32((lam.view(np.uint32) != lam_def.view(np.uint32)).sum())
+        print(key, "direct-sum pixels differing:", int(rec[key + "_n_direct_sum_differs"]), " default-dispatch pixels differing:",
+              int(rec[key + "_n_default_dispatch_differs"]), " corners equal across dispatches:",
+              np.array_equal(c_scalar, c_default), " set-equal:",
+              set(map(tuple, c_scalar)) == set(map(tuple, c_default)))
+    rec["names"] = np.array(names)
+    rec["opencv"] = np.array(ref.gftt_impl)
+    np.savez_compressed(os.path.join(OUT, "response_large.npz"), **rec)
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "orb":
+    if len(sys.argv) > 1 and sys.argv[1] == "response_large":
+        response_large()
+    elif len(sys.argv) > 1 and sys.argv[1] == "orb":
         orb()
     elif len(sys.argv) > 1 and sys.argv[1] == "orb_params":
         orb_params()
@@ -269,6 +315,7 @@ if __name__ == "__main__":
         harris()
     else:
         main()
+        response_large()
         landmarks()
         geometry()
         euroc()

@@ -2,6 +2,9 @@
 """Summarise ncu outputs brought back in gpurun_out/ into small text files for profiles/.
   ncu_summary.py launches <launches.csv>            per-kernel launch count, total time, share
   ncu_summary.py raw <report.ncu-rep> [metric ...]  selected raw metrics of every captured launch
+  ncu_summary.py traffic <report.ncu-rep> <kernel-regex> <units-per-launch> <source-file> <out.json>
+        dram__bytes_read/write of the captured launch of that kernel, per unit, with the sha256 of the kernel's source
+        file: bench.py reads the JSON and marks the roofline's traffic stale when the source has changed since
 """
 import collections
 import csv
@@ -51,8 +54,34 @@ def raw(path, metrics):
                 print("%-70s %-14s %s" % (m, U[H.index(m)], r[H.index(m)]))
 
 
+def traffic(path, pattern, units, source, out_json):
+    import hashlib, json, os, re
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    H = rows[0]
+    best = None
+    for r in rows[2:]:
+        if re.search(pattern, r[H.index("Kernel Name")]):
+            best = r
+    if best is None:
+        sys.exit("no launch of %s in %s" % (pattern, path))
+    def val(m):
+        v, u = float(best[H.index(m)].replace(",", "")), rows[1][H.index(m)]
+        return v * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[u]
+    rd, wr = val("dram__bytes_read.sum"), val("dram__bytes_write.sum")
+    rec = {"kernel": best[H.index("Kernel Name")].split("(")[0], "report": os.path.basename(path), "units_per_launch": int(units),
+           "dram_bytes_read": rd, "dram_bytes_write": wr, "dram_bytes_per_unit": (rd + wr) / int(units),
+           "gpu_time_us": float(best[H.index("gpu__time_duration.sum")].replace(",", "")) *
+                          {"ns": 1e-3, "us": 1.0, "ms": 1e3}.get(rows[1][H.index("gpu__time_duration.sum")], 1.0),
+           "source": source, "source_sha256": hashlib.sha256(open(source, "rb").read()).hexdigest()}
+    json.dump(rec, open(out_json, "w"), indent=1)
+    print(json.dumps(rec))
+
+
 if __name__ == "__main__":
     if sys.argv[1] == "launches":
         launches(sys.argv[2])
+    elif sys.argv[1] == "traffic":
+        traffic(*sys.argv[2:7])
     else:
         raw(sys.argv[2], sys.argv[3:] or DEFAULT)

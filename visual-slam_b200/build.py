@@ -11,6 +11,10 @@ CSRC = os.path.join(_HERE, "csrc")
 LIB = os.path.join(CSRC, "libvisnav_b200.so")
 SOURCES = ["api.cu", "detect.cu", "describe.cu", "match.cu", "match_mma.cu", "landmarks.cu", "pyramid.cu", "geometry.cu", "bow.cu", "orb.cu"]
 HEADERS = ["common.cuh", "rbrief_pattern.inc", os.path.join("..", "..", "include", "visnav_b200.h")]
+# geometry.cu spells its arithmetic with plain * and +: without contraction it evaluates every expression exactly as the
+# oracle (gcc -ffp-contract=off) does, so inlier / visibility decisions do not depend on where nvcc would fuse.  The other
+# files pin their rounding with explicit __f*_rn / __d*_rn / __fma_rn intrinsics and are unaffected by the flag.
+PER_FILE_FLAGS = {"geometry.cu": ["-fmad=false"]}
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
 
@@ -41,7 +45,7 @@ def build_native(force=False, verbose=False):
         objs.append(o)
         if force or _stale(o, [s] + hdrs):
             extra = os.environ.get("VSLAM_NVCC_EXTRA", "").split()   # e.g. -DVSLAM_SEL_PROFILE for latency work
-            cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
+            cmd = [nvcc] + NVCC_FLAGS + PER_FILE_FLAGS.get(src, []) + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
             procs.append((src, subprocess.Popen(cmd, cwd=CSRC, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
     for src, p in procs:
         out, _ = p.communicate()

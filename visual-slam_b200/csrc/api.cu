@@ -122,6 +122,7 @@ void vslam_destroy(vslam_ctx* ctx) {
     if (ctx->copy_stream[i]) cudaStreamDestroy(ctx->copy_stream[i]);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  if (ctx->pinned_status) cudaFreeHost(ctx->pinned_status);
   delete ctx;
 }
 
@@ -802,6 +803,20 @@ static int stereo_batch_impl(vslam_ctx* ctx, const uint8_t* images, int count, c
     plans[i] = cp;
   }
   int bad_kp = 0;
+  // keypoint counts / detector statuses land in the caller's n_kp, or in the ctx's own pinned block when the caller
+  // passes none (an overflowed image must not come back as "no matches, OK")
+  int32_t* kp_status_host = n_kp;
+  if (!kp_status_host && !rc) {
+    const size_t need = 2 * (size_t)count * sizeof(int32_t);
+    if (need > ctx->pinned_status_bytes) {
+      if (ctx->pinned_status) cudaFreeHost(ctx->pinned_status);
+      ctx->pinned_status = nullptr;
+      ctx->pinned_status_bytes = 0;
+      if (cudaMallocHost(&ctx->pinned_status, need) != cudaSuccess) rc = vs_fail(ctx, VSLAM_E_CUDA, "stereo batch: pinned status block");
+      else ctx->pinned_status_bytes = need;
+    }
+    kp_status_host = static_cast<int32_t*>(ctx->pinned_status);
+  }
   for (int c0 = 0, k = 0; k < nchunks && !rc; c0 += sizes[k], ++k) {
     vslam_stereo_plan* p = plans[k % nplans];
     const int nc = sizes[k];
@@ -811,20 +826,30 @@ static int stereo_batch_impl(vslam_ctx* ctx, const uint8_t* images, int count, c
     if (rc) break;
     cudaStream_t s = p->stream;
     const size_t i0 = 2 * (size_t)c0, ni = 2 * (size_t)nc, cp = cap;
-    if (xy) VS_CUDA(ctx, cudaMemcpyAsync(xy + i0 * cp * 2, p->xy.p, ni * cp * 16, cudaMemcpyDeviceToHost, s));
-    if (angles) VS_CUDA(ctx, cudaMemcpyAsync(angles + i0 * cp, p->ang.p, ni * cp * 8, cudaMemcpyDeviceToHost, s));
-    if (desc) VS_CUDA(ctx, cudaMemcpyAsync(desc + i0 * cp * 8, p->desc.p, ni * cp * 32, cudaMemcpyDeviceToHost, s));
-    if (n_kp) VS_CUDA(ctx, cudaMemcpyAsync(n_kp + i0, p->nkp.p, ni * 4, cudaMemcpyDeviceToHost, s));
-    if (matches) VS_CUDA(ctx, cudaMemcpyAsync(matches + (size_t)c0 * cp * 2, p->matches.p, (size_t)nc * cp * 8, cudaMemcpyDeviceToHost, s));
-    if (n_matches) VS_CUDA(ctx, cudaMemcpyAsync(n_matches + c0, p->nmatch.p, (size_t)nc * 4, cudaMemcpyDeviceToHost, s));
-    if (ep && inliers) VS_CUDA(ctx, cudaMemcpyAsync(inliers + (size_t)c0 * cp * 2, p->inliers.p, (size_t)nc * cp * 8, cudaMemcpyDeviceToHost, s));
-    if (ep && n_inliers) VS_CUDA(ctx, cudaMemcpyAsync(n_inliers + c0, p->ninl.p, (size_t)nc * 4, cudaMemcpyDeviceToHost, s));
+    // no early return inside the pipeline: queued copies of earlier chunks still write into the caller's buffers, so
+    // every exit goes through the stream synchronisation below
+    cudaError_t e = cudaSuccess;
+    auto d2h = [&](void* dst, const void* src, size_t bytes) {
+      if (e == cudaSuccess) e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s);
+    };
+    if (xy) d2h(xy + i0 * cp * 2, p->xy.p, ni * cp * 16);
+    if (angles) d2h(angles + i0 * cp, p->ang.p, ni * cp * 8);
+    if (desc) d2h(desc + i0 * cp * 8, p->desc.p, ni * cp * 32);
+    d2h(kp_status_host + i0, p->nkp.p, ni * 4);  // the detector's overflow statuses are checked whatever the caller asks for
+    if (matches) d2h(matches + (size_t)c0 * cp * 2, p->matches.p, (size_t)nc * cp * 8);
+    if (n_matches) d2h(n_matches + c0, p->nmatch.p, (size_t)nc * 4);
+    if (ep && inliers) d2h(inliers + (size_t)c0 * cp * 2, p->inliers.p, (size_t)nc * cp * 8);
+    if (ep && n_inliers) d2h(n_inliers + c0, p->ninl.p, (size_t)nc * 4);
+    if (e != cudaSuccess) {
+      ctx->err = std::string("stereo batch: cudaMemcpyAsync: ") + cudaGetErrorString(e);
+      rc = VSLAM_E_CUDA;
+    }
   }
   for (int i = 0; i < nplans; ++i)
     if (plans[i]) cudaStreamSynchronize(plans[i]->stream);
-  if (!rc && n_kp)
+  if (!rc)
     for (size_t i = 0; i < 2 * (size_t)count; ++i)
-      if (n_kp[i] < 0) bad_kp = n_kp[i];
+      if (kp_status_host[i] < 0) bad_kp = kp_status_host[i];
   if (!rc && bad_kp) rc = kp_status(ctx, bad_kp);
   return rc;
 }
@@ -1073,6 +1098,8 @@ int vslam_match_batch(vslam_ctx* ctx, const vslam_desc_store* s, const int32_t* 
   if (!ctx) return VSLAM_E_ARG;
   if (!s || s->ctx != ctx || !jobs || n_jobs < 0 || cap <= 0) return vs_fail(ctx, VSLAM_E_ARG, "bad batch arguments");
   if (n_jobs == 0) return VSLAM_OK;
+  for (int k = 0; k < 2 * n_jobs; ++k)
+    if (jobs[k] < 0 || jobs[k] >= s->n_sets) return vs_fail(ctx, VSLAM_E_ARG, "match batch: set index out of range");
   if (!match_fits_fused(s->max_count, s->max_count))
     return vs_fail(ctx, VSLAM_E_LIMIT, "descriptor sets too large for batched matching; use vslam_match");
   VS_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -1097,6 +1124,7 @@ int vslam_match_batch(vslam_ctx* ctx, const vslam_desc_store* s, const int32_t* 
     ms->expanded = s->total;
   }
   float total_ms = 0.f;
+  int status = VSLAM_OK;
   for (int c0 = 0; c0 < n_jobs; c0 += chunk) {
     const int nc = n_jobs - c0 < chunk ? n_jobs - c0 : chunk;
     VS_CUDA(ctx, cudaMemcpyAsync(ji_dev, jobs + 2 * (size_t)c0, (size_t)nc * 8, cudaMemcpyHostToDevice, ctx->stream));
@@ -1120,8 +1148,17 @@ int vslam_match_batch(vslam_ctx* ctx, const vslam_desc_store* s, const int32_t* 
     float ms = 0.f;
     VS_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
     total_ms += ms;
+    // the same contract as vslam_match: a list longer than cap is an error, not a silently truncated result
+    if (n_matches)
+      for (int k = 0; k < nc; ++k) {
+        const int32_t c = n_matches[c0 + k];
+        if (c < 0) status = status ? status : VSLAM_E_LIMIT;
+        else if (c > cap) status = status ? status : VSLAM_E_CAPACITY;
+      }
   }
   ctx->last_match_ms = total_ms;
+  if (status == VSLAM_E_CAPACITY) return vs_fail(ctx, status, "match batch: a job has more matches than cap (n_matches holds the full counts, the lists their first cap pairs)");
+  if (status) return vs_fail(ctx, status, "match batch: a job failed on the device (n_matches < 0)");
   return VSLAM_OK;
 }
 

@@ -62,6 +62,8 @@ struct vslam_ctx {
   int orb_tab_key[4] = {0, 0, 0, 0};  // geometry the resize tables in orb[8] were built for (w, h, levels, scale bits)
   DevBuf pyr;  // vslam_pyramid_detect_describe_batch: levels 1.. of the chunk in flight
   void* pinned = nullptr;  // small pinned staging block for counts
+  void* pinned_status = nullptr;  // vslam_stereo_batch: per-image detector statuses when the caller passes no n_kp
+  size_t pinned_status_bytes = 0;
   // pipeline plans of vslam_stereo_batch, kept between calls (same geometry -> no reallocation)
   static constexpr int kMaxBatchDepth = 4;
   struct vslam_stereo_plan* batch_plans[kMaxBatchDepth] = {nullptr, nullptr, nullptr, nullptr};
