@@ -160,6 +160,9 @@ int launch_expand_desc(vslam_ctx* ctx, const uint32_t* desc, long long rows, int
                        uint8_t* expanded);
 int launch_match_jobs_mma(vslam_ctx* ctx, const MatchJob* jobs_dev, int n_jobs, int max_n1, int max_n2, int threshold,
                           double ratio, int cap, const MatchExpanded& x1, const MatchExpanded& x2);
+int match_mma_split_range(const vslam_ctx* ctx, int n2);
+int launch_match_split_mma(vslam_ctx* ctx, const uint8_t* x1, int n1, const uint8_t* x2, int n2, int range, uint2* rowpart,
+                           uint2* colstat);
 int match_mma_timeouts(int* flag);
 // pyramid.cu: dst level = 2x2 rounded mean of src (dst.w = src.w / 2, dst.h = src.h / 2)
 int launch_pyr_down(vslam_ctx* ctx, const DevImages& src, const DevImages& dst, int count);

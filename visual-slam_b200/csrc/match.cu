@@ -614,11 +614,22 @@ static int split_range(const vslam_ctx* ctx, int n2) {
   return range;
 }
 
+// Columns per CTA of a large job and which scan runs it: the tensor-core one (match_mma.cu) when there is enough work
+// to fill the GPU and the query set's statistics fit one CTA's shared memory, else the POPC one.
+static int large_range(const vslam_ctx* ctx, int n1, int n2, bool* mma) {
+  const int mrange = match_mma_split_range(ctx, n2);
+  *mma = ctx->match_mma && (long long)n1 * n2 >= (1LL << 23) && n2 >= 4 * ctx->num_sms && match_mma_fits(n1, mrange);
+  return *mma ? mrange : split_range(ctx, n2);
+}
+
 int launch_match_large(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_t* d2, int n2,
                        int threshold, double ratio, int32_t* pairs, int32_t* count, int cap,
                        int32_t* best2_out) {
   if (n1 > kMaxIndex) return vs_fail(ctx, VSLAM_E_LIMIT, "more than 2^20 query descriptors");
-  const int range = split_range(ctx, n2);
+  // enough work to fill the GPU and a query set whose statistics fit one CTA's shared memory: the Hamming matrix goes
+  // to the tensor cores (match_mma.cu, column ranges over the SMs); the merge / finalize kernels below are shared
+  bool mma;
+  const int range = large_range(ctx, n1, n2, &mma);
   const int nsplit = (n2 + range - 1) / range;
   VS_CUDA(ctx, ctx->rowpart.reserve((size_t)nsplit * n1 * sizeof(uint2) + (size_t)n1 * sizeof(int3)));
   VS_CUDA(ctx, ctx->colstat.reserve((size_t)n2 * sizeof(uint2)));
@@ -628,10 +639,19 @@ int launch_match_large(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_
   p.d1 = d1; p.d2 = d2; p.n1 = n1; p.n2 = n2; p.range = range;
   p.rowpart = rowpart;
   p.colstat = ctx->colstat.as<uint2>();
-  const size_t smem = (size_t)kScanSmemBytes + (size_t)range * sizeof(uint2);
-  auto kern = ctx->match_csa ? match_split_kernel<true> : match_split_kernel<false>;
-  VS_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<nsplit, kThreads, smem, ctx->stream>>>(p);
+  if (mma) {
+    VS_CUDA(ctx, ctx->d1x.reserve((size_t)n1 * 256));
+    VS_CUDA(ctx, ctx->d2x.reserve((size_t)n2 * 256));
+    int rc = launch_expand_desc(ctx, d1, n1, 1, nullptr, ctx->d1x.as<uint8_t>());
+    if (!rc) rc = launch_expand_desc(ctx, d2, n2, 1, nullptr, ctx->d2x.as<uint8_t>());
+    if (!rc) rc = launch_match_split_mma(ctx, ctx->d1x.as<uint8_t>(), n1, ctx->d2x.as<uint8_t>(), n2, range, rowpart, p.colstat);
+    if (rc) return rc;
+  } else {
+    const size_t smem = (size_t)kScanSmemBytes + (size_t)range * sizeof(uint2);
+    auto kern = ctx->match_csa ? match_split_kernel<true> : match_split_kernel<false>;
+    VS_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<nsplit, kThreads, smem, ctx->stream>>>(p);
+  }
   merge_rows_kernel<<<(n1 + 255) / 256, 256, 0, ctx->stream>>>(rowpart, n1, nsplit, range, rowstat);
   ctx->launches += 2;
   if (best2_out) {
@@ -707,7 +727,8 @@ int launch_match_shard(vslam_ctx* ctx, const uint32_t* d1, int n1, const uint32_
   // row statistics land in ctx->rowpart (after the partials), column statistics in ctx->colstat
   int rc = launch_match_large(ctx, d1, n1, d2, n2, threshold, ratio, nullptr, nullptr, 0, part4 /*scratch: 12 B/row*/);
   if (rc) return rc;
-  const int range = split_range(ctx, n2);
+  bool mma;
+  const int range = large_range(ctx, n1, n2, &mma);
   const int nsplit = (n2 + range - 1) / range;
   const int3* rowstat = reinterpret_cast<const int3*>(ctx->rowpart.as<uint2>() + (size_t)nsplit * n1);
   shard_part_kernel<<<(n1 + 255) / 256, 256, 0, ctx->stream>>>(rowstat, ctx->colstat.as<uint2>(), n1, index_offset,

@@ -180,6 +180,13 @@ struct MmaParams {
   // -64 and -64 << 16: the multipliers that turn two accumulators into a packed key pair (fold_chunk).  Kernel
   // parameters rather than literals: as literals ptxas re-materialises them with a MOV in front of every second IMAD
   int key_mul_lo, key_mul_hi;
+  // Column-split mode for ONE large job (split_range > 0; BASELINE config 4: a query set against a large map): CTA s
+  // takes all split_n1 rows of the first array against columns [s * split_range, + split_range) of the second; its
+  // row statistics are partial (rowpart[s][i], column indices relative to the range), its column statistics complete
+  // (colstat[column]); match.cu's merge_rows / finalize kernels finish the job.
+  int split_range, split_n1, split_n2;
+  uint2* rowpart;
+  uint2* colstat;
 };
 
 struct MmaSmem {
@@ -325,16 +332,27 @@ __global__ void __launch_bounds__(kThreads, 1)
   uint32_t a_it = 0, b_it = 0, t_it = 0, t_it1 = 0;  // (t_it1: the epilogue's count for stage 1)
   volatile int* fail = &s.fail;
   for (int jb = blockIdx.x; jb < p.n_jobs; jb += gridDim.x) {
-    const MatchJob job = p.jobs[jb];
-    const int n1 = job.n1p ? *job.n1p : job.n1;
-    const int n2 = job.n2p ? *job.n2p : job.n2;
+    const bool split = p.split_range > 0;
+    MatchJob job{};
+    int n1, n2, row1, row2;
+    if (split) {  // job jb = column range jb of the one large job
+      n1 = p.split_n1;
+      n2 = min(p.split_range, p.split_n2 - jb * p.split_range);
+      row1 = 0;
+      row2 = jb * p.split_range;
+    } else {
+      job = p.jobs[jb];
+      n1 = job.n1p ? *job.n1p : job.n1;
+      n2 = job.n2p ? *job.n2p : job.n2;
+      row1 = (int)((job.d1 - p.base1) >> 3);
+      row2 = (int)((job.d2 - p.base2) >> 3);
+    }
     const bool valid = n1 > 0 && n2 > 0 && n1 <= p.max_n1 && n2 <= p.max_n2;  // uniform over the CTA
     if (!valid) {
-      if (threadIdx.x == 0) *job.count = (n1 > p.max_n1 || n2 > p.max_n2) ? -1 : 0;
+      if (threadIdx.x == 0 && !split) *job.count = (n1 > p.max_n1 || n2 > p.max_n2) ? -1 : 0;
       continue;
     }
     const int nA = (n1 + kTile - 1) / kTile, nB = (n2 + kTile - 1) / kTile;
-    const int row1 = (int)((job.d1 - p.base1) >> 3), row2 = (int)((job.d2 - p.base2) >> 3);
 
     if (warp == kEpiWarps) {
       // ================= TMA producer =================
@@ -461,6 +479,14 @@ __global__ void __launch_bounds__(kThreads, 1)
       epi_barrier();
       MMA_T0();
       const bool good = *fail == 0;  // read behind the barrier: the same for all epilogue warps
+      if (split) {
+        // partial row statistics and complete column statistics of this column range; a pipeline failure leaves the
+        // "never matched" sentinel with an impossible index so that the host-visible result is empty, and the global flag
+        uint2* rp = p.rowpart + (size_t)jb * p.split_n1;
+        uint2* cp = p.colstat + (size_t)jb * p.split_range;
+        for (int i = et; i < n1; i += kEpiWarps * 32) rp[i] = good ? rs[i] : make_uint2(kSent, kSent);
+        for (int j = et; j < n2; j += kEpiWarps * 32) cp[j] = good ? cs[j] : make_uint2(kSent, kSent);
+      } else
       // ---- ratio test both ways, mutual check, compaction in ascending row order (as match_fused_kernel) ----
       if (good) {
         for (int base = 0; base < n1; base += kEpiWarps * 32) {
@@ -594,6 +620,8 @@ int launch_match_jobs_mma(vslam_ctx* ctx, const MatchJob* jobs_dev, int n_jobs, 
   p.max_n2 = max_n2;
   p.key_mul_lo = -64;
   p.key_mul_hi = -(64 << 16);
+  p.split_range = 0; p.split_n1 = p.split_n2 = 0;
+  p.rowpart = p.colstat = nullptr;
   const size_t smem = match_mma_smem_bytes(max_n1, max_n2);
   VS_CUDA(ctx, cudaFuncSetAttribute(match_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int grid = n_jobs < ctx->num_sms ? n_jobs : ctx->num_sms;
@@ -616,6 +644,40 @@ extern "C" int vslam_debug_mma_clocks(long long* out32, int reset) {
   return 0;
 }
 #endif
+
+// One large job with its columns split over the SMs: fills rowpart [nsplit][n1] and colstat [n2] in the layout of
+// match.cu's column-split path (merge_rows_kernel / finalize_large_kernel take it from there).
+int match_mma_split_range(const vslam_ctx* ctx, int n2) {
+  int range = (n2 + ctx->num_sms - 1) / ctx->num_sms;
+  range = ((range + kTile - 1) / kTile) * kTile;
+  return range < kTile ? kTile : range;
+}
+
+int launch_match_split_mma(vslam_ctx* ctx, const uint8_t* x1, int n1, const uint8_t* x2, int n2, int range, uint2* rowpart,
+                           uint2* colstat) {
+  const int nsplit = (n2 + range - 1) / range;
+  if (!match_mma_fits(n1, range)) return vs_fail(ctx, VSLAM_E_LIMIT, "job too large for the tensor-core matcher");
+  CUtensorMap tm1, tm2;
+  int rc = make_desc_tmap(ctx, x1, n1, &tm1);
+  if (!rc) rc = make_desc_tmap(ctx, x2, n2, &tm2);
+  if (rc) return rc;
+  MmaParams p{};
+  p.n_jobs = nsplit;
+  p.max_n1 = n1;
+  p.max_n2 = range;
+  p.key_mul_lo = -64;
+  p.key_mul_hi = -(64 << 16);
+  p.split_range = range; p.split_n1 = n1; p.split_n2 = n2;
+  p.rowpart = rowpart;
+  p.colstat = colstat;
+  const size_t smem = match_mma_smem_bytes(n1, range);
+  VS_CUDA(ctx, cudaFuncSetAttribute(match_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int grid = nsplit < ctx->num_sms ? nsplit : ctx->num_sms;
+  match_mma_kernel<<<grid, kThreads, smem, ctx->stream>>>(tm1, tm2, p);
+  ctx->launches++;
+  VS_CUDA(ctx, cudaGetLastError());
+  return VSLAM_OK;
+}
 
 int match_mma_timeouts(int* flag) {
   return cudaMemcpyFromSymbol(flag, g_mma_timeout, sizeof(int)) == cudaSuccess ? 0 : -1;
