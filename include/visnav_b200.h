@@ -69,6 +69,9 @@ typedef struct vslam_desc_store vslam_desc_store;
                                  kind::i8 on descriptors expanded to signed bytes: dot = 256 - 2 * hamming, exact);
                                  0: the POPC kernels; 2: the tensor cores for every batch, however small (tests).
                                  Results identical. */
+#define VSLAM_OPT_GRAPH 8 /* 1 (default): vslam_stereo_batch calls of a few pairs (one chunk whose results fit 2 MB: the
+                             one-pair-at-a-time use of slam.cpp:1125-1143) replay their kernel sequence as one CUDA graph
+                             from the third call with the same arguments on; 0: plain launches.  Results identical. */
 
 /* ---- context ------------------------------------------------------------------------ */
 int vslam_create(int device, vslam_ctx** out);

@@ -278,3 +278,36 @@ def test_stereo_batch_small_counts_split_matcher(ctx, n):
     for k in range(n):
         m = a["n_matches"][k]
         assert np.array_equal(a["matches"][k, :m], b["matches"][k, :m])
+
+
+def test_stereo_batch_single_pair_graph_replay(ctx, oracle_port):
+    """Config 1 the way slam.cpp:1125-1143 issues it: one pair per call, again and again.  From the third call with the
+    same arguments the pipeline plan replays its launches as one CUDA graph and the results travel in one copy; every
+    call returns the oracle's result, also when the arguments or the image change in between, and with VSLAM_OPT_GRAPH off."""
+    from visnav_b200.keypoints import VSLAM_OPT_GRAPH
+    pairs = wl.synth_stereo_batch(3, workers=1)
+    want = {}
+    for k in range(3):
+        dl = oracle_port.detect_describe(pairs[k, 0], 1500)
+        dr = oracle_port.detect_describe(pairs[k, 1], 1500)
+        want[k] = (dl, dr, oracle_port.match(dl[2], dr[2], 70, 1.2), oracle_port.match(dl[2], dr[2], 50, 1.5))
+
+    def check(out, k, m_idx):
+        for side, d in enumerate(want[k][:2]):
+            n = out["n_kp"][side]
+            assert n == len(d[0]) and np.array_equal(out["xy"][side, :n], d[0]) and np.array_equal(out["desc"][side, :n], d[2])
+            assert np.abs(out["angles"][side, :n] - d[1]).max() <= ANGLE_TOL
+        m = out["n_matches"][0]
+        assert m == len(want[k][m_idx]) and np.array_equal(out["matches"][0, :m], want[k][m_idx])
+
+    for graph in (1, 0, 1):
+        ctx.set_option(VSLAM_OPT_GRAPH, graph)
+        try:
+            for rep in range(5):                      # same arguments: plain, captured, replayed, replayed, replayed
+                k = rep % 3                           # ... on changing images
+                check(ctx.stereo_batch(pairs[k:k + 1], 1500, True, 70, 1.2), k, 2)
+            for rep in range(4):                      # other arguments: the graph is rebuilt
+                check(ctx.stereo_batch(pairs[1:2], 1500, True, 50, 1.5), 1, 3)
+            check(ctx.stereo_batch(pairs[2:3], 1500, True, 70, 1.2), 2, 2)
+        finally:
+            ctx.set_option(VSLAM_OPT_GRAPH, 1)

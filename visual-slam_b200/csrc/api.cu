@@ -123,6 +123,7 @@ void vslam_destroy(vslam_ctx* ctx) {
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   if (ctx->pinned_status) cudaFreeHost(ctx->pinned_status);
+  if (ctx->pinned_out) cudaFreeHost(ctx->pinned_out);
   delete ctx;
 }
 
@@ -134,6 +135,7 @@ int vslam_set_option(vslam_ctx* ctx, int option, int value) {
   else if (option == VSLAM_OPT_MATCH_CSA) ctx->match_csa = value != 0;
   else if (option == VSLAM_OPT_MATCH_SPLIT_SMALL) ctx->match_split_small = value != 0;
   else if (option == VSLAM_OPT_MATCH_MMA && value >= 0 && value <= 2) ctx->match_mma = value;
+  else if (option == VSLAM_OPT_GRAPH) ctx->use_graph = value != 0;
   else if (option == VSLAM_OPT_RESPONSE_BAND && (value == 0 || (value >= 8 && value <= 65535))) ctx->resp_band = value;
   else if (option == VSLAM_OPT_BATCH_CHUNK && value >= 1 && value <= 4096) ctx->batch_chunk = value;
   else if (option == VSLAM_OPT_BATCH_DEPTH && value >= 1 && value <= vslam_ctx::kMaxBatchDepth) ctx->batch_depth = value;
@@ -514,6 +516,7 @@ int vslam_debug_mma_timeouts(vslam_ctx* ctx) {
 }  // extern "C"
 
 // ---- stereo plan --------------------------------------------------------------------------------------
+static constexpr size_t kArenaMaxBytes = 2u << 20;  // plans whose results fit 2 MB (up to ~5 pairs of 1500) use one arena
 
 struct vslam_stereo_plan {
   vslam_ctx* ctx = nullptr;
@@ -521,6 +524,19 @@ struct vslam_stereo_plan {
   DevImages im{};
   DevBuf images, xy, ang, desc, nkp, matches, nmatch, jobs;
   DevBuf descx;  // the descriptors as 256 signed bytes each: operands of the tensor-core matcher (match_mma.cu)
+  // small plans (a few pairs: the latency path) keep xy | ang | desc | matches | nkp | nmatch in ONE allocation, so that a
+  // call's results travel in one device-to-host copy instead of six
+  DevBuf arena;
+  size_t arena_used = 0;
+  // ... and replay their launch sequence (init, response, select, describe, the two-launch split matcher) as ONE CUDA
+  // graph: captured on the second run with the same arguments and options, replayed from the third (config 1: the
+  // reference calls the path one pair at a time, slam.cpp:1125-1143, and six launches cost more host time than the
+  // copies).  0: nothing yet, 1: ran once uncaptured with graph_key (allocations are warm), 2: graph_exec ready,
+  // 3: capture failed once, never again.
+  int graph_state = 0;
+  unsigned long long graph_key = 0;
+  cudaGraphExec_t graph_exec = nullptr;
+  long long graph_launches = 0;
   DevBuf cand, candcnt, imgmax, selws;
   DevBuf mrow, mcol;            // scratch of the small-batch column-split matcher (plans run on their own streams)
   DevBuf inliers, ninl, epiws;  // optional fused findInliersEssential stage (vslam_stereo_plan_set_epipolar)
@@ -540,10 +556,11 @@ void vslam_stereo_plan_destroy(vslam_stereo_plan* plan) {
   cudaDeviceSynchronize();
   DevBuf* bufs[] = {&plan->images, &plan->xy, &plan->ang, &plan->desc, &plan->nkp, &plan->matches, &plan->nmatch,
                     &plan->jobs, &plan->cand, &plan->candcnt, &plan->imgmax, &plan->selws, &plan->inliers,
-                    &plan->ninl, &plan->epiws, &plan->mrow, &plan->mcol, &plan->descx};
+                    &plan->ninl, &plan->epiws, &plan->mrow, &plan->mcol, &plan->descx, &plan->arena};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 6; ++i)
     if (plan->ev[i]) cudaEventDestroy(plan->ev[i]);
+  if (plan->graph_exec) cudaGraphExecDestroy(plan->graph_exec);
   if (plan->stream) cudaStreamDestroy(plan->stream);
   delete plan;
 }
@@ -573,12 +590,29 @@ static int plan_create_impl(vslam_ctx* ctx, int w, int h, int max_pairs, int cap
   } while (0)
   PLAN_CUDA(p->images.reserve(p->im.stride * nimg));
   p->im.base = p->images.as<uint8_t>();
-  PLAN_CUDA(p->xy.reserve((size_t)nimg * cap * 16));
-  PLAN_CUDA(p->ang.reserve((size_t)nimg * cap * 8));
-  PLAN_CUDA(p->desc.reserve((size_t)nimg * cap * 32));
-  PLAN_CUDA(p->nkp.reserve((size_t)nimg * 4));
-  PLAN_CUDA(p->matches.reserve((size_t)max_pairs * cap * 8));
-  PLAN_CUDA(p->nmatch.reserve((size_t)max_pairs * 4));
+  {
+    const size_t b_xy = (size_t)nimg * cap * 16, b_ang = (size_t)nimg * cap * 8, b_desc = (size_t)nimg * cap * 32;
+    const size_t b_m = (size_t)max_pairs * cap * 8, b_nkp = ((size_t)nimg * 4 + 15) & ~(size_t)15, b_nm = ((size_t)max_pairs * 4 + 15) & ~(size_t)15;
+    const size_t total = b_xy + b_ang + b_desc + b_m + b_nkp + b_nm;
+    if (total <= kArenaMaxBytes) {
+      PLAN_CUDA(p->arena.reserve(total));
+      uint8_t* a = p->arena.as<uint8_t>();
+      p->xy.alias(a, b_xy); a += b_xy;
+      p->ang.alias(a, b_ang); a += b_ang;
+      p->desc.alias(a, b_desc); a += b_desc;
+      p->matches.alias(a, b_m); a += b_m;
+      p->nkp.alias(a, b_nkp); a += b_nkp;
+      p->nmatch.alias(a, b_nm);
+      p->arena_used = total;
+    } else {
+      PLAN_CUDA(p->xy.reserve(b_xy));
+      PLAN_CUDA(p->ang.reserve(b_ang));
+      PLAN_CUDA(p->desc.reserve(b_desc));
+      PLAN_CUDA(p->nkp.reserve((size_t)nimg * 4));
+      PLAN_CUDA(p->matches.reserve(b_m));
+      PLAN_CUDA(p->nmatch.reserve((size_t)max_pairs * 4));
+    }
+  }
   PLAN_CUDA(p->jobs.reserve((size_t)max_pairs * sizeof(MatchJob)));
   rc = prepare_detect_ws(ctx, w, h, nimg, p->cand, p->candcnt, p->imgmax, p->selws, &p->ws);
   if (rc) return fail(rc);
@@ -626,22 +660,55 @@ int vslam_stereo_plan_run(vslam_stereo_plan* plan, int count, int num_features, 
   if (num_features <= 0 || num_features > plan->cap) return vs_fail(ctx, VSLAM_E_ARG, "num_features must be in [1, cap]");
   if (count == 0) return VSLAM_OK;
   VS_CUDA(ctx, cudaSetDevice(ctx->device));
+  // latency path: a small pipeline plan replays its launches as one graph (see vslam_stereo_plan::graph_state)
+  const bool want_graph = ctx->use_graph && plan->arena_used && plan->stream && !plan->epi_on && plan->graph_state != 3;
+  unsigned long long key = 1469598103934665603ull;
+  if (want_graph) {
+    unsigned long long rbits, kbits;
+    memcpy(&rbits, &match_dist_2_best, 8);
+    memcpy(&kbits, &ctx->harris_k, 8);
+    const unsigned long long parts[] = {(unsigned long long)count, (unsigned long long)num_features, (unsigned long long)(rotate != 0),
+                                        (unsigned long long)(unsigned)match_threshold, rbits, kbits,
+                                        (unsigned long long)ctx->fp_contract, (unsigned long long)ctx->match_csa,
+                                        (unsigned long long)ctx->harris_on, (unsigned long long)ctx->resp_band,
+                                        (unsigned long long)ctx->match_split_small, (unsigned long long)ctx->match_mma};
+    for (unsigned long long v : parts) key = (key ^ v) * 1099511628211ull;
+    if (plan->graph_state == 2 && plan->graph_key == key) {
+      VS_CUDA(ctx, cudaGraphLaunch(plan->graph_exec, plan->stream));
+      ctx->launches += plan->graph_launches;
+      plan->timed = false;  // no per-stage events inside a replay
+      return VSLAM_OK;
+    }
+    if (plan->graph_state == 2) {  // other arguments: start over
+      cudaGraphExecDestroy(plan->graph_exec);
+      plan->graph_exec = nullptr;
+      plan->graph_state = 0;
+    }
+  }
+  const bool capture = want_graph && plan->graph_state == 1 && plan->graph_key == key;
+  const long long launches0 = ctx->launches;
   cudaStream_t saved = ctx->stream;
   ctx->stream = plan_stream(plan);
+  if (capture && cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed) != cudaSuccess) {
+    ctx->stream = saved;
+    plan->graph_state = 3;
+    return vslam_stereo_plan_run(plan, count, num_features, rotate, match_threshold, match_dist_2_best);
+  }
+#define PLAN_EVENT(i) do { if (!capture) cudaEventRecord(plan->ev[i], ctx->stream); } while (0)
   const int nimg = 2 * count;
   int rc = VSLAM_OK;
-  cudaEventRecord(plan->ev[0], ctx->stream);
+  PLAN_EVENT(0);
   if (plan->w < 2 * kEdgeThreshold + 1 || plan->h < 2 * kEdgeThreshold + 1) {
     cudaMemsetAsync(plan->nkp.p, 0, (size_t)nimg * 4, ctx->stream);
-    cudaEventRecord(plan->ev[1], ctx->stream);
-    cudaEventRecord(plan->ev[2], ctx->stream);
+    PLAN_EVENT(1);
+    PLAN_EVENT(2);
   } else {
     rc = launch_response(ctx, plan->im, nimg, plan->ws, nullptr);
-    cudaEventRecord(plan->ev[1], ctx->stream);
+    PLAN_EVENT(1);
     if (!rc)
       rc = launch_select(ctx, plan->im, nimg, plan->ws, num_features, kQuality, kMinDistance, kEdgeThreshold,
                          plan->xy.as<double>(), plan->nkp.as<int32_t>(), plan->cap);
-    cudaEventRecord(plan->ev[2], ctx->stream);
+    PLAN_EVENT(2);
   }
   // enough jobs to fill the GPU with one CTA per SM: Hamming matrix on the tensor cores (the describe kernel then also
   // writes every descriptor as 256 signed bytes, the matcher's operand format); else the POPC kernels, whose
@@ -656,7 +723,7 @@ int vslam_stereo_plan_run(vslam_stereo_plan* plan, int count, int num_features, 
     rc = launch_orient_describe(ctx, plan->im, nimg, plan->xy.as<double>(), plan->nkp.as<int32_t>(), plan->cap,
                                 rotate ? 1 : 0, plan->ang.as<double>(), plan->desc.as<uint32_t>(),
                                 mma ? plan->descx.as<uint8_t>() : nullptr);
-  cudaEventRecord(plan->ev[3], ctx->stream);
+  PLAN_EVENT(3);
   if (!rc) {
     if (mma) {
       const long long rows = (long long)nimg * plan->cap;
@@ -668,7 +735,7 @@ int vslam_stereo_plan_run(vslam_stereo_plan* plan, int count, int num_features, 
                              match_dist_2_best, plan->cap, &plan->mrow, &plan->mcol);
     }
   }
-  cudaEventRecord(plan->ev[4], ctx->stream);
+  PLAN_EVENT(4);
   if (!rc && plan->epi_on) {
     // matching_utils.h:63-88 on the matcher's device output: left corners of pair k are image 2k, right 2k+1
     rc = launch_essential_jobs(ctx, &plan->epi.cam1, &plan->epi.cam2, plan->epi.E, plan->epi.epipolar_error_threshold,
@@ -678,8 +745,31 @@ int vslam_stereo_plan_run(vslam_stereo_plan* plan, int count, int num_features, 
                                plan->inliers.as<int32_t>(), (size_t)plan->cap, plan->cap, plan->ninl.as<int32_t>(),
                                nullptr);
   }
-  cudaEventRecord(plan->ev[5], ctx->stream);
-  plan->timed = true;
+  PLAN_EVENT(5);
+#undef PLAN_EVENT
+  plan->timed = !capture;
+  if (capture) {
+    cudaGraph_t g = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(ctx->stream, &g);
+    ctx->stream = saved;
+    if (rc == VSLAM_OK && e == cudaSuccess && g &&
+        cudaGraphInstantiate(&plan->graph_exec, g, 0) == cudaSuccess) {
+      plan->graph_state = 2;
+      plan->graph_launches = ctx->launches - launches0;
+      cudaGraphDestroy(g);
+      VS_CUDA(ctx, cudaGraphLaunch(plan->graph_exec, plan->stream));
+      return VSLAM_OK;
+    }
+    if (g) cudaGraphDestroy(g);
+    cudaGetLastError();
+    plan->graph_state = 3;     // nothing has run: do it the ordinary way, and never try again on this plan
+    ctx->launches = launches0;
+    return vslam_stereo_plan_run(plan, count, num_features, rotate, match_threshold, match_dist_2_best);
+  }
+  if (want_graph && rc == VSLAM_OK) {
+    plan->graph_state = 1;
+    plan->graph_key = key;
+  }
   ctx->stream = saved;
   return rc;
 }
@@ -803,6 +893,7 @@ static int stereo_batch_impl(vslam_ctx* ctx, const uint8_t* images, int count, c
     plans[i] = cp;
   }
   int bad_kp = 0;
+  const vslam_stereo_plan* arena_plan = nullptr;
   // keypoint counts / detector statuses land in the caller's n_kp, or in the ctx's own pinned block when the caller
   // passes none (an overflowed image must not come back as "no matches, OK")
   int32_t* kp_status_host = n_kp;
@@ -810,6 +901,7 @@ static int stereo_batch_impl(vslam_ctx* ctx, const uint8_t* images, int count, c
     const size_t need = 2 * (size_t)count * sizeof(int32_t);
     if (need > ctx->pinned_status_bytes) {
       if (ctx->pinned_status) cudaFreeHost(ctx->pinned_status);
+  if (ctx->pinned_out) cudaFreeHost(ctx->pinned_out);
       ctx->pinned_status = nullptr;
       ctx->pinned_status_bytes = 0;
       if (cudaMallocHost(&ctx->pinned_status, need) != cudaSuccess) rc = vs_fail(ctx, VSLAM_E_CUDA, "stereo batch: pinned status block");
@@ -832,6 +924,23 @@ static int stereo_batch_impl(vslam_ctx* ctx, const uint8_t* images, int count, c
     auto d2h = [&](void* dst, const void* src, size_t bytes) {
       if (e == cudaSuccess) e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s);
     };
+    if (nchunks == 1 && p->arena_used && nc == p->max_pairs && !ep) {
+      // latency path (one chunk, a few pairs: config 1 as slam.cpp:1125-1143 issues it): ONE copy of the plan's result
+      // arena into the ctx's pinned block; after the synchronisation below the CPU hands the rows that exist to the
+      // caller's arrays (six small copies on the stream cost ~7 us each, and far more into pageable memory)
+      if (p->arena_used > ctx->pinned_out_bytes) {
+        if (ctx->pinned_out) cudaFreeHost(ctx->pinned_out);
+        ctx->pinned_out = nullptr;
+        ctx->pinned_out_bytes = 0;
+        e = cudaMallocHost(&ctx->pinned_out, p->arena_used);
+        if (e == cudaSuccess) ctx->pinned_out_bytes = p->arena_used;
+      }
+      d2h(ctx->pinned_out, p->arena.p, p->arena_used);
+      if (e == cudaSuccess) {
+        arena_plan = p;
+        continue;
+      }
+    }
     if (xy) d2h(xy + i0 * cp * 2, p->xy.p, ni * cp * 16);
     if (angles) d2h(angles + i0 * cp, p->ang.p, ni * cp * 8);
     if (desc) d2h(desc + i0 * cp * 8, p->desc.p, ni * cp * 32);
@@ -847,6 +956,31 @@ static int stereo_batch_impl(vslam_ctx* ctx, const uint8_t* images, int count, c
   }
   for (int i = 0; i < nplans; ++i)
     if (plans[i]) cudaStreamSynchronize(plans[i]->stream);
+  if (!rc && arena_plan) {
+    // hand the arena out: rows [0, n_kp) of every image, [0, n_matches) of every pair (the slabs' tails stay untouched,
+    // as undefined as the device left them before)
+    const vslam_stereo_plan* p = arena_plan;
+    const uint8_t* a = static_cast<const uint8_t*>(ctx->pinned_out);
+    const size_t nimg = 2 * (size_t)count, cp = cap;
+    const double* h_xy = reinterpret_cast<const double*>(a + ((uint8_t*)p->xy.p - (uint8_t*)p->arena.p));
+    const double* h_ang = reinterpret_cast<const double*>(a + ((uint8_t*)p->ang.p - (uint8_t*)p->arena.p));
+    const uint32_t* h_desc = reinterpret_cast<const uint32_t*>(a + ((uint8_t*)p->desc.p - (uint8_t*)p->arena.p));
+    const int32_t* h_m = reinterpret_cast<const int32_t*>(a + ((uint8_t*)p->matches.p - (uint8_t*)p->arena.p));
+    const int32_t* h_nkp = reinterpret_cast<const int32_t*>(a + ((uint8_t*)p->nkp.p - (uint8_t*)p->arena.p));
+    const int32_t* h_nm = reinterpret_cast<const int32_t*>(a + ((uint8_t*)p->nmatch.p - (uint8_t*)p->arena.p));
+    for (size_t i = 0; i < nimg; ++i) {
+      const size_t n = h_nkp[i] > 0 ? (size_t)(h_nkp[i] < cap ? h_nkp[i] : cap) : 0;
+      kp_status_host[i] = h_nkp[i];
+      if (xy) memcpy(xy + i * cp * 2, h_xy + i * cp * 2, n * 16);
+      if (angles) memcpy(angles + i * cp, h_ang + i * cp, n * 8);
+      if (desc) memcpy(desc + i * cp * 8, h_desc + i * cp * 8, n * 32);
+    }
+    for (size_t k = 0; k < (size_t)count; ++k) {
+      const size_t n = h_nm[k] > 0 ? (size_t)(h_nm[k] < cap ? h_nm[k] : cap) : 0;
+      if (n_matches) n_matches[k] = h_nm[k];
+      if (matches) memcpy(matches + k * cp * 2, h_m + k * cp * 2, n * 8);
+    }
+  }
   if (!rc)
     for (size_t i = 0; i < 2 * (size_t)count; ++i)
       if (kp_status_host[i] < 0) bad_kp = kp_status_host[i];

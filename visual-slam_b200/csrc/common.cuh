@@ -25,10 +25,19 @@ struct DevBuf {
     return e;
   }
   void release() {
-    if (p) cudaFree(p);
+    if (p && owned) cudaFree(p);
     p = nullptr;
     bytes = 0;
+    owned = true;
   }
+  // a window into another buffer (never freed, never grown)
+  void alias(void* ptr, size_t n) {
+    release();
+    p = ptr;
+    bytes = n;
+    owned = false;
+  }
+  bool owned = true;
   template <class T>
   T* as() const { return reinterpret_cast<T*>(p); }
 };
@@ -46,6 +55,7 @@ struct vslam_ctx {
   double harris_k = 0.04;  // cv::goodFeaturesToTrack's default k
   int resp_band = 0;  // response kernel: forced box height (0 = chosen per launch)
   int match_split_small = 1;  // batches with fewer jobs than SMs/2: split every job's columns over CTAs
+  int use_graph = 1;          // small pipeline plans of vslam_stereo_batch replay their launches as one CUDA graph
   int match_mma = 1;          // batches with at least SMs/2 jobs: Hamming matrix on the tensor cores (match_mma.cu)
   long long launches = 0;
   float last_match_ms = 0.f;
@@ -64,6 +74,8 @@ struct vslam_ctx {
   void* pinned = nullptr;  // small pinned staging block for counts
   void* pinned_status = nullptr;  // vslam_stereo_batch: per-image detector statuses when the caller passes no n_kp
   size_t pinned_status_bytes = 0;
+  void* pinned_out = nullptr;     // vslam_stereo_batch, single-chunk calls of a few pairs: the plan's whole result arena
+  size_t pinned_out_bytes = 0;    // arrives here in ONE copy and is handed out to the caller's arrays by the CPU
   // pipeline plans of vslam_stereo_batch, kept between calls (same geometry -> no reallocation)
   static constexpr int kMaxBatchDepth = 4;
   struct vslam_stereo_plan* batch_plans[kMaxBatchDepth] = {nullptr, nullptr, nullptr, nullptr};

@@ -52,6 +52,7 @@ VSLAM_OPT_BATCH_DEPTH = 4
 VSLAM_OPT_MATCH_SPLIT_SMALL = 5
 VSLAM_OPT_RESPONSE_BAND = 6
 VSLAM_OPT_MATCH_MMA = 7
+VSLAM_OPT_GRAPH = 8
 
 
 class VslamError(RuntimeError):
