@@ -379,7 +379,7 @@ def run_ours(args):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": t_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "u8 -> f32/f64 (response), f64 (rBRIEF rotation), u32 popc (matching)", "data": "synthetic",
+        "dtype": "u8 -> f32/f64 (response), f64 (rBRIEF rotation), s8 x s8 -> s32 on tcgen05 (matching: dot = 256 - 2 * hamming, exact)", "data": "synthetic",
         "config": {"workload": "BASELINE configs[1]: %d synthetic 752x480 stereo pairs per GPU per step (%d distinct, "
                                "repeated), detect+describe both images (1500 features) + stereo match (70, 1.2)"
                                % (n_pairs, n_distinct),
