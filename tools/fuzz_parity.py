@@ -7,7 +7,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 import oracle, visnav_b200
 from visnav_b200 import workloads as wl
-from visnav_b200.keypoints import DescStore, VSLAM_OPT_RESPONSE_BAND
+from visnav_b200.keypoints import DescStore, VSLAM_OPT_RESPONSE_BAND, VSLAM_OPT_MATCH_MMA
 
 budget = float(os.environ.get("FUZZ_SECONDS", "60"))
 seed = int(os.environ.get("FUZZ_SEED", "1"))
@@ -23,6 +23,8 @@ while time.time() < t_end and len(stats["failures"]) < 5:
     w, h = int(rng.integers(40, 1300)), int(rng.integers(40, 900))
     # box height of the response kernel: chosen by the library, the whole image, or anything in between
     ctx.set_option(VSLAM_OPT_RESPONSE_BAND, [0, 65535, int(rng.integers(8, 300))][it % 3])
+    # matcher: library's choice, tensor cores forced for every batch, POPC kernels only
+    ctx.set_option(VSLAM_OPT_MATCH_MMA, [2, 1, 2, 0][(it // 8) % 4])
     if kind == 0:
         img = wl.synth_image(int(rng.integers(0, 1 << 30)), w, h)
     elif kind == 1:
@@ -54,7 +56,7 @@ while time.time() < t_end and len(stats["failures"]) < 5:
     stats["match_calls"] += 1
     if not np.array_equal(got, want):
         stats["failures"].append(dict(what="match", n1=n1, n2=n2, thr=thr, ratio=ratio, got=len(got), want=len(want)))
-    if it % 8 == 0:   # batched jobs on a store (both matcher layouts depending on the job count)
+    if it % 4 == 0:   # batched jobs on a store (both matcher layouts depending on the job count)
         ns = int(rng.integers(2, 7))
         sets = [wl.flip_bits(base[:int(rng.integers(0, len(base) + 1))], 10, rng) for _ in range(ns)]
         store = DescStore(ctx, sets)
@@ -67,6 +69,9 @@ while time.time() < t_end and len(stats["failures"]) < 5:
                 stats["failures"].append(dict(what="match_batch", a=int(a), b=int(b), sizes=[len(s) for s in sets]))
         store.close()
 stats["iterations"] = it
+stats["mma_timeouts"] = ctx.mma_timeouts()
+if stats["mma_timeouts"]:
+    stats["failures"].append(dict(what="mma pipeline timeout"))
 print(json.dumps(stats))
 os.makedirs("gpurun_out", exist_ok=True)
 json.dump(stats, open("gpurun_out/fuzz.json", "w"), indent=1)

@@ -113,24 +113,29 @@ def main():
     ref = oracle.load_ref()
     rep = dict(cv2=(cv2.__version__ if cv2 is not None else None), reference_library=ref is not None, sizes=[])
     if cv2 is not None:
-        # response MAP vs cv2.cornerMinEigenVal (scalar dispatch) pixel by pixel: OpenCV's box filter keeps a RUNNING
-        # column sum in double (ColumnSum<double, float>); where an addition is inexact its rounding residue travels
-        # down the column, and far below a strong edge it can tip the float rounding of a WEAK response by one ulp.
-        # The band-parallel kernel (and the oracle) sum the three rows directly.
+        # response MAP vs cv2.cornerMinEigenVal (scalar dispatch) pixel by pixel, in both kernel modes: OpenCV's box
+        # filter keeps a RUNNING column sum in double (ColumnSum<double, float>); where an addition is inexact its
+        # rounding residue travels down the column.  Full-height boxes (what launches that fill the GPU use) restate it
+        # and must differ nowhere; row-banded launches (the default for a single image) sum the three rows directly.
+        from visnav_b200.keypoints import VSLAM_OPT_RESPONSE_BAND
         rm = []
-        for (w, h, seed) in [(752, 480, 1234), (1920, 1080, 77), (320, 240, 5)]:
+        for (w, h, seed) in [(752, 480, 1234), (1920, 1080, 77), (1920, 1080, 302), (320, 240, 5)]:
             img = wl.synth_image(seed, w, h)
             cv2.setUseOptimized(False)
             want = cv2.cornerMinEigenVal(img, 3, ksize=3)
             cv2.setUseOptimized(True)
-            got = ctx.response(img)
-            diff = got.view(np.int32).astype(np.int64) - want.view(np.int32).astype(np.int64)
-            bad = np.nonzero(diff)
             thr = float(want.max()) * 0.01
-            rm.append(dict(size="%dx%d" % (w, h), pixels=w * h, differing=int(len(bad[0])),
-                           max_ulp=int(np.abs(diff).max()), rate=len(bad[0]) / (w * h),
-                           largest_differing_response_over_threshold=(float(want[bad].max()) / thr if len(bad[0]) else 0.0),
-                           equals_oracle=bool(np.array_equal(got.view(np.uint32), o.response(img).view(np.uint32)))))
+            rec = dict(size="%dx%d" % (w, h), seed=seed, pixels=w * h,
+                       oracle_differing=int((o.response(img).view(np.uint32) != want.view(np.uint32)).sum()))
+            for mode, band in (("full_height", 65535), ("banded_default", 0)):
+                ctx.set_option(VSLAM_OPT_RESPONSE_BAND, band)
+                got = ctx.response(img)
+                ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 0)
+                diff = got.view(np.int32).astype(np.int64) - want.view(np.int32).astype(np.int64)
+                bad = np.nonzero(diff)
+                rec[mode] = dict(differing=int(len(bad[0])), max_ulp=int(np.abs(diff).max()), rate=len(bad[0]) / (w * h),
+                                 largest_differing_response_over_threshold=(float(want[bad].max()) / thr if len(bad[0]) else 0.0))
+            rm.append(rec)
         rep["response_map_vs_cv2_scalar"] = rm
     rep["sizes"].append(run_size(ctx, o, ref, 752, 480, 1500, a.pairs, 7000))
     rep["sizes"].append(run_size(ctx, o, ref, 1920, 1080, 4000, a.pairs_1080, 8000))
