@@ -131,8 +131,11 @@ __device__ __forceinline__ void rotate_pair(double c, double s, char4 q, double&
   }
 }
 
+#ifndef VSLAM_DESC_CTAS
+#define VSLAM_DESC_CTAS 6
+#endif
 template <bool kContract>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 6) orient_describe_kernel(const DescribeParams p) {
+__global__ void __launch_bounds__(kWarpsPerCta * 32, VSLAM_DESC_CTAS) orient_describe_kernel(const DescribeParams p) {
   __shared__ __align__(16) unsigned char patch_all[kWarpsPerCta][2][kPatchRows * kPatchPitch];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int img = blockIdx.y;
@@ -256,7 +259,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) orient_describe_kernel(c
       patch_wait<0>();
     }
     const unsigned char* centre = patch + kReach * kPatchPitch + off;
-    uint32_t my_word = 0, my_xword = 0;
+    uint32_t my_word = 0;
     int fmin = 1;  // smallest fixed-point fraction seen: 0 <=> some coordinate needs the exact round()
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
@@ -268,7 +271,6 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) orient_describe_kernel(c
       const int va = centre[yai * kPatchPitch + xai], vb = centre[ybi * kPatchPitch + xbi];
       const uint32_t word = __ballot_sync(0xFFFFFFFFu, va < vb);
       if (lane == k) my_word = word;
-      if ((lane >> 2) == k) my_xword = word;
     }
     if (__any_sync(0xFFFFFFFFu, fmin == 0)) {
       // a coordinate within 2^-21 of a halfway point (practically never): redo the keypoint with round()
@@ -280,13 +282,13 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) orient_describe_kernel(c
         const int va = centre[yai * kPatchPitch + xai], vb = centre[ybi * kPatchPitch + xbi];
         const uint32_t word = __ballot_sync(0xFFFFFFFFu, va < vb);
         if (lane == k) my_word = word;
-        if ((lane >> 2) == k) my_xword = word;
       }
     }
     if (lane < 8) p.desc[(slot0 + i) * 8 + lane] = my_word;
     if (p.descx) {
-      // lane l expands bits [8l, 8l + 8) = byte (l & 3) of word l >> 2 to eight signed bytes (1 -> 0x01, 0 -> 0xFF):
-      // one coalesced 256-byte row per keypoint
+      // lane l expands bits [8l, 8l + 8) = byte (l & 3) of word l >> 2 (held by lane l >> 2: one shuffle) to eight signed
+      // bytes (1 -> 0x01, 0 -> 0xFF): one coalesced 256-byte row per keypoint
+      const uint32_t my_xword = __shfl_sync(0xFFFFFFFFu, my_word, lane >> 2);
       const uint32_t bits = (my_xword >> (8 * (lane & 3))) & 0xFFu;
       const uint32_t b0 = ((bits & 0xFu) * 0x00204081u) & 0x01010101u, b1 = ((bits >> 4) * 0x00204081u) & 0x01010101u;
       reinterpret_cast<uint2*>(p.descx + (slot0 + i) * 256)[lane] =
