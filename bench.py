@@ -49,8 +49,14 @@ def kernel_traffic(name):
     try:
         rec = json.load(open(path))
         cur = hashlib.sha256(open(os.path.join(ROOT, rec["source"]), "rb").read()).hexdigest()
-        return rec["dram_bytes_per_unit"], {"traffic_source": "ncu --set full, profiles/%s_traffic.json (%s, per unit x units per launch)"
-                                            % (name, rec.get("report", "?")), "traffic_stale": cur != rec["source_sha256"]}
+        info = {"traffic_source": "ncu --set full, profiles/%s_traffic.json (%s, per unit x units per launch)"
+                                  % (name, rec.get("report", "?")), "traffic_stale": cur != rec["source_sha256"]}
+        if rec.get("issue_active_pct") is not None:
+            # what actually bounds these kernels: issue slots and pipes busy in the same capture
+            info["compute"] = {"issue_active_pct": rec["issue_active_pct"], "pipe_pct": rec.get("pipe_pct"),
+                               "warp_instructions_per_unit": (rec["warp_instructions"] / rec["units_per_launch"]
+                                                              if rec.get("warp_instructions") else None)}
+        return rec["dram_bytes_per_unit"], info
     except Exception as e:   # no capture committed: say so instead of inventing a number
         return None, {"traffic_source": "no capture (%s)" % type(e).__name__, "traffic_stale": True}
 

@@ -69,7 +69,19 @@ def traffic(path, pattern, units, source, out_json):
         v, u = float(best[H.index(m)].replace(",", "")), rows[1][H.index(m)]
         return v * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[u]
     rd, wr = val("dram__bytes_read.sum"), val("dram__bytes_write.sum")
+    def opt(m):
+        try:
+            return float(best[H.index(m)].replace(",", ""))
+        except (ValueError, IndexError):
+            return None
     rec = {"kernel": best[H.index("Kernel Name")].split("(")[0], "report": os.path.basename(path), "units_per_launch": int(units),
+           "warp_instructions": opt("smsp__inst_executed.sum"),
+           "issue_active_pct": opt("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+           "pipe_pct": {"alu": opt("sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active"),
+                        "fma": opt("sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active"),
+                        "fp64": opt("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"),
+                        "xu": opt("sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"),
+                        "tensor": opt("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active")},
            "dram_bytes_read": rd, "dram_bytes_write": wr, "dram_bytes_per_unit": (rd + wr) / int(units),
            "gpu_time_us": float(best[H.index("gpu__time_duration.sum")].replace(",", "")) *
                           {"ns": 1e-3, "us": 1.0, "ms": 1e3}.get(rows[1][H.index("gpu__time_duration.sum")], 1.0),

@@ -266,6 +266,73 @@ __global__ void __launch_bounds__(32 * (kEpiWarps + 1), 1)
   }
 }
 
+// ---- MMA-only rate for other instruction shapes: N = 128 tiles, optionally as the matcher issues them (per tile pair
+// eight MMAs A x B^T and eight with the operands swapped), no epilogue, two TMEM stages ----
+template <int kNn, bool kSwap>
+__global__ void __launch_bounds__(32 * (kEpiWarps + 1), 1)
+    umma_shape_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int tiles) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  Smem& s = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    mbar_init(&s.bar_load, 1);
+    mbar_init(&s.bar_full[0], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kEpiWarps) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s.tmem_base)), "n"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s.tmem_base;
+  if (warp == kEpiWarps && lane == 0) {
+    mbar_expect_tx(&s.bar_load, (kM + kN) * kKB);
+    for (int hk = 0; hk < 2; ++hk) {
+      tma_load_2d(&tmA, s.a[hk], &s.bar_load, hk * 128, 0);
+      tma_load_2d(&tmB, s.b[hk], &s.bar_load, hk * 128, 0);
+    }
+    bool ok = mbar_wait(&s.bar_load, 0);
+    tc_fence_after();
+    const uint32_t idesc = umma_idesc_s8(kM, kNn);
+    for (int t = 0; t < tiles && ok; ++t) {
+      const uint32_t d = tmem + (t & 1) * 256;
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        umma_i8(d, umma_desc_sw128(smem_u32(s.a[k >> 2]) + (k & 3) * 32), umma_desc_sw128(smem_u32(s.b[k >> 2]) + (k & 3) * 32), idesc, k > 0);
+      if (kSwap) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          umma_i8(d + 128, umma_desc_sw128(smem_u32(s.b[k >> 2]) + (k & 3) * 32), umma_desc_sw128(smem_u32(s.a[k >> 2]) + (k & 3) * 32), idesc, k > 0);
+      }
+    }
+    umma_commit(&s.bar_full[0]);
+    mbar_wait(&s.bar_full[0], 0);
+  }
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kEpiWarps) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512) : "memory");
+}
+
+template <int kNn, bool kSwap>
+static double run_shape(const CUtensorMap& tmA, const CUtensorMap& tmB, int sms, int tiles, size_t smem) {
+  CK(cudaFuncSetAttribute(umma_shape_kernel<kNn, kSwap>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaEvent_t e0, e1;
+  CK(cudaEventCreate(&e0));
+  CK(cudaEventCreate(&e1));
+  umma_shape_kernel<kNn, kSwap><<<sms, 32 * (kEpiWarps + 1), smem>>>(tmA, tmB, 64);
+  CK(cudaDeviceSynchronize());
+  CK(cudaEventRecord(e0));
+  umma_shape_kernel<kNn, kSwap><<<sms, 32 * (kEpiWarps + 1), smem>>>(tmA, tmB, tiles);
+  CK(cudaEventRecord(e1));
+  CK(cudaDeviceSynchronize());
+  float ms = 0;
+  CK(cudaEventElapsedTime(&ms, e0, e1));
+  return (double)sms * tiles * kM * kNn * (kSwap ? 2 : 1) / (ms * 1e-3);   // raw 128 x N x 256 products per second, as distances
+}
+
 // ---- legacy mma.sync probes: register-only loops, 8 warps per CTA, many CTAs ----
 __global__ void mma_b1_kernel(int iters, int* sink) {
   uint32_t a0 = threadIdx.x * 2654435761u, a1 = a0 ^ 0x9E3779B9u, a2 = a0 * 3, a3 = a1 * 5, b0 = a0 + 7, b1 = a1 + 11;
@@ -492,6 +559,17 @@ int main() {
   }
   fflush(stdout);
 
+  if (!timeout && !bad) {
+    const double s256 = run_shape<256, false>(tmA, tmB, sms, 4000, smem);
+    const double s128 = run_shape<128, false>(tmA, tmB, sms, 8000, smem);
+    const double s128s = run_shape<128, true>(tmA, tmB, sms, 4000, smem);
+    CK(cudaMemcpyFromSymbol(&timeout, g_timeout, sizeof(int)));
+    printf("{\"probe\": \"umma_shapes\", \"timeout\": %d, \"raw_dist_per_s\": {\"m128n256\": %.4g, \"m128n128\": %.4g, "
+           "\"m128n128_plus_swapped\": %.4g}, \"cycles_per_mma_at_1965\": {\"m128n256\": %.1f, \"m128n128\": %.1f, \"m128n128_plus_swapped\": %.1f}}\n",
+           timeout, s256, s128, s128s, 128.0 * 256 / 8 / (s256 / sms / 1.965e9), 128.0 * 128 / 8 / (s128 / sms / 1.965e9),
+           128.0 * 128 / 8 / (s128s / sms / 1.965e9));
+    fflush(stdout);
+  }
   printf("{\"probe\": \"minmax_pipes\", \"lane_ops_per_clk_per_sm\": {\"vimnmx_u16x2\": %.1f, \"hmnmx2\": %.1f, \"mixed\": %.1f}}\n",
          run_minmax<0>(sms), run_minmax<1>(sms), run_minmax<2>(sms));
 
