@@ -246,7 +246,8 @@ __device__ __forceinline__ void fold_chunk(const uint32_t (&v)[32], int c0, int 
 // (min, second min) of one matrix row over the nvalid first columns of a 128-column TMEM tile, as 16-bit keys
 // hamming << 7 | column.  All of the row's loads are issued before the first one is consumed: a TMEM load behind a
 // running MMA takes several hundred cycles (measured: a warp that loaded chunk by chunk spent 2/3 of its time waiting).
-__device__ __forceinline__ void fold_tile(uint32_t taddr, int nvalid, int mlo, int mhi, uint32_t& k1, uint32_t& k2) {
+__device__ __forceinline__ void fold_tile(uint32_t taddr, int nvalid, int mlo, int mhi, uint64_t* t_empty, int lane, uint32_t& k1,
+                                          uint32_t& k2) {
   uint32_t p1a = 0xFFFFFFFFu, p2a = 0xFFFFFFFFu, p1b = 0xFFFFFFFFu, p2b = 0xFFFFFFFFu;
   uint32_t v0[32], v1[32], v2[32], v3[32];
   const int nch = (nvalid + 31) >> 5;  // 1..4 chunks hold a real column (warp-uniform)
@@ -255,6 +256,11 @@ __device__ __forceinline__ void fold_tile(uint32_t taddr, int nvalid, int mlo, i
   if (nch > 2) tmem_ld32(taddr + 64, v2);
   if (nch > 3) tmem_ld32(taddr + 96, v3);
   tmem_ld_wait();
+  // the row now sits in registers: hand the TMEM stage back to the MMA issuer BEFORE the fold, so that the next product
+  // into this stage runs under the ~1000 cycles of min/max below instead of after them
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(t_empty);
   if (nvalid == kTile) {
     // the common case as ONE basic block: the scheduler can run the key IMADs (FMA pipe) of one chunk under the min/max
     // (ALU pipe) of another -- both pipes issue every other cycle, and two warps share a scheduler
@@ -456,7 +462,8 @@ __global__ void __launch_bounds__(kThreads, 1)
             const uint32_t cbase = d2 ? i0 : j0;
             if (ok && q * 32 < (d2 ? n2 - j0 : n1 - i0)) {  // warp-uniform: the warp holds at least one real row
               uint32_t k1, k2;
-              fold_tile(tmem + ((uint32_t)(q * 32) << 16) + ts * 256 + (d2 ? kTile : 0), nvalid, p.key_mul_lo, p.key_mul_hi, k1, k2);
+              fold_tile(tmem + ((uint32_t)(q * 32) << 16) + ts * 256 + (d2 ? kTile : 0), nvalid, p.key_mul_lo, p.key_mul_hi,
+                        &s.t_empty[ts], lane, k1, k2);
               if (row < nrows) {
                 uint2* sp = (d2 ? cs : rs) + row;
                 uint2 acc = *sp;
@@ -466,10 +473,11 @@ __global__ void __launch_bounds__(kThreads, 1)
                 acc.y = min(min(acc.y, w2), hi);
                 *sp = acc;
               }
+            } else {  // nothing to read from this stage: release it at once
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&s.t_empty[ts]);
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&s.t_empty[ts]);
             if (lane == 0 && q == 0) MMA_ACC(d2 ? 18 : 10);
             if (lane == 0 && q == 0) MMA_TRACE(2 * use + t, d2 ? 3 : 2);
             if (t) ++t_it1; else ++t_it;
