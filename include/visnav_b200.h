@@ -357,6 +357,20 @@ int vslam_popc_peak(vslam_ctx* ctx, double* popc_per_s);
  * run: the job then reports count -2 instead of hanging the GPU), 0 if not, < 0 on a CUDA error. */
 int vslam_debug_mma_timeouts(vslam_ctx* ctx);
 
+/* ---- allocation-free entry point ------------------------------------------------------- */
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * vslam_best2 -- out3[3*i..] = (best distance, lowest index attaining it, second best), the row scan of
+ * keypoints.h:331-354 -- but d_q [nq][8], d_db [ndb][8] and d_out3 [nq][3] are DEVICE pointers (d_q / d_db 16-byte
+ * aligned) and the call allocates nothing: the per-range partials live in a fixed 2 MiB file-scope device array
+ * (csrc/noalloc.cu; every GPU that loads the library holds it until exit).  Limits: nq <= 4096, ndb <= 2^20;
+ * beyond them VSLAM_E_LIMIT with a message in vslam_last_error.  Work is issued on `stream` (a cudaStream_t; NULL:
+ * vslam_stream(ctx)) and is NOT synchronised.  The first call on a device looks the array's address up
+ * (cudaGetSymbolAddress): make it once before a capture.  All calls on a device share the array: calls that
+ * overlap on the GPU race and must be serialised by the caller. */
+int vslam_best2_noalloc(vslam_ctx* ctx, const uint32_t* d_q, int nq, const uint32_t* d_db, int ndb,
+                        int32_t* d_out3, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -9,7 +9,7 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB = os.path.join(CSRC, "libvisnav_b200.so")
-SOURCES = ["api.cu", "detect.cu", "describe.cu", "match.cu", "match_mma.cu", "landmarks.cu", "pyramid.cu", "geometry.cu", "bow.cu", "orb.cu"]
+SOURCES = ["api.cu", "detect.cu", "describe.cu", "match.cu", "match_mma.cu", "landmarks.cu", "pyramid.cu", "geometry.cu", "bow.cu", "orb.cu", "noalloc.cu"]
 HEADERS = ["common.cuh", "rbrief_pattern.inc", os.path.join("..", "..", "include", "visnav_b200.h")]
 # geometry.cu spells its arithmetic with plain * and +: without contraction it evaluates every expression exactly as the
 # oracle (gcc -ffp-contract=off) does, so inlier / visibility decisions do not depend on where nvcc would fuse.  The other

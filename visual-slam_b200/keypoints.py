@@ -28,7 +28,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 ABI_SYMBOLS = [
     "vslam_create", "vslam_destroy", "vslam_last_error", "vslam_set_option", "vslam_stream", "vslam_sync",
     "vslam_launch_count", "vslam_host_alloc", "vslam_host_free", "vslam_detect", "vslam_angles",
-    "vslam_describe", "vslam_detect_describe", "vslam_match", "vslam_best2", "vslam_response",
+    "vslam_describe", "vslam_detect_describe", "vslam_match", "vslam_best2", "vslam_best2_noalloc", "vslam_response",
     "vslam_match_landmarks", "vslam_pyramid_detect_describe_batch",
     "vslam_detect_describe_batch", "vslam_stereo_batch", "vslam_stereo_plan_create",
     "vslam_stereo_plan_destroy", "vslam_stereo_plan_upload", "vslam_stereo_plan_run",
@@ -132,6 +132,7 @@ def load_library():
     L.vslam_detect_describe.argtypes = [vp, vp, i, i, i, i, i, vp, vp, vp, i, C.POINTER(i)]
     L.vslam_match.argtypes = [vp, vp, i, vp, i, i, d, vp, i, C.POINTER(i)]
     L.vslam_best2.argtypes = [vp, vp, i, vp, i, vp]
+    L.vslam_best2_noalloc.argtypes = [vp, vp, i, vp, i, vp, vp]
     L.vslam_match_landmarks.argtypes = [vp, vp, vp, i, vp, i, vp, vp, d, i, d, vp, i, C.POINTER(i)]
     L.vslam_response.argtypes = [vp, vp, i, i, i, vp]
     L.vslam_detect_describe_batch.argtypes = [vp, vp, i, i, i, i, sz, i, i, vp, vp, vp, vp, i]
@@ -434,6 +435,12 @@ class Context:
         out = np.empty((len(q), 3), np.int32)
         self._check(self.lib.vslam_best2(self.h, _ptr(q), len(q), _ptr(db), len(db), _ptr(out)))
         return out
+
+    def best2_noalloc(self, d_q, nq, d_db, ndb, d_out3, stream=None):
+        """vslam_best2 on DEVICE buffers (integer addresses) with no allocation inside the call: see the header.  Not
+        synchronised; issued on `stream` (a cudaStream_t value) or the context's own stream."""
+        self._check(self.lib.vslam_best2_noalloc(self.h, C.c_void_p(d_q), int(nq), C.c_void_p(d_db), int(ndb),
+                                                 C.c_void_p(d_out3), C.c_void_p(stream)))
 
     def last_match_ms(self):
         return float(self.lib.vslam_last_match_ms(self.h))
