@@ -106,6 +106,18 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
       : "r"(taddr)
       : "memory");
 }
+// 64 columns as 32 registers: register j = low 16 bits of column 2j | low 16 bits of column 2j + 1 << 16
+__device__ __forceinline__ void tmem_ld32_pack16(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.pack::16b.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,"
+      "%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+        "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+        "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+        "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -202,7 +214,38 @@ __global__ void __launch_bounds__(32 * (kEpiWarps + 1), 1)
       ok = mbar_wait(&s.bar_full[st], (t >> 1) & 1);
       tc_fence_after();
       if (!ok) break;
-      if (kMode != 1) {
+      if (kMode >= 6) {
+        // 16-bit packed loads (dot in [-256, 256] fits): 64 columns per load.  6: loads only; 7: keys
+        // (256 - dot) << 6 | column & 63 from ONE xor (sign bits -> offset binary, no borrow between the halves) and ONE
+        // IMAD per two distances, then the packed (min, second min); 8: the registers as they arrive, for the host check
+#pragma unroll 1
+        for (int c0 = 0; c0 < kN; c0 += 64) {
+          uint32_t v[32];
+          tmem_ld32_pack16(lane_base + st * kN + c0, v);
+          tmem_ld_wait();
+          if (kMode == 8) {
+            int32_t* o = out + (size_t)(warp * 32 + lane) * kN + c0 / 2;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) o[j] = (int32_t)v[j];
+          } else if (kMode == 6) {
+            uint32_t x = 0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) x ^= (v[j] ^ v[j + 1]) ^ (v[j + 2] ^ v[j + 3]);
+            acc += x;
+          } else {
+            const int mul = -64;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const uint32_t half = 64u * (32768u + 256u) + (uint32_t)(2 * j);
+              const uint32_t cst = half + ((half + 1u) << 16);  // mod 2^32: per half (33024 - x) * 64 + column
+              const uint32_t key = (uint32_t)((int)(v[j] ^ 0x80008000u) * mul + (int)cst);
+              const uint32_t tmax = __vmaxu2(p1, key);
+              p1 = __vminu2(p1, key);
+              p2 = __vminu2(p2, tmax);
+            }
+          }
+        }
+      } else if (kMode != 1) {
 #pragma unroll 1
         for (int c0 = 0; c0 < kN; c0 += 32) {
           uint32_t v[32];
@@ -543,6 +586,36 @@ int main() {
          "\"d_0_0\": %d, \"d_0_1\": %d, \"d_1_0\": %d}\n",
          timeout, bad, kM * kN, first_bad, hout[3 * kN + 5], hout[0], hout[1], hout[kN]);
   fflush(stdout);
+  {  // what pack::16b hands out: register j of the k-th 64-column load = columns (64k + 2j, 64k + 2j + 1) as int16 halves?
+    CK(cudaFuncSetAttribute(umma_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CK(cudaMemset(dout, 0x7F, (size_t)kM * kN * 4));
+    umma_kernel<8><<<1, 32 * (kEpiWarps + 1), smem>>>(tmA, tmB, 1, dout, sink);
+    CK(cudaDeviceSynchronize());
+    std::vector<int32_t> hp((size_t)kM * kN);
+    CK(cudaMemcpy(hp.data(), dout, hp.size() * 4, cudaMemcpyDeviceToHost));
+    long badp = 0, badkey = 0;
+    int firstp = -1;
+    for (int i = 0; i < kM; ++i)
+      for (int j = 0; j < kN / 2; ++j) {
+        const uint32_t r = (uint32_t)hp[(size_t)i * kN + j];
+        const int lo = (int16_t)(r & 0xFFFF), hi = (int16_t)(r >> 16);
+        const int wlo = hout[(size_t)i * kN + 2 * j], whi = hout[(size_t)i * kN + 2 * j + 1];
+        if (lo != wlo || hi != whi) {
+          if (firstp < 0) firstp = i * kN + j;
+          ++badp;
+        }
+        // the key arithmetic of mode 7 on the host: per half (256 - dot) << 6 | column & 63, no cross-half borrow
+        const uint32_t half = 64u * (32768u + 256u) + (uint32_t)((2 * j) & 63);
+        const uint32_t cst = half + ((half + 1u) << 16);
+        const uint32_t key = (uint32_t)((int)(r ^ 0x80008000u) * -64 + (int)cst);
+        const uint32_t want = (uint32_t)(((256 - wlo) << 6) | ((2 * j) & 63)) | ((uint32_t)(((256 - whi) << 6) | ((2 * j + 1) & 63)) << 16);
+        badkey += key != want;
+      }
+    printf("{\"probe\": \"tmem_ld_pack16\", \"mismatches\": %ld, \"key_mismatches\": %ld, \"of\": %d, \"first_bad\": %d, "
+           "\"r_0_0\": \"%08x\", \"want_0_0\": [%d, %d]}\n",
+           badp, badkey, kM * kN / 2, firstp, (uint32_t)hp[0], hout[0], hout[1]);
+    fflush(stdout);
+  }
   if (timeout || bad) {
     printf("{\"probe\": \"umma_rates\", \"skipped\": \"tile test failed\"}\n");
   } else {
@@ -552,10 +625,13 @@ int main() {
     const double r3 = run_rate<3>(tmA, tmB, sms, tiles, dout, sink, smem);
     const double r4 = run_rate<4>(tmA, tmB, sms, tiles, dout, sink, smem);
     const double r5 = run_rate<5>(tmA, tmB, sms, tiles, dout, sink, smem);
+    const double r6 = run_rate<6>(tmA, tmB, sms, tiles, dout, sink, smem);
+    const double r7 = run_rate<7>(tmA, tmB, sms, tiles, dout, sink, smem);
     CK(cudaMemcpyFromSymbol(&timeout, g_timeout, sizeof(int)));
     printf("{\"probe\": \"umma_rates\", \"sms\": %d, \"tiles_per_cta\": %d, \"timeout\": %d, \"dist_per_s\": {\"mma\": %.4g, "
-           "\"ld\": %.4g, \"e32\": %.4g, \"e16\": %.4g, \"eh16\": %.4g}, \"int8_tops_mma\": %.1f}\n",
-           sms, tiles, timeout, r1, r2, r3, r4, r5, r1 * 512 / 1e12);
+           "\"ld\": %.4g, \"e32\": %.4g, \"e16\": %.4g, \"eh16\": %.4g, \"ld_pack16\": %.4g, \"e16_pack16\": %.4g}, "
+           "\"int8_tops_mma\": %.1f}\n",
+           sms, tiles, timeout, r1, r2, r3, r4, r5, r6, r7, r1 * 512 / 1e12);
   }
   fflush(stdout);
 
