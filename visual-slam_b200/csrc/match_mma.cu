@@ -128,10 +128,14 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t da, uint64_t d
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+// 64 accumulator columns of this thread's TMEM lane as 32 registers: pack::16b keeps the low 16 bits of every column
+// (exact here: dot is in [-256, 256]) and puts columns (2j, 2j + 1) into the halves of register j.  Half the TMEM read
+// traffic of the 32-bit form: measured (tools/probes/umma_hamming.cu, profiles/r3c_umma_pack16_probe.jsonl) the MMA runs
+// at its full rate under these loads (8.6e12 distances/s) and at 6.75e12 under the 32-bit ones.
+__device__ __forceinline__ void tmem_ld64_pack16(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,"
-      "%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      "tcgen05.ld.sync.aligned.32x32b.x32.pack::16b.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,"
+      "%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
       : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
         "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
         "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
@@ -177,9 +181,9 @@ struct MmaParams {
   double ratio;
   int cap;
   int max_n1, max_n2;
-  // -64 and -64 << 16: the multipliers that turn two accumulators into a packed key pair (fold_chunk).  Kernel
-  // parameters rather than literals: as literals ptxas re-materialises them with a MOV in front of every second IMAD
-  int key_mul_lo, key_mul_hi;
+  // -64: the multiplier that turns a register of two 16-bit accumulators into a packed key pair (fold_half).  A kernel
+  // parameter rather than a literal: as a literal ptxas re-materialises it with MOVs between the IMADs
+  int key_mul;
   // Column-split mode for ONE large job (split_range > 0; BASELINE config 4: a query set against a large map): CTA s
   // takes all split_n1 rows of the first array against columns [s * split_range, + split_range) of the second; its
   // row statistics are partial (rowpart[s][i], column indices relative to the range), its column statistics complete
@@ -220,69 +224,58 @@ __device__ __forceinline__ void fold2(uint32_t x, uint32_t y, uint32_t& m1, uint
   m2 = __vimin3_u16x2(m2, t, hi);
 }
 
-// One 32-column chunk of a row into two independent (min, second min) chains of packed 16-bit keys (columns 0-15 of
-// the chunk -> chain a, 16-31 -> chain b: the serial min/max dependency is what bounds a warp here).
-// acc = dot = 256 - 2 hamming, key16 = (256 - dot) << 6 | column; for the column pair (c, c + 1):
-//   P = dot_c * -64 + dot_c1 * (-64 << 16) + ((16384 + c) | (16384 + c + 1) << 16)      (two IMADs, FMA pipe)
+// One 64-column half of a row (32 registers of two 16-bit accumulators each) into two independent (min, second min)
+// chains of packed 16-bit keys (registers 0-15 -> chain a, 16-31 -> chain b: the serial min/max dependency is what
+// bounds a warp here).  acc = dot = 256 - 2 hamming, key16 = (256 - dot) << 6 | column = hamming << 7 | column.
+// Both halves of a register in ONE xor and ONE IMAD: flipping the sign bits turns the two's-complement halves into
+// offset binary x = dot + 32768 > 0, and then in plain 32-bit arithmetic
+//   (64 * 33024 + c) * 0x00010001 + 0x00010000 - 64 * (x_lo + 65536 x_hi)
+//     = ((256 - dot_lo) * 64 + c) + 65536 ((256 - dot_hi) * 64 + c + 1)          (mod 2^32)
+// with both parentheses in [0, 65536): no borrow crosses the halves.  (Without the xor a negative low half would
+// borrow 64 from the high one.)
 template <bool kMasked>
-__device__ __forceinline__ void fold_chunk(const uint32_t (&v)[32], int c0, int nv, int mlo, int mhi, uint32_t& p1a,
-                                           uint32_t& p2a, uint32_t& p1b, uint32_t& p2b) {
+__device__ __forceinline__ void fold_half(const uint32_t (&v)[32], int c0, int nv, int mul, uint32_t& p1a, uint32_t& p2a,
+                                          uint32_t& p1b, uint32_t& p2b) {
   const uint32_t cb = (uint32_t)c0 * 0x00010001u;
-  uint32_t key[16];
+  uint32_t key[32];
 #pragma unroll
-  for (int j = 0; j < 32; j += 2) {
-    const uint32_t cst = (uint32_t)(16384 + j) | ((uint32_t)(16384 + j + 1) << 16);
-    uint32_t k = (uint32_t)((int)v[j + 1] * mhi + (int)(cst + cb));
-    k = (uint32_t)((int)v[j] * mlo + (int)k);
-    if (kMasked) k |= (j >= nv ? 0x0000FFFFu : 0u) | (j + 1 >= nv ? 0xFFFF0000u : 0u);  // nv = valid columns of the chunk
-    key[j >> 1] = k;
+  for (int j = 0; j < 32; ++j) {
+    const uint32_t half = 64u * (32768u + 256u) + (uint32_t)(2 * j);
+    const uint32_t cst = half + ((half + 1u) << 16);
+    uint32_t k = (uint32_t)((int)(v[j] ^ 0x80008000u) * mul + (int)(cst + cb));
+    if (kMasked) k |= (2 * j >= nv ? 0x0000FFFFu : 0u) | (2 * j + 1 >= nv ? 0xFFFF0000u : 0u);  // nv = valid columns of the half
+    key[j] = k;
   }
 #pragma unroll
-  for (int i = 0; i < 8; i += 2) fold2(key[i], key[i + 1], p1a, p2a);
+  for (int i = 0; i < 16; i += 2) fold2(key[i], key[i + 1], p1a, p2a);
 #pragma unroll
-  for (int i = 8; i < 16; i += 2) fold2(key[i], key[i + 1], p1b, p2b);
+  for (int i = 16; i < 32; i += 2) fold2(key[i], key[i + 1], p1b, p2b);
 }
 
 // (min, second min) of one matrix row over the nvalid first columns of a 128-column TMEM tile, as 16-bit keys
-// hamming << 7 | column.  All of the row's loads are issued before the first one is consumed: a TMEM load behind a
+// hamming << 7 | column.  Both of the row's loads are issued before the first one is consumed: a TMEM load behind a
 // running MMA takes several hundred cycles (measured: a warp that loaded chunk by chunk spent 2/3 of its time waiting).
-__device__ __forceinline__ void fold_tile(uint32_t taddr, int nvalid, int mlo, int mhi, uint64_t* t_empty, int lane, uint32_t& k1,
+__device__ __forceinline__ void fold_tile(uint32_t taddr, int nvalid, int mul, uint64_t* t_empty, int lane, uint32_t& k1,
                                           uint32_t& k2) {
   uint32_t p1a = 0xFFFFFFFFu, p2a = 0xFFFFFFFFu, p1b = 0xFFFFFFFFu, p2b = 0xFFFFFFFFu;
-  uint32_t v0[32], v1[32], v2[32], v3[32];
-  const int nch = (nvalid + 31) >> 5;  // 1..4 chunks hold a real column (warp-uniform)
-  tmem_ld32(taddr, v0);
-  if (nch > 1) tmem_ld32(taddr + 32, v1);
-  if (nch > 2) tmem_ld32(taddr + 64, v2);
-  if (nch > 3) tmem_ld32(taddr + 96, v3);
+  uint32_t v0[32], v1[32];
+  tmem_ld64_pack16(taddr, v0);
+  if (nvalid > 64) tmem_ld64_pack16(taddr + 64, v1);  // warp-uniform
   tmem_ld_wait();
   // the row now sits in registers: hand the TMEM stage back to the MMA issuer BEFORE the fold, so that the next product
-  // into this stage runs under the ~1000 cycles of min/max below instead of after them
+  // into this stage runs under the min/max below instead of after them
   tc_fence_before();
   __syncwarp();
   if (lane == 0) mbar_arrive(t_empty);
   if (nvalid == kTile) {
-    // the common case as ONE basic block: the scheduler can run the key IMADs (FMA pipe) of one chunk under the min/max
-    // (ALU pipe) of another -- both pipes issue every other cycle, and two warps share a scheduler
-    fold_chunk<false>(v0, 0, 32, mlo, mhi, p1a, p2a, p1b, p2b);
-    fold_chunk<false>(v1, 32, 32, mlo, mhi, p1a, p2a, p1b, p2b);
-    fold_chunk<false>(v2, 64, 32, mlo, mhi, p1a, p2a, p1b, p2b);
-    fold_chunk<false>(v3, 96, 32, mlo, mhi, p1a, p2a, p1b, p2b);
+    // the common case as ONE basic block: the scheduler can run the key IMADs (FMA pipe) of one half under the min/max
+    // (ALU pipe) of the other
+    fold_half<false>(v0, 0, 64, mul, p1a, p2a, p1b, p2b);
+    fold_half<false>(v1, 64, 64, mul, p1a, p2a, p1b, p2b);
   } else {
-  if (nvalid >= 32) fold_chunk<false>(v0, 0, 32, mlo, mhi, p1a, p2a, p1b, p2b);
-  else fold_chunk<true>(v0, 0, nvalid, mlo, mhi, p1a, p2a, p1b, p2b);
-  if (nch > 1) {
-    if (nvalid >= 64) fold_chunk<false>(v1, 32, 32, mlo, mhi, p1a, p2a, p1b, p2b);
-    else fold_chunk<true>(v1, 32, nvalid - 32, mlo, mhi, p1a, p2a, p1b, p2b);
-  }
-  if (nch > 2) {
-    if (nvalid >= 96) fold_chunk<false>(v2, 64, 32, mlo, mhi, p1a, p2a, p1b, p2b);
-    else fold_chunk<true>(v2, 64, nvalid - 64, mlo, mhi, p1a, p2a, p1b, p2b);
-  }
-  if (nch > 3) {
-    if (nvalid >= 128) fold_chunk<false>(v3, 96, 32, mlo, mhi, p1a, p2a, p1b, p2b);
-    else fold_chunk<true>(v3, 96, nvalid - 96, mlo, mhi, p1a, p2a, p1b, p2b);
-  }
+    if (nvalid >= 64) fold_half<false>(v0, 0, 64, mul, p1a, p2a, p1b, p2b);
+    else fold_half<true>(v0, 0, nvalid, mul, p1a, p2a, p1b, p2b);
+    if (nvalid > 64) fold_half<true>(v1, 64, nvalid - 64, mul, p1a, p2a, p1b, p2b);
   }
   // merge the two chains, then the even-column list (low halves) with the odd-column list (high halves)
   const uint32_t p1 = __vminu2(p1a, p1b), p2 = __vminu2(__vmaxu2(p1a, p1b), __vminu2(p2a, p2b));
@@ -462,7 +455,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             const uint32_t cbase = d2 ? i0 : j0;
             if (ok && q * 32 < (d2 ? n2 - j0 : n1 - i0)) {  // warp-uniform: the warp holds at least one real row
               uint32_t k1, k2;
-              fold_tile(tmem + ((uint32_t)(q * 32) << 16) + ts * 256 + (d2 ? kTile : 0), nvalid, p.key_mul_lo, p.key_mul_hi,
+              fold_tile(tmem + ((uint32_t)(q * 32) << 16) + ts * 256 + (d2 ? kTile : 0), nvalid, p.key_mul,
                         &s.t_empty[ts], lane, k1, k2);
               if (row < nrows) {
                 uint2* sp = (d2 ? cs : rs) + row;
@@ -626,8 +619,7 @@ int launch_match_jobs_mma(vslam_ctx* ctx, const MatchJob* jobs_dev, int n_jobs, 
   p.cap = cap;
   p.max_n1 = max_n1;
   p.max_n2 = max_n2;
-  p.key_mul_lo = -64;
-  p.key_mul_hi = -(64 << 16);
+  p.key_mul = -64;
   p.split_range = 0; p.split_n1 = p.split_n2 = 0;
   p.rowpart = p.colstat = nullptr;
   const size_t smem = match_mma_smem_bytes(max_n1, max_n2);
@@ -673,8 +665,7 @@ int launch_match_split_mma(vslam_ctx* ctx, const uint8_t* x1, int n1, const uint
   p.n_jobs = nsplit;
   p.max_n1 = n1;
   p.max_n2 = range;
-  p.key_mul_lo = -64;
-  p.key_mul_hi = -(64 << 16);
+  p.key_mul = -64;
   p.split_range = range; p.split_n1 = n1; p.split_n2 = n2;
   p.rowpart = rowpart;
   p.colstat = colstat;
