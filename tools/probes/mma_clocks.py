@@ -39,7 +39,7 @@ if prof and hasattr(L, "vslam_debug_mma_trace"):
     assert L.vslam_debug_mma_trace(tr) == 0
     t = np.array(list(tr), np.int64).reshape(256, 12)
     t0 = t[0, 0]
-    print("pair | loop_top  t_empty_ok  issue_start  issued  committed | w0_full w0_done w4_done   (cycles since the first issue)")
+    print("pair | pre_b_full loop_top  t_empty_ok  issue_start  issued  issued_d2 committed | w0_full w0_loaded w0_done w4_done   (cycles since the first issue)")
     for k in list(range(0, 30)) + list(range(118, 126)):
         r = t[k] - t0
-        print("%4d | %8d %8d %8d %8d %8d | %8d %8d %8d" % (k, r[4], r[5], r[0], r[6], r[1], r[10], r[2], r[3]))
+        print("%4d | %8d %8d %8d %8d %8d %8d %8d | %8d %8d %8d %8d" % (k, r[8], r[4], r[5], r[0], r[6], r[9], r[1], r[10], r[7], r[2], r[3]))

@@ -313,13 +313,16 @@ __global__ void __launch_bounds__(32 * (kEpiWarps + 1), 1)
 // eight MMAs A x B^T and eight with the operands swapped), no epilogue, two TMEM stages ----
 template <int kNn, bool kSwap>
 __global__ void __launch_bounds__(32 * (kEpiWarps + 1), 1)
-    umma_shape_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int tiles) {
+    umma_shape_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int tiles, int side = 0,
+                      uint32_t* side_sink = nullptr) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   Smem& s = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  volatile uint32_t* done = reinterpret_cast<volatile uint32_t*>(&s.bar_empty[0]);  // (unused barrier slot as a flag)
   if (threadIdx.x == 0) {
     mbar_init(&s.bar_load, 1);
     mbar_init(&s.bar_full[0], 1);
+    *done = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == kEpiWarps) {
@@ -352,6 +355,30 @@ __global__ void __launch_bounds__(32 * (kEpiWarps + 1), 1)
     }
     umma_commit(&s.bar_full[0]);
     mbar_wait(&s.bar_full[0], 0);
+    *done = 1;
+  } else if (warp < kEpiWarps && side) {
+    // side work on the other warps (one per scheduler) while the MMAs run: does register-only arithmetic slow the tensor pipe?
+    //   1: 16-bit min/max (ALU pipe)  2: IMAD (FMA pipe)  3: both  4: shared-memory loads and stores
+    uint32_t x[8], y[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { x[i] = threadIdx.x * 2654435761u + i; y[i] = x[i] ^ 0x5bd1e995u; }
+    uint32_t* sm = reinterpret_cast<uint32_t*>(s.b[1]) + 8192 + threadIdx.x;  // a corner the MMA's operands do not use (kN = 256 rows: all used; see below)
+    while (!*done) {
+#pragma unroll 1
+      for (int it = 0; it < 64; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          if (side & 1) { const uint32_t t = __vmaxu2(x[i], y[i]); x[i] = __vminu2(x[i], y[i]); y[i] = __vminu2(y[i] + 1, t); }
+          if (side & 2) { x[i] = x[i] * 0x9E3779B1u + y[i]; y[i] = y[i] * 0x85EBCA77u + x[i]; }
+          if (side & 4) { x[i] += side_sink[(x[i] & 1023u)]; }
+        }
+      }
+    }
+    uint32_t a = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a += x[i] + y[i];
+    side_sink[1024 + blockIdx.x * 128 + threadIdx.x] = a;
+    (void)sm;
   }
   __syncwarp();
   tc_fence_before();
@@ -360,15 +387,20 @@ __global__ void __launch_bounds__(32 * (kEpiWarps + 1), 1)
 }
 
 template <int kNn, bool kSwap>
-static double run_shape(const CUtensorMap& tmA, const CUtensorMap& tmB, int sms, int tiles, size_t smem) {
+static double run_shape(const CUtensorMap& tmA, const CUtensorMap& tmB, int sms, int tiles, size_t smem, int side = 0) {
+  static uint32_t* side_sink = nullptr;
+  if (!side_sink) {
+    CK(cudaMalloc(&side_sink, (1024 + 148 * 256) * 4));
+    CK(cudaMemset(side_sink, 0, (1024 + 148 * 256) * 4));
+  }
   CK(cudaFuncSetAttribute(umma_shape_kernel<kNn, kSwap>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaEvent_t e0, e1;
   CK(cudaEventCreate(&e0));
   CK(cudaEventCreate(&e1));
-  umma_shape_kernel<kNn, kSwap><<<sms, 32 * (kEpiWarps + 1), smem>>>(tmA, tmB, 64);
+  umma_shape_kernel<kNn, kSwap><<<sms, 32 * (kEpiWarps + 1), smem>>>(tmA, tmB, 64, side, side_sink);
   CK(cudaDeviceSynchronize());
   CK(cudaEventRecord(e0));
-  umma_shape_kernel<kNn, kSwap><<<sms, 32 * (kEpiWarps + 1), smem>>>(tmA, tmB, tiles);
+  umma_shape_kernel<kNn, kSwap><<<sms, 32 * (kEpiWarps + 1), smem>>>(tmA, tmB, tiles, side, side_sink);
   CK(cudaEventRecord(e1));
   CK(cudaDeviceSynchronize());
   float ms = 0;
@@ -644,6 +676,13 @@ int main() {
            "\"m128n128_plus_swapped\": %.4g}, \"cycles_per_mma_at_1965\": {\"m128n256\": %.1f, \"m128n128\": %.1f, \"m128n128_plus_swapped\": %.1f}}\n",
            timeout, s256, s128, s128s, 128.0 * 256 / 8 / (s256 / sms / 1.965e9), 128.0 * 128 / 8 / (s128 / sms / 1.965e9),
            128.0 * 128 / 8 / (s128s / sms / 1.965e9));
+    fflush(stdout);
+    // the same MMA stream with the other four warps (one per scheduler) busy with register-only arithmetic
+    double sd[5];
+    for (int side = 0; side < 5; ++side) sd[side] = run_shape<128, true>(tmA, tmB, sms, 4000, smem, side);
+    printf("{\"probe\": \"umma_under_side_work\", \"shape\": \"m128n128_plus_swapped\", \"raw_dist_per_s\": {\"none\": %.4g, "
+           "\"minmax_alu\": %.4g, \"imad_fma\": %.4g, \"both\": %.4g, \"global_loads\": %.4g}}\n",
+           sd[0], sd[1], sd[2], sd[3], sd[4]);
     fflush(stdout);
   }
   printf("{\"probe\": \"minmax_pipes\", \"lane_ops_per_clk_per_sm\": {\"vimnmx_u16x2\": %.1f, \"hmnmx2\": %.1f, \"mixed\": %.1f}}\n",

@@ -39,14 +39,21 @@ constexpr int kHalfBytes = kTile * 128;    // one K half of a tile: [128 rows][1
 constexpr int kTileBytes = 2 * kHalfBytes; // 32 KB
 constexpr int kGroup = 2;                  // desc1 tiles resident per pass over desc2
 constexpr int kBStages = 3;                // ring of desc2 tiles
-constexpr int kEpiWarps = 8;
+constexpr int kEpiWarps = 16;              // two groups of 8: group g takes the tile pairs of TMEM stage g
+constexpr int kEpiGroupWarps = 8;
 constexpr int kMmaWarps = 2;               // one MMA-issuing warp per TMEM stage (see the kernel's header)
-constexpr int kThreads = (kEpiWarps + 1 + kMmaWarps) * 32;
+constexpr int kCtlWarps = 4;                // hardware warps 0-3: TMA producer, two MMA issuers, one spare (keeps the epilogue's
+                                           // warp % 4 = TMEM lane quarter); the epilogue warps follow
+constexpr int kThreads = (kCtlWarps + kEpiWarps) * 32;
 constexpr uint32_t kShift = 20;            // 32-bit key = distance << 20 | index (as in match.cu)
 constexpr uint32_t kIdxMask = (1u << kShift) - 1;
 constexpr uint32_t kSent = 256u << kShift;
 constexpr int kMaxIndex = 1 << kShift;
 constexpr uint32_t kSpinLimit = 1u << 26;
+#ifndef VSLAM_MMA_HANDOFF
+#define VSLAM_MMA_HANDOFF 13
+#endif
+constexpr uint32_t kHandoff = VSLAM_MMA_HANDOFF;  // MMAs (of a pair's 16) an issuer has issued when the other may start its pair
 
 #ifdef VSLAM_MMA_PROFILE
 // cycle counters of CTA 0 (build with -DVSLAM_MMA_PROFILE; read with vslam_debug_mma_clocks):
@@ -80,6 +87,14 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 // still reached by everybody) and the job's result is reported as an error instead of hanging the GPU.
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, volatile int* fail) {
   uint32_t ok = 0;
+  asm volatile(  // the common case first: a phase that has completed already costs one non-blocking test
+      "{\n.reg .pred p;\n"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  if (ok) return true;
   for (uint32_t it = 0; it < kSpinLimit; ++it) {
     if ((it & 1023u) == 1023u && *fail) return false;
     asm volatile(
@@ -90,6 +105,16 @@ __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, volati
         : "r"(smem_u32(bar)), "r"(parity)
         : "memory");
     if (ok) return true;
+  }
+  *fail = 1;
+  atomicExch(&g_mma_timeout, 1);
+  return false;
+}
+// bounded spin on a shared-memory counter another thread of the CTA advances (same failure protocol as mbar_wait)
+__device__ __forceinline__ bool spin_until_ge(volatile uint32_t* ctr, uint32_t target, volatile int* fail) {
+  for (uint32_t it = 0; it < kSpinLimit; ++it) {
+    if ((int32_t)(*ctr - target) >= 0) return true;
+    if ((it & 1023u) == 1023u && *fail) return false;
   }
   *fail = 1;
   atomicExch(&g_mma_timeout, 1);
@@ -125,6 +150,11 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t da, uint64_t d
       "l"(da), "l"(db), "r"(kIdesc), "r"(accumulate), "r"(0u)
       : "memory");
 }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -142,6 +172,13 @@ __device__ __forceinline__ void tmem_ld64_pack16(uint32_t taddr, uint32_t (&v)[3
         "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
       : "r"(taddr)
       : "memory");
+}
+// 128 columns in one instruction (64 registers)
+__device__ __forceinline__ void tmem_ld128_pack16(uint32_t taddr, uint32_t (&v)[64]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x64.pack::16b.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32,%33,%34,%35,%36,%37,%38,%39,%40,%41,%42,%43,%44,%45,%46,%47,%48,%49,%50,%51,%52,%53,%54,%55,%56,%57,%58,%59,%60,%61,%62,%63}, [%64];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31]), "=r"(v[32]), "=r"(v[33]), "=r"(v[34]), "=r"(v[35]), "=r"(v[36]), "=r"(v[37]), "=r"(v[38]), "=r"(v[39]), "=r"(v[40]), "=r"(v[41]), "=r"(v[42]), "=r"(v[43]), "=r"(v[44]), "=r"(v[45]), "=r"(v[46]), "=r"(v[47]), "=r"(v[48]), "=r"(v[49]), "=r"(v[50]), "=r"(v[51]), "=r"(v[52]), "=r"(v[53]), "=r"(v[54]), "=r"(v[55]), "=r"(v[56]), "=r"(v[57]), "=r"(v[58]), "=r"(v[59]), "=r"(v[60]), "=r"(v[61]), "=r"(v[62]), "=r"(v[63])
+               : "r"(taddr)
+               : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -203,6 +240,7 @@ struct MmaSmem {
   int warp_sums[kEpiWarps];
   int running;
   int fail;
+  uint32_t progress[kMmaWarps];  // MMAs each issuer has issued so far (16 per tile pair): the issuers' turn-taking
 #ifdef VSLAM_MMA_PROFILE
   long long prof_clk[32];
   long long prof_trace[256][12];
@@ -256,17 +294,41 @@ __device__ __forceinline__ void fold_half(const uint32_t (&v)[32], int c0, int n
 // hamming << 7 | column.  Both of the row's loads are issued before the first one is consumed: a TMEM load behind a
 // running MMA takes several hundred cycles (measured: a warp that loaded chunk by chunk spent 2/3 of its time waiting).
 __device__ __forceinline__ void fold_tile(uint32_t taddr, int nvalid, int mul, uint64_t* t_empty, int lane, uint32_t& k1,
-                                          uint32_t& k2) {
+                                          uint32_t& k2, long long* loaded_clk = nullptr) {
   uint32_t p1a = 0xFFFFFFFFu, p2a = 0xFFFFFFFFu, p1b = 0xFFFFFFFFu, p2b = 0xFFFFFFFFu;
   uint32_t v0[32], v1[32];
+#if defined(VSLAM_MMA_EXP) && (VSLAM_MMA_EXP == 2 || VSLAM_MMA_EXP == 5)
+  for (int i = 0; i < 32; ++i) { v0[i] = (taddr + i) * (uint32_t)mul; v1[i] = v0[i] ^ (uint32_t)(lane << i); }
+#else
+#if defined(VSLAM_MMA_EXP) && VSLAM_MMA_EXP == 4
+  {
+    uint32_t w[64];
+    tmem_ld128_pack16(taddr, w);
+    tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < 32; ++i) { v0[i] = w[i]; v1[i] = w[32 + i]; }
+  }
+#else
   tmem_ld64_pack16(taddr, v0);
+#if defined(VSLAM_MMA_EXP) && VSLAM_MMA_EXP == 3
+  tmem_ld_wait();
+#endif
   if (nvalid > 64) tmem_ld64_pack16(taddr + 64, v1);  // warp-uniform
   tmem_ld_wait();
+#endif
+#endif
+#ifdef VSLAM_MMA_PROFILE
+  if (loaded_clk) *loaded_clk = clock64();
+#endif
   // the row now sits in registers: hand the TMEM stage back to the MMA issuer BEFORE the fold, so that the next product
   // into this stage runs under the min/max below instead of after them
   tc_fence_before();
   __syncwarp();
   if (lane == 0) mbar_arrive(t_empty);
+#if defined(VSLAM_MMA_EXP) && (VSLAM_MMA_EXP == 1 || VSLAM_MMA_EXP == 2)
+  k1 = v0[0] ^ v1[5]; k2 = v0[7] ^ v1[9];
+  return;
+#endif
   if (nvalid == kTile) {
     // the common case as ONE basic block: the scheduler can run the key IMADs (FMA pipe) of one half under the min/max
     // (ALU pipe) of the other
@@ -294,8 +356,10 @@ __global__ void __launch_bounds__(kThreads, 1)
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   MmaSmem& s = *reinterpret_cast<MmaSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint2* rs = reinterpret_cast<uint2*>(&s + 1);  // [max_n1] row statistics T(d1[i], desc2)
-  uint2* cs = rs + p.max_n1;                     // [max_n2] column statistics T(d2[j], desc1)
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint2* cs = rs + p.max_n1;                     // [2][max_n2] column statistics T(d2[j], desc1), one copy per epilogue
+                                                 // group (both groups meet every desc2 tile); merged at the end
+  // (broadcast: ptxas then knows the warp index -- and everything derived from it -- is uniform over the warp)
+  const int warp = __shfl_sync(0xFFFFFFFFu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
     mbar_init(&s.a_full, 1);
@@ -306,16 +370,17 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&s.t_full[i], 1);
-      mbar_init(&s.t_empty[i], kEpiWarps);
+      mbar_init(&s.t_empty[i], kEpiGroupWarps);
     }
     s.running = 0;
     s.fail = 0;
+    s.progress[0] = s.progress[1] = 0;
 #ifdef VSLAM_MMA_PROFILE
     for (int i = 0; i < 32; ++i) s.prof_clk[i] = 0;
 #endif
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == kEpiWarps + 1) {  // the MMA warp owns the TMEM allocation: 512 columns = two stages of (D1 | D2)
+  if (warp == 1) {  // the first MMA warp owns the TMEM allocation: 512 columns = two stages of (D1 | D2)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s.tmem_base)), "n"(512)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -328,7 +393,8 @@ __global__ void __launch_bounds__(kThreads, 1)
   // Pipeline positions, each role advancing the ones it uses: desc1 groups, desc2 tiles, tile pairs.  After a failed
   // wait (fail flag) every role still walks the same loops -- waits return at once, work is skipped -- so that the
   // barriers below are reached by everybody.
-  uint32_t a_it = 0, b_it = 0, t_it = 0, t_it1 = 0;  // (t_it1: the epilogue's count for stage 1)
+  uint32_t a_it = 0, b_it = 0, t_it = 0;
+  uint32_t seq0 = 0, seq1 = 0;  // MMA issuers: tile pairs of stage 0 / of stage 1 before the current (g0, b)
   volatile int* fail = &s.fail;
   for (int jb = blockIdx.x; jb < p.n_jobs; jb += gridDim.x) {
     const bool split = p.split_range > 0;
@@ -346,6 +412,8 @@ __global__ void __launch_bounds__(kThreads, 1)
       row1 = (int)((job.d1 - p.base1) >> 3);
       row2 = (int)((job.d2 - p.base2) >> 3);
     }
+    n1 = __shfl_sync(0xFFFFFFFFu, n1, 0);  // (the same in every lane already: the broadcast tells ptxas so)
+    n2 = __shfl_sync(0xFFFFFFFFu, n2, 0);
     const bool valid = n1 > 0 && n2 > 0 && n1 <= p.max_n1 && n2 <= p.max_n2;  // uniform over the CTA
     if (!valid) {
       if (threadIdx.x == 0 && !split) *job.count = (n1 > p.max_n1 || n2 > p.max_n2) ? -1 : 0;
@@ -353,7 +421,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
     const int nA = (n1 + kTile - 1) / kTile, nB = (n2 + kTile - 1) / kTile;
 
-    if (warp == kEpiWarps) {
+    if (warp == 0) {
       // ================= TMA producer =================
       if (lane == 0) {
         for (int g0 = 0; g0 < nA; g0 += kGroup) {
@@ -380,102 +448,142 @@ __global__ void __launch_bounds__(kThreads, 1)
         }
       }
       __syncwarp();
-    } else if (warp > kEpiWarps) {
-      // ================= MMA issuers: warp kEpiWarps + 1 + t multiplies the group's tile t into TMEM stage t =========
-      // A tcgen05.mma issue blocks while the tensor pipe's short queue is full, so one issuing thread serialises its own
-      // barrier waits (a try_wait costs it ~300 cycles, measured) with the MMAs: the pipe idled 55 % of the time.  With
-      // one issuer per stage, the waits of one run under the MMAs of the other.
-      const int t = warp - kEpiWarps - 1;
-      if (lane == 0) {
-        for (int g0 = 0; g0 < nA; g0 += kGroup) {
-          const int ng = min(kGroup, nA - g0);
-          bool ok;
-          { MMA_T0(); ok = mbar_wait(&s.a_full, a_it & 1, fail); MMA_ACC(1); }
-          for (int b = 0; b < nB; ++b) {
-            const int st = b_it % kBStages;
-            { MMA_T0(); ok = mbar_wait(&s.b_full[st], (b_it / kBStages) & 1, fail) && ok; MMA_ACC(2); }
-            if (t < ng) {
-              MMA_TRACE(2 * t_it + t, 4);
-              { MMA_T0(); if (t_it >= 1) ok = mbar_wait(&s.t_empty[t], (t_it - 1) & 1, fail) && ok; MMA_ACC(3); }
-              MMA_TRACE(2 * t_it + t, 5);
-              tc_fence_after();
-              MMA_T0();
-              MMA_TRACE(2 * t_it + t, 0);
+    } else if (warp == 3) {
+      // spare
+    } else if (warp < kCtlWarps) {
+      // ================= MMA issuers: warp 1 + t multiplies the group's desc1 tile t into TMEM stage t =================
+      // A tcgen05.mma issue blocks while the tensor pipe's short queue is full, and everything else this thread does per
+      // pair (barrier waits, commits, descriptor arithmetic) is one serial dependency chain of several hundred cycles:
+      // with one issuer per stage that chain runs under the other stage's MMAs.
+      // The issuers take turns in the order the pairs are consumed -- stage 1's pair (g0, b) behind stage 0's pair
+      // (g0, b), stage 0's next pair behind that -- handing over kHandoff MMAs into a pair, so that the next pair's first
+      // MMA queues up behind this pair's last.  The tensor pipe executes in issue order: the pairs complete one pair time
+      // apart and the two epilogue groups alternate.  (Without the turns both issuers start together, their MMAs
+      // interleave, both pairs complete together and both groups then load and fold at the same time while the pipe
+      // idles: measured 1775 cycles per pair.)
+      // The whole warp walks the loops with warp-uniform values (sizes and the TMEM base are broadcast, wait results
+      // voted), one elected lane issues the tcgen05 instructions: ptxas then builds the shared-memory descriptors in
+      // uniform registers (two UIADDs per MMA) instead of per-lane arithmetic followed by an ELECT / R2UR loop per operand
+      // (21 instructions per MMA, which is what bounded the issue rate once four epilogue warps share the scheduler).
+      const int t = warp - 1;
+      const bool leader = elect_one();
+      volatile uint32_t* mine = &s.progress[t];
+      volatile uint32_t* other = &s.progress[1 - t];
+      const uint32_t tm = __shfl_sync(0xFFFFFFFFu, tmem, 0) + t * 256;
+      for (int g0 = 0; g0 < nA; g0 += kGroup) {
+        const int ng = min(kGroup, nA - g0);
+        bool ok;
+        { MMA_T0(); ok = mbar_wait(&s.a_full, a_it & 1, fail); MMA_ACC(1); }
+        for (int b = 0; b < nB; ++b) {
+          const int st = b_it % kBStages;
+          { MMA_T0(); ok = mbar_wait(&s.b_full[st], (b_it / kBStages) & 1, fail) && ok; MMA_ACC(2); }
+          if (t < ng) {
+            if (leader) MMA_TRACE(2 * t_it + t, 4);
+            { MMA_T0(); if (t_it >= 1) ok = mbar_wait(&s.t_empty[t], (t_it - 1) & 1, fail) && ok; MMA_ACC(3); }
+            if (leader) MMA_TRACE(2 * t_it + t, 5);
+            if (t == 1 || seq1 > 0) ok = spin_until_ge(other, (t ? 16 * seq0 : 16 * (seq1 - 1)) + kHandoff, fail) && ok;
+            ok = __all_sync(0xFFFFFFFFu, ok);
+            tc_fence_after();
+            MMA_T0();
+            if (leader) MMA_TRACE(2 * t_it + t, 0);
+            // descriptor low words (address >> 4 | LBO): adding (offset >> 4) moves the start address (no carry: < 2^14)
+            const uint32_t a_lo = (uint32_t)umma_desc_sw128(smem_u32(s.a[t])), b_lo = (uint32_t)umma_desc_sw128(smem_u32(s.b[st]));
+            constexpr uint64_t kDescHi = (64ull << 32) | (1ull << 46) | (2ull << 61);
+            if (leader) {
               if (ok) {
-                const uint32_t sa = smem_u32(s.a[t]), sb = smem_u32(s.b[st]);
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {  // D1[i][j] = dot(desc1 row i, desc2 row j)
-                  const uint32_t off = (k >> 2) * kHalfBytes + (k & 3) * 32;
-                  umma_i8(tmem + t * 256, umma_desc_sw128(sa + off), umma_desc_sw128(sb + off), k > 0);
-                }
-#pragma unroll
-                for (int k = 0; k < 8; ++k) {  // D2[j][i]: the same operands with the roles swapped
-                  const uint32_t off = (k >> 2) * kHalfBytes + (k & 3) * 32;
-                  umma_i8(tmem + t * 256 + kTile, umma_desc_sw128(sb + off), umma_desc_sw128(sa + off), k > 0);
+                for (int k = 0; k < 16; ++k) {  // k < 8: D1[i][j] = dot(desc1 row i, desc2 row j); then D2[j][i], roles swapped
+                  const uint32_t off = (((k & 7) >> 2) * kHalfBytes + (k & 3) * 32) >> 4;
+                  const uint32_t r_lo = (k < 8 ? a_lo : b_lo) + off, c_lo = (k < 8 ? b_lo : a_lo) + off;
+                  umma_i8(tm + (k < 8 ? 0 : kTile), kDescHi | r_lo, kDescHi | c_lo, (k & 7) > 0);
+                  if (k == kHandoff - 1) *mine = 16 * t_it + kHandoff;
                 }
                 MMA_TRACE(2 * t_it + t, 6);
                 umma_commit(&s.t_full[t]);
+              } else {
+                *mine = 16 * t_it + kHandoff;
               }
-              MMA_ACC(4);
               MMA_TRACE(2 * t_it + t, 1);
-              ++t_it;  // uses of this warp's stage
             }
-            if (ok) umma_commit(&s.b_empty[st]);  // arrives when this warp's MMAs that read the desc2 tile are done
-            ++b_it;
+            MMA_ACC(4);
+            __syncwarp();
+            ++t_it;  // uses of this warp's stage
           }
-          if (ok) umma_commit(&s.a_empty);
-          ++a_it;
+          ++seq0;
+          if (ng == kGroup) ++seq1;
+          ok = __all_sync(0xFFFFFFFFu, ok);
+          if (ok && leader) umma_commit(&s.b_empty[st]);  // arrives when this warp's MMAs that read the desc2 tile are done
+          ++b_it;
         }
+        ok = __all_sync(0xFFFFFFFFu, ok);
+        if (ok && leader) umma_commit(&s.a_empty);
+        ++a_it;
       }
       __syncwarp();
     } else {
-      // ================= epilogue: warps 0-3 rows of D1, warps 4-7 rows of D2 =================
-      const int et = threadIdx.x;  // 0..255
+      // ================= epilogue: group g = warp / 8 takes the tile pairs of TMEM stage g (= desc1 tile g of the
+      // resident group); in a group warps 0-3 fold the rows of D1, warps 4-7 the rows of D2.  While one group folds a
+      // pair (ALU work), the other waits for / loads the next one: the TMEM load latency (several hundred cycles behind
+      // a running MMA) and the barrier waits hide behind the other group's min/max =================
+      const int ew = warp - kCtlWarps;           // 0..15
+      const int et = threadIdx.x - kCtlWarps * 32;  // 0..511
+      const int g = ew >> 3;
+      uint2* csg = cs + (size_t)g * p.max_n2;
       for (int i = et; i < n1; i += kEpiWarps * 32) rs[i] = make_uint2(kSent, kSent);
-      for (int j = et; j < n2; j += kEpiWarps * 32) cs[j] = make_uint2(kSent, kSent);
+      for (int j = et; j < n2; j += kEpiWarps * 32) cs[j] = cs[p.max_n2 + j] = make_uint2(kSent, kSent);
       epi_barrier();
-      const bool d2 = warp >= 4;
-      const int q = warp & 3;
+      const bool d2 = (ew & 4) != 0;
+      const int q = ew & 3;  // = warp % 4: the TMEM lane quarter this warp may read
       for (int g0 = 0; g0 < nA; g0 += kGroup) {
         const int ng = min(kGroup, nA - g0);
+        if (g >= ng) continue;  // an odd last group: stage 1 is not used
+        const int t = g;
         for (int b = 0; b < nB; ++b) {
-          for (int t = 0; t < ng; ++t) {
-            const int ts = t;  // stage = index of the desc1 tile in its group
-            const uint32_t use = t ? t_it1 : t_it;  // uses of the stage so far
-            bool ok;
-            { MMA_T0(); ok = mbar_wait(&s.t_full[ts], use & 1, fail); if (lane == 0 && q == 0) MMA_ACC(d2 ? 17 : 9); }
-            tc_fence_after();
-            MMA_T0();
-            if (lane == 0 && q == 0) MMA_TRACE(2 * use + t, d2 ? 11 : 10);
-            const int i0 = (g0 + t) * kTile, j0 = b * kTile;
-            // my row of the tile, the columns that exist, and where the row's statistics live
-            const int row = (d2 ? j0 : i0) + q * 32 + lane;
-            const int nrows = d2 ? n2 : n1;
-            const int nvalid = d2 ? min(kTile, n1 - i0) : min(kTile, n2 - j0);
-            const uint32_t cbase = d2 ? i0 : j0;
-            if (ok && q * 32 < (d2 ? n2 - j0 : n1 - i0)) {  // warp-uniform: the warp holds at least one real row
-              uint32_t k1, k2;
-              fold_tile(tmem + ((uint32_t)(q * 32) << 16) + ts * 256 + (d2 ? kTile : 0), nvalid, p.key_mul,
-                        &s.t_empty[ts], lane, k1, k2);
-              if (row < nrows) {
-                uint2* sp = (d2 ? cs : rs) + row;
-                uint2 acc = *sp;
-                const uint32_t w1 = widen_key(k1, cbase), w2 = widen_key(k2, cbase);
-                const uint32_t hi = max(acc.x, w1);
-                acc.x = min(acc.x, w1);
-                acc.y = min(min(acc.y, w2), hi);
-                *sp = acc;
-              }
-            } else {  // nothing to read from this stage: release it at once
-              tc_fence_before();
-              __syncwarp();
-              if (lane == 0) mbar_arrive(&s.t_empty[ts]);
+          const uint32_t use = t_it;  // uses of my stage so far
+          bool ok;
+          { MMA_T0(); ok = mbar_wait(&s.t_full[t], use & 1, fail); if (lane == 0 && q == 0 && g == 0) MMA_ACC(d2 ? 17 : 9); }
+          tc_fence_after();
+          MMA_T0();
+          if (lane == 0 && q == 0) MMA_TRACE(2 * use + t, d2 ? 11 : 10);
+          const int i0 = (g0 + t) * kTile, j0 = b * kTile;
+          // my row of the tile, the columns that exist, and where the row's statistics live
+          const int row = (d2 ? j0 : i0) + q * 32 + lane;
+          const int nrows = d2 ? n2 : n1;
+          const int nvalid = d2 ? min(kTile, n1 - i0) : min(kTile, n2 - j0);
+          const uint32_t cbase = d2 ? i0 : j0;
+          if (ok && q * 32 < (d2 ? n2 - j0 : n1 - i0)) {  // warp-uniform: the warp holds at least one real row
+            uint32_t k1, k2;
+#ifdef VSLAM_MMA_PROFILE
+            long long* lc = (lane == 0 && q == 0 && !d2 && 2 * use + t < 256) ? &s.prof_trace[2 * use + t][7] : nullptr;
+#else
+            long long* lc = nullptr;
+#endif
+            fold_tile(tmem + ((uint32_t)(q * 32) << 16) + t * 256 + (d2 ? kTile : 0), nvalid, p.key_mul, &s.t_empty[t], lane,
+                      k1, k2, lc);
+            if (row < nrows) {
+              uint2* sp = (d2 ? csg : rs) + row;
+              uint2 acc = *sp;
+              const uint32_t w1 = widen_key(k1, cbase), w2 = widen_key(k2, cbase);
+              const uint32_t hi = max(acc.x, w1);
+              acc.x = min(acc.x, w1);
+              acc.y = min(min(acc.y, w2), hi);
+              *sp = acc;
             }
-            if (lane == 0 && q == 0) MMA_ACC(d2 ? 18 : 10);
-            if (lane == 0 && q == 0) MMA_TRACE(2 * use + t, d2 ? 3 : 2);
-            if (t) ++t_it1; else ++t_it;
+          } else {  // nothing to read from this stage: release it at once
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s.t_empty[t]);
           }
+          if (lane == 0 && q == 0 && g == 0) MMA_ACC(d2 ? 18 : 10);
+          if (lane == 0 && q == 0) MMA_TRACE(2 * use + t, d2 ? 3 : 2);
+          ++t_it;
         }
+      }
+      epi_barrier();
+      // one list of column statistics out of the two groups' (the associative merge of the scan)
+      for (int j = et; j < n2; j += kEpiWarps * 32) {
+        const uint2 a = cs[j], c = cs[p.max_n2 + j];
+        cs[j] = make_uint2(min(a.x, c.x), min(max(a.x, c.x), min(a.y, c.y)));
       }
       epi_barrier();
       MMA_T0();
@@ -503,11 +611,11 @@ __global__ void __launch_bounds__(kThreads, 1)
             }
           }
           const unsigned bal = __ballot_sync(0xFFFFFFFFu, hit);
-          if (lane == 0) s.warp_sums[warp] = __popc(bal);
+          if (lane == 0) s.warp_sums[ew] = __popc(bal);
           epi_barrier();
           int off = s.running, tot = 0;
           for (int w = 0; w < kEpiWarps; ++w) {
-            if (w < warp) off += s.warp_sums[w];
+            if (w < ew) off += s.warp_sums[w];
             tot += s.warp_sums[w];
           }
           const int pos = off + __popc(bal & ((1u << lane) - 1));
@@ -539,7 +647,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     for (int i = threadIdx.x; i < 256 * 12; i += kThreads) g_mma_trace[i / 12][i % 12] = s.prof_trace[i / 12][i % 12];
   }
 #endif
-  if (warp == kEpiWarps + 1) {
+  if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512) : "memory");
   }
 }
@@ -581,7 +689,7 @@ int make_desc_tmap(vslam_ctx* ctx, const uint8_t* expanded, long long rows, CUte
 }  // namespace
 
 size_t match_mma_smem_bytes(int max_n1, int max_n2) {
-  return sizeof(MmaSmem) + 1024 + (size_t)(max_n1 + max_n2) * sizeof(uint2);
+  return sizeof(MmaSmem) + 1024 + (size_t)(max_n1 + 2 * max_n2) * sizeof(uint2);
 }
 
 bool match_mma_fits(int max_n1, int max_n2) {
