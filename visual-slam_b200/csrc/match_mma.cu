@@ -12,19 +12,23 @@
 //
 // Layout: descriptors are EXPANDED once per set to 256 signed bytes (expand_desc_kernel; the describe stage's output is
 // expanded right behind it, a keyframe store at append time).  One CTA owns one job (one matchDescriptors call) at a
-// time, persistent over the batch, warp-specialised:
-//   warp 8  (one lane)  TMA producer: 128-descriptor operand tiles ([2 K halves][128 rows][128 B], 128-byte swizzle,
+// time, persistent over the batch, warp-specialised (20 warps):
+//   warp 0  (one lane)  TMA producer: 128-descriptor operand tiles ([2 K halves][128 rows][128 B], 128-byte swizzle,
 //                       K-major) -- kGroup tiles of desc1 stay resident while the tiles of desc2 stream through a ring
-//   warps 9, 10 (one lane each)  MMA issuers, one per TMEM stage: per (desc1 tile, desc2 tile) TWO 128 x 128 products,
+//   warps 1, 2          MMA issuers, one per TMEM stage: per (desc1 tile, desc2 tile) TWO 128 x 128 products,
 //                       D1 = A * B^T (rows = desc1) and D2 = B * A^T (rows = desc2): both directions of the reference's
-//                       test become ROW statistics, so no reduction ever crosses threads.  Two issuers because a
-//                       tcgen05.mma issue blocks on the pipe's short queue: a single thread's barrier waits then sit
-//                       between its MMAs (measured: pipe 45 % busy); with two, one waits while the other multiplies
-//   warps 0-3 / 4-7     epilogue of D1 / D2: thread = one TMEM lane = one matrix row; tcgen05.ld 32 columns at a time;
-//                       two distances per register as 16-bit keys (hamming << 7 | column) built by two IMADs on the FMA
-//                       pipe, (min, second min) kept with VIMNMX.U16x2 (3 ALU instructions per TWO distances); per tile
-//                       the pair is widened to the 32-bit keys of match.cu and merged into the row's running
-//                       statistics in shared memory
+//                       test become ROW statistics, so no reduction ever crosses threads.  The whole warp walks the
+//                       loops with warp-uniform values and an elected lane issues, so the descriptors live in uniform
+//                       registers (3 instructions per MMA); the two issuers take turns, handing over 13 MMAs into a
+//                       pair, so that pairs complete one after the other
+//   warp 3              spare (keeps warp % 4 = TMEM lane quarter for the epilogue warps)
+//   warps 4-19          epilogue, two groups of eight: group g takes the pairs of TMEM stage g; in a group four warps
+//                       fold the rows of D1, four the rows of D2.  thread = one TMEM lane = one matrix row;
+//                       tcgen05.ld pack::16b hands out two adjacent columns per register (dot fits 16 bits); one xor +
+//                       one IMAD turn the register into two 16-bit keys (hamming << 7 | column); (min, second min)
+//                       kept with VIMNMX.U16x2 / VIMNMX3 (ALU pipe) and, for part of the max, IMAD pairs (FMA pipe);
+//                       per tile the pair is widened to the 32-bit keys of match.cu and merged into the row's
+//                       running statistics in shared memory
 // Two TMEM stages (2 x 256 columns = the whole TMEM) let the MMA of the next tile pair run under the epilogue of the
 // current one.  The ratio test, the mutual check and the ordered compaction run in the same CTA on the epilogue warps
 // while the producer / MMA warps already work on the next job.
@@ -173,13 +177,6 @@ __device__ __forceinline__ void tmem_ld64_pack16(uint32_t taddr, uint32_t (&v)[3
       : "r"(taddr)
       : "memory");
 }
-// 128 columns in one instruction (64 registers)
-__device__ __forceinline__ void tmem_ld128_pack16(uint32_t taddr, uint32_t (&v)[64]) {
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x64.pack::16b.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32,%33,%34,%35,%36,%37,%38,%39,%40,%41,%42,%43,%44,%45,%46,%47,%48,%49,%50,%51,%52,%53,%54,%55,%56,%57,%58,%59,%60,%61,%62,%63}, [%64];"
-               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31]), "=r"(v[32]), "=r"(v[33]), "=r"(v[34]), "=r"(v[35]), "=r"(v[36]), "=r"(v[37]), "=r"(v[38]), "=r"(v[39]), "=r"(v[40]), "=r"(v[41]), "=r"(v[42]), "=r"(v[43]), "=r"(v[44]), "=r"(v[45]), "=r"(v[46]), "=r"(v[47]), "=r"(v[48]), "=r"(v[49]), "=r"(v[50]), "=r"(v[51]), "=r"(v[52]), "=r"(v[53]), "=r"(v[54]), "=r"(v[55]), "=r"(v[56]), "=r"(v[57]), "=r"(v[58]), "=r"(v[59]), "=r"(v[60]), "=r"(v[61]), "=r"(v[62]), "=r"(v[63])
-               : "r"(taddr)
-               : "memory");
-}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -221,6 +218,7 @@ struct MmaParams {
   // -64: the multiplier that turns a register of two 16-bit accumulators into a packed key pair (fold_half).  A kernel
   // parameter rather than a literal: as a literal ptxas re-materialises it with MOVs between the IMADs
   int key_mul;
+  int key_one, key_neg1;  // 1 and -1, for the same reason (fold2)
   // Column-split mode for ONE large job (split_range > 0; BASELINE config 4: a query set against a large map): CTA s
   // takes all split_n1 rows of the first array against columns [s * split_range, + split_range) of the second; its
   // row statistics are partial (rowpart[s][i], column indices relative to the range), its column statistics complete
@@ -253,14 +251,29 @@ __device__ __forceinline__ bool passes(uint32_t m1, uint32_t m2, int threshold, 
   return !((double)(int)m2 < __dmul_rn((double)(int)m1, ratio));
 }
 
-// Folds two packed keys into a (min, second min) pair of packed lists: 5 min/max per TWO registers (= four distances):
+// Folds two packed keys into a (min, second min) pair of packed lists:
 //   lo = min(x, y), hi = max(x, y);  m1' = min(m1, lo);  m2' = min3(m2, max(m1, lo), hi)
-__device__ __forceinline__ void fold2(uint32_t x, uint32_t y, uint32_t& m1, uint32_t& m2) {
-  const uint32_t lo = __vminu2(x, y), hi = __vmaxu2(x, y);
-  const uint32_t t = __vmaxu2(m1, lo);
-  m1 = __vminu2(m1, lo);
+// Five min/max on the ALU pipe, which is what bounds the epilogue (16-bit min/max issue every other cycle, like all ALU
+// work).  The FMA pipe idles next to it, so kFma of the two plain max are computed there instead, per 16-bit half
+//   max(a, b) = (a - min(a, b)) + b        (a - min >= 0: no borrow between the halves; the sum is the max: no carry)
+// as two IMADs with multipliers -1 and 1 that are kernel parameters (as literals ptxas folds them back into IADD3s on
+// the ALU pipe).
+template <int kFma>
+__device__ __forceinline__ void fold2(uint32_t x, uint32_t y, uint32_t& m1, uint32_t& m2, int one, int neg1) {
+  const uint32_t lo = __vminu2(x, y);
+  const uint32_t hi = kFma >= 1 ? (uint32_t)(((int)lo * neg1 + (int)x) * one + (int)y) : __vmaxu2(x, y);
+  const uint32_t n1 = __vminu2(m1, lo);
+  const uint32_t t = kFma >= 2 ? (uint32_t)(((int)n1 * neg1 + (int)m1) * one + (int)lo) : __vmaxu2(m1, lo);
+  m1 = n1;
   m2 = __vimin3_u16x2(m2, t, hi);
 }
+
+#ifndef VSLAM_FOLD_FMA_A
+#define VSLAM_FOLD_FMA_A 2  // max on the FMA pipe in the even / odd fold2 of a chain (0, 1 or 2 each)
+#endif
+#ifndef VSLAM_FOLD_FMA_B
+#define VSLAM_FOLD_FMA_B 1
+#endif
 
 // One 64-column half of a row (32 registers of two 16-bit accumulators each) into two independent (min, second min)
 // chains of packed 16-bit keys (registers 0-15 -> chain a, 16-31 -> chain b: the serial min/max dependency is what
@@ -272,8 +285,8 @@ __device__ __forceinline__ void fold2(uint32_t x, uint32_t y, uint32_t& m1, uint
 // with both parentheses in [0, 65536): no borrow crosses the halves.  (Without the xor a negative low half would
 // borrow 64 from the high one.)
 template <bool kMasked>
-__device__ __forceinline__ void fold_half(const uint32_t (&v)[32], int c0, int nv, int mul, uint32_t& p1a, uint32_t& p2a,
-                                          uint32_t& p1b, uint32_t& p2b) {
+__device__ __forceinline__ void fold_half(const uint32_t (&v)[32], int c0, int nv, int mul, int one, int neg1, uint32_t& p1a,
+                                          uint32_t& p2a, uint32_t& p1b, uint32_t& p2b) {
   const uint32_t cb = (uint32_t)c0 * 0x00010001u;
   uint32_t key[32];
 #pragma unroll
@@ -285,38 +298,27 @@ __device__ __forceinline__ void fold_half(const uint32_t (&v)[32], int c0, int n
     key[j] = k;
   }
 #pragma unroll
-  for (int i = 0; i < 16; i += 2) fold2(key[i], key[i + 1], p1a, p2a);
+  for (int i = 0; i < 16; i += 4) {
+    fold2<VSLAM_FOLD_FMA_A>(key[i], key[i + 1], p1a, p2a, one, neg1);
+    fold2<VSLAM_FOLD_FMA_B>(key[i + 2], key[i + 3], p1a, p2a, one, neg1);
+  }
 #pragma unroll
-  for (int i = 16; i < 32; i += 2) fold2(key[i], key[i + 1], p1b, p2b);
+  for (int i = 16; i < 32; i += 4) {
+    fold2<VSLAM_FOLD_FMA_A>(key[i], key[i + 1], p1b, p2b, one, neg1);
+    fold2<VSLAM_FOLD_FMA_B>(key[i + 2], key[i + 3], p1b, p2b, one, neg1);
+  }
 }
 
 // (min, second min) of one matrix row over the nvalid first columns of a 128-column TMEM tile, as 16-bit keys
 // hamming << 7 | column.  Both of the row's loads are issued before the first one is consumed: a TMEM load behind a
 // running MMA takes several hundred cycles (measured: a warp that loaded chunk by chunk spent 2/3 of its time waiting).
-__device__ __forceinline__ void fold_tile(uint32_t taddr, int nvalid, int mul, uint64_t* t_empty, int lane, uint32_t& k1,
-                                          uint32_t& k2, long long* loaded_clk = nullptr) {
+__device__ __forceinline__ void fold_tile(uint32_t taddr, int nvalid, int mul, int one, int neg1, uint64_t* t_empty, int lane,
+                                          uint32_t& k1, uint32_t& k2, long long* loaded_clk = nullptr) {
   uint32_t p1a = 0xFFFFFFFFu, p2a = 0xFFFFFFFFu, p1b = 0xFFFFFFFFu, p2b = 0xFFFFFFFFu;
   uint32_t v0[32], v1[32];
-#if defined(VSLAM_MMA_EXP) && (VSLAM_MMA_EXP == 2 || VSLAM_MMA_EXP == 5)
-  for (int i = 0; i < 32; ++i) { v0[i] = (taddr + i) * (uint32_t)mul; v1[i] = v0[i] ^ (uint32_t)(lane << i); }
-#else
-#if defined(VSLAM_MMA_EXP) && VSLAM_MMA_EXP == 4
-  {
-    uint32_t w[64];
-    tmem_ld128_pack16(taddr, w);
-    tmem_ld_wait();
-#pragma unroll
-    for (int i = 0; i < 32; ++i) { v0[i] = w[i]; v1[i] = w[32 + i]; }
-  }
-#else
   tmem_ld64_pack16(taddr, v0);
-#if defined(VSLAM_MMA_EXP) && VSLAM_MMA_EXP == 3
-  tmem_ld_wait();
-#endif
   if (nvalid > 64) tmem_ld64_pack16(taddr + 64, v1);  // warp-uniform
   tmem_ld_wait();
-#endif
-#endif
 #ifdef VSLAM_MMA_PROFILE
   if (loaded_clk) *loaded_clk = clock64();
 #endif
@@ -325,19 +327,15 @@ __device__ __forceinline__ void fold_tile(uint32_t taddr, int nvalid, int mul, u
   tc_fence_before();
   __syncwarp();
   if (lane == 0) mbar_arrive(t_empty);
-#if defined(VSLAM_MMA_EXP) && (VSLAM_MMA_EXP == 1 || VSLAM_MMA_EXP == 2)
-  k1 = v0[0] ^ v1[5]; k2 = v0[7] ^ v1[9];
-  return;
-#endif
   if (nvalid == kTile) {
     // the common case as ONE basic block: the scheduler can run the key IMADs (FMA pipe) of one half under the min/max
     // (ALU pipe) of the other
-    fold_half<false>(v0, 0, 64, mul, p1a, p2a, p1b, p2b);
-    fold_half<false>(v1, 64, 64, mul, p1a, p2a, p1b, p2b);
+    fold_half<false>(v0, 0, 64, mul, one, neg1, p1a, p2a, p1b, p2b);
+    fold_half<false>(v1, 64, 64, mul, one, neg1, p1a, p2a, p1b, p2b);
   } else {
-    if (nvalid >= 64) fold_half<false>(v0, 0, 64, mul, p1a, p2a, p1b, p2b);
-    else fold_half<true>(v0, 0, nvalid, mul, p1a, p2a, p1b, p2b);
-    if (nvalid > 64) fold_half<true>(v1, 64, nvalid - 64, mul, p1a, p2a, p1b, p2b);
+    if (nvalid >= 64) fold_half<false>(v0, 0, 64, mul, one, neg1, p1a, p2a, p1b, p2b);
+    else fold_half<true>(v0, 0, nvalid, mul, one, neg1, p1a, p2a, p1b, p2b);
+    if (nvalid > 64) fold_half<true>(v1, 64, nvalid - 64, mul, one, neg1, p1a, p2a, p1b, p2b);
   }
   // merge the two chains, then the even-column list (low halves) with the odd-column list (high halves)
   const uint32_t p1 = __vminu2(p1a, p1b), p2 = __vminu2(__vmaxu2(p1a, p1b), __vminu2(p2a, p2b));
@@ -479,16 +477,17 @@ __global__ void __launch_bounds__(kThreads, 1)
           { MMA_T0(); ok = mbar_wait(&s.b_full[st], (b_it / kBStages) & 1, fail) && ok; MMA_ACC(2); }
           if (t < ng) {
             if (leader) MMA_TRACE(2 * t_it + t, 4);
-            { MMA_T0(); if (t_it >= 1) ok = mbar_wait(&s.t_empty[t], (t_it - 1) & 1, fail) && ok; MMA_ACC(3); }
-            if (leader) MMA_TRACE(2 * t_it + t, 5);
-            if (t == 1 || seq1 > 0) ok = spin_until_ge(other, (t ? 16 * seq0 : 16 * (seq1 - 1)) + kHandoff, fail) && ok;
-            ok = __all_sync(0xFFFFFFFFu, ok);
-            tc_fence_after();
-            MMA_T0();
-            if (leader) MMA_TRACE(2 * t_it + t, 0);
             // descriptor low words (address >> 4 | LBO): adding (offset >> 4) moves the start address (no carry: < 2^14)
             const uint32_t a_lo = (uint32_t)umma_desc_sw128(smem_u32(s.a[t])), b_lo = (uint32_t)umma_desc_sw128(smem_u32(s.b[st]));
             constexpr uint64_t kDescHi = (64ull << 32) | (1ull << 46) | (2ull << 61);
+            // my turn (true long before it is needed once the pipeline runs), then the stage: what follows the stage's
+            // release is on the critical path of the pair (release -> first MMA), so nothing else is left for there
+            if (t == 1 || seq1 > 0) ok = spin_until_ge(other, (t ? 16 * seq0 : 16 * (seq1 - 1)) + kHandoff, fail) && ok;
+            if (leader) MMA_TRACE(2 * t_it + t, 5);
+            { MMA_T0(); if (t_it >= 1) ok = mbar_wait(&s.t_empty[t], (t_it - 1) & 1, fail) && ok; MMA_ACC(3); }
+            tc_fence_after();
+            MMA_T0();
+            if (leader) MMA_TRACE(2 * t_it + t, 0);
             if (leader) {
               if (ok) {
 #pragma unroll
@@ -558,8 +557,8 @@ __global__ void __launch_bounds__(kThreads, 1)
 #else
             long long* lc = nullptr;
 #endif
-            fold_tile(tmem + ((uint32_t)(q * 32) << 16) + t * 256 + (d2 ? kTile : 0), nvalid, p.key_mul, &s.t_empty[t], lane,
-                      k1, k2, lc);
+            fold_tile(tmem + ((uint32_t)(q * 32) << 16) + t * 256 + (d2 ? kTile : 0), nvalid, p.key_mul, p.key_one, p.key_neg1,
+                      &s.t_empty[t], lane, k1, k2, lc);
             if (row < nrows) {
               uint2* sp = (d2 ? csg : rs) + row;
               uint2 acc = *sp;
@@ -727,7 +726,7 @@ int launch_match_jobs_mma(vslam_ctx* ctx, const MatchJob* jobs_dev, int n_jobs, 
   p.cap = cap;
   p.max_n1 = max_n1;
   p.max_n2 = max_n2;
-  p.key_mul = -64;
+  p.key_mul = -64; p.key_one = 1; p.key_neg1 = -1;
   p.split_range = 0; p.split_n1 = p.split_n2 = 0;
   p.rowpart = p.colstat = nullptr;
   const size_t smem = match_mma_smem_bytes(max_n1, max_n2);
@@ -773,7 +772,7 @@ int launch_match_split_mma(vslam_ctx* ctx, const uint8_t* x1, int n1, const uint
   p.n_jobs = nsplit;
   p.max_n1 = n1;
   p.max_n2 = range;
-  p.key_mul = -64;
+  p.key_mul = -64; p.key_one = 1; p.key_neg1 = -1;
   p.split_range = range; p.split_n1 = n1; p.split_n2 = n2;
   p.rowpart = rowpart;
   p.colstat = colstat;
