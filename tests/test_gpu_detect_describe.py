@@ -7,7 +7,8 @@ import pytest
 
 import visnav_b200
 from visnav_b200 import workloads as wl
-from visnav_b200.keypoints import KeypointsData, VSLAM_OPT_FP_CONTRACT, VSLAM_OPT_RESPONSE_BAND
+from visnav_b200.keypoints import (KeypointsData, VSLAM_OPT_FP_CONTRACT, VSLAM_OPT_RESPONSE_BAND,
+                                   VSLAM_OPT_RESPONSE_MULTI)
 
 pytestmark = pytest.mark.gpu
 
@@ -106,6 +107,32 @@ def test_detect_ordered_equal(ctx, oracle_port, w, h, nf):
     got = ctx.detect(img, nf)
     want = oracle_port.detect(img, nf)
     assert got.shape == want.shape and np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("w,h", [(752, 480), (640, 200), (296, 130), (130, 70), (121, 97), (177, 64)])
+def test_narrow_last_strip_shared_by_images(ctx, oracle_port, w, h):
+    """The narrow last column strip of two or three images in one warp (response_multi_kernel; 752 = 6 x 120 + 32 gives
+    three groups of ten lanes, 640 two of twelve, 296 two of sixteen, 130 / 121 three of five / three; 177 has a strip of
+    57 columns and keeps one warp per strip): corners identical to one warp per strip for every image count modulo the
+    group count, in row bands and in full-height boxes, and equal to the oracle's."""
+    imgs = np.stack([_image(w, h, 4000 + 13 * k + w) for k in range(7)])
+    want = [oracle_port.detect(im, 400) for im in imgs]
+    for band in (0, 65535):
+        ctx.set_option(VSLAM_OPT_RESPONSE_BAND, band)
+        try:
+            for count in (2, 3, 4, 7):
+                ctx.set_option(VSLAM_OPT_RESPONSE_MULTI, 1)
+                a_xy, _, a_desc, a_n = ctx.detect_describe_batch(imgs[:count], 400)
+                ctx.set_option(VSLAM_OPT_RESPONSE_MULTI, 0)
+                b_xy, _, b_desc, b_n = ctx.detect_describe_batch(imgs[:count], 400)
+                assert np.array_equal(a_n, b_n), (band, count)
+                for k in range(count):
+                    n = a_n[k]
+                    assert np.array_equal(a_xy[k, :n], b_xy[k, :n]) and np.array_equal(a_desc[k, :n], b_desc[k, :n])
+                    assert n == len(want[k]) and np.array_equal(a_xy[k, :n], want[k]), (band, count, k)
+        finally:
+            ctx.set_option(VSLAM_OPT_RESPONSE_MULTI, 1)
+            ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 0)
 
 
 def test_response_ring_bottom_alignments(ctx, oracle_port):

@@ -136,6 +136,7 @@ int vslam_set_option(vslam_ctx* ctx, int option, int value) {
   else if (option == VSLAM_OPT_MATCH_SPLIT_SMALL) ctx->match_split_small = value != 0;
   else if (option == VSLAM_OPT_MATCH_MMA && value >= 0 && value <= 2) ctx->match_mma = value;
   else if (option == VSLAM_OPT_GRAPH) ctx->use_graph = value != 0;
+  else if (option == VSLAM_OPT_RESPONSE_MULTI) ctx->resp_multi = value != 0;
   else if (option == VSLAM_OPT_RESPONSE_BAND && (value == 0 || (value >= 8 && value <= 65535))) ctx->resp_band = value;
   else if (option == VSLAM_OPT_BATCH_CHUNK && value >= 1 && value <= 4096) ctx->batch_chunk = value;
   else if (option == VSLAM_OPT_BATCH_DEPTH && value >= 1 && value <= vslam_ctx::kMaxBatchDepth) ctx->batch_depth = value;
@@ -671,7 +672,8 @@ int vslam_stereo_plan_run(vslam_stereo_plan* plan, int count, int num_features, 
                                         (unsigned long long)(unsigned)match_threshold, rbits, kbits,
                                         (unsigned long long)ctx->fp_contract, (unsigned long long)ctx->match_csa,
                                         (unsigned long long)ctx->harris_on, (unsigned long long)ctx->resp_band,
-                                        (unsigned long long)ctx->match_split_small, (unsigned long long)ctx->match_mma};
+                                        (unsigned long long)ctx->match_split_small, (unsigned long long)ctx->match_mma,
+                                        (unsigned long long)ctx->resp_multi};
     for (unsigned long long v : parts) key = (key ^ v) * 1099511628211ull;
     if (plan->graph_state == 2 && plan->graph_key == key) {
       VS_CUDA(ctx, cudaGraphLaunch(plan->graph_exec, plan->stream));

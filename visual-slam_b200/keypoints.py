@@ -53,6 +53,7 @@ VSLAM_OPT_MATCH_SPLIT_SMALL = 5
 VSLAM_OPT_RESPONSE_BAND = 6
 VSLAM_OPT_MATCH_MMA = 7
 VSLAM_OPT_GRAPH = 8
+VSLAM_OPT_RESPONSE_MULTI = 9
 
 
 class VslamError(RuntimeError):
