@@ -35,9 +35,9 @@ out = {"pairs": n, "jobs_of_cta0": jobs0, "match_ms": float(ms[4]), "match_clk_a
        "mean_kp": float(res["n_kp"].mean())}
 print(json.dumps(out))
 if prof and hasattr(L, "vslam_debug_mma_trace"):
-    tr = (C.c_longlong * 3072)()
+    tr = (C.c_longlong * 1536)()
     assert L.vslam_debug_mma_trace(tr) == 0
-    t = np.array(list(tr), np.int64).reshape(256, 12)
+    t = np.array(list(tr), np.int64).reshape(128, 12)
     t0 = t[0, 0]
     print("pair | pre_b_full loop_top  t_empty_ok  issue_start  issued  issued_d2 committed | w0_full w0_loaded w0_done w4_done   (cycles since the first issue)")
     for k in list(range(0, 30)) + list(range(118, 126)):

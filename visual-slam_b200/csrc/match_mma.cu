@@ -54,8 +54,16 @@ constexpr uint32_t kIdxMask = (1u << kShift) - 1;
 constexpr uint32_t kSent = 256u << kShift;
 constexpr int kMaxIndex = 1 << kShift;
 constexpr uint32_t kSpinLimit = 1u << 26;
+// 1: a ninth K = 32 step multiplies a constant tile by itself (sixteen bytes of 4 per row: 16 * 4 * 4 = 256), so the
+// accumulators are dot + 256 = 512 - 2 hamming >= 0 and the epilogue's packed 16-bit arithmetic needs no sign handling
+// (one ALU instruction less per two distances, on the pipe that bounds the epilogue) for 12.5 % more tensor work,
+// which has the slack.  0: eight steps, signed accumulators, one xor per register.
+#ifndef VSLAM_MMA_BIAS
+#define VSLAM_MMA_BIAS 1
+#endif
+constexpr int kMmasPerPair = VSLAM_MMA_BIAS ? 18 : 16;
 #ifndef VSLAM_MMA_HANDOFF
-#define VSLAM_MMA_HANDOFF 13
+#define VSLAM_MMA_HANDOFF (VSLAM_MMA_BIAS ? 15 : 13)
 #endif
 constexpr uint32_t kHandoff = VSLAM_MMA_HANDOFF;  // MMAs (of a pair's 16) an issuer has issued when the other may start its pair
 
@@ -66,8 +74,8 @@ constexpr uint32_t kHandoff = VSLAM_MMA_HANDOFF;  // MMAs (of a pair's 16) an is
 __device__ long long g_mma_clk[32];
 // per tile pair of CTA 0 (first 256): clock64 at 0 MMA issue start, 1 issue end (commit), 2 + w: epilogue warp w done
 // (arrived on t_empty), 10: warp 0 saw t_full, 11: warp 4 saw t_full
-__device__ long long g_mma_trace[256][12];
-#define MMA_TRACE(pair, k) do { if ((pair) < 256) s.prof_trace[pair][k] = clock64(); } while (0)
+__device__ long long g_mma_trace[128][12];
+#define MMA_TRACE(pair, k) do { if ((pair) < 128) s.prof_trace[pair][k] = clock64(); } while (0)
 // the counters live in shared memory while the kernel runs (a global read-modify-write per event would put ~700
 // cycles on the MMA thread's critical path -- measured) and are dumped by CTA 0 at the end
 #if VSLAM_MMA_PROFILE >= 2  // trace only: the accumulating counters cost a shared-memory read-modify-write per event
@@ -231,6 +239,9 @@ struct MmaParams {
 struct MmaSmem {
   uint8_t a[kGroup][kTileBytes];
   uint8_t b[kBStages][kTileBytes];
+#if VSLAM_MMA_BIAS
+  uint8_t bias[kHalfBytes];  // [128 rows][128 B], 128-byte swizzle: logical bytes 0-15 of every row = 4, 16-31 = 0
+#endif
   uint64_t a_full, a_empty;
   uint64_t b_full[kBStages], b_empty[kBStages];
   uint64_t t_full[2], t_empty[2];
@@ -241,7 +252,7 @@ struct MmaSmem {
   uint32_t progress[kMmaWarps];  // MMAs each issuer has issued so far (16 per tile pair): the issuers' turn-taking
 #ifdef VSLAM_MMA_PROFILE
   long long prof_clk[32];
-  long long prof_trace[256][12];
+  long long prof_trace[128][12];
 #endif
 };
 
@@ -269,7 +280,7 @@ __device__ __forceinline__ void fold2(uint32_t x, uint32_t y, uint32_t& m1, uint
 }
 
 #ifndef VSLAM_FOLD_FMA_A
-#define VSLAM_FOLD_FMA_A 2  // max on the FMA pipe in the even / odd fold2 of a chain (0, 1 or 2 each)
+#define VSLAM_FOLD_FMA_A (VSLAM_MMA_BIAS ? 1 : 2)  // max on the FMA pipe in the even / odd fold2 of a chain (0, 1 or 2 each)
 #endif
 #ifndef VSLAM_FOLD_FMA_B
 #define VSLAM_FOLD_FMA_B 1
@@ -291,9 +302,16 @@ __device__ __forceinline__ void fold_half(const uint32_t (&v)[32], int c0, int n
   uint32_t key[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) {
+#if VSLAM_MMA_BIAS
+    // accumulators are 512 - 2 hamming in [0, 512]: key = (512 - acc) * 64 + column per half, nothing crosses the halves
+    const uint32_t half = 64u * 512u + (uint32_t)(2 * j);
+    const uint32_t cst = half + ((half + 1u) << 16);
+    uint32_t k = (uint32_t)((int)v[j] * mul + (int)(cst + cb));
+#else
     const uint32_t half = 64u * (32768u + 256u) + (uint32_t)(2 * j);
     const uint32_t cst = half + ((half + 1u) << 16);
     uint32_t k = (uint32_t)((int)(v[j] ^ 0x80008000u) * mul + (int)(cst + cb));
+#endif
     if (kMasked) k |= (2 * j >= nv ? 0x0000FFFFu : 0u) | (2 * j + 1 >= nv ? 0xFFFF0000u : 0u);  // nv = valid columns of the half
     key[j] = k;
   }
@@ -378,6 +396,16 @@ __global__ void __launch_bounds__(kThreads, 1)
 #endif
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+#if VSLAM_MMA_BIAS
+  // the constant operand of the bias step, written as TMA would have (16-byte chunk c of row r sits at chunk c ^ (r & 7)),
+  // then made visible to the tensor core's (async proxy) reads
+  for (int i = threadIdx.x; i < kHalfBytes / 16; i += kThreads) {
+    const int r = i >> 3, pc = i & 7;
+    const uint32_t v = ((pc ^ (r & 7)) == 0) ? 0x04040404u : 0u;
+    reinterpret_cast<uint4*>(s.bias)[i] = make_uint4(v, v, v, v);
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
   if (warp == 1) {  // the first MMA warp owns the TMEM allocation: 512 columns = two stages of (D1 | D2)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s.tmem_base)), "n"(512)
                  : "memory");
@@ -480,9 +508,14 @@ __global__ void __launch_bounds__(kThreads, 1)
             // descriptor low words (address >> 4 | LBO): adding (offset >> 4) moves the start address (no carry: < 2^14)
             const uint32_t a_lo = (uint32_t)umma_desc_sw128(smem_u32(s.a[t])), b_lo = (uint32_t)umma_desc_sw128(smem_u32(s.b[st]));
             constexpr uint64_t kDescHi = (64ull << 32) | (1ull << 46) | (2ull << 61);
+#if VSLAM_MMA_BIAS
+            const uint32_t bias_lo = (uint32_t)umma_desc_sw128(smem_u32(s.bias));
+#else
+            const uint32_t bias_lo = 0;
+#endif
             // my turn (true long before it is needed once the pipeline runs), then the stage: what follows the stage's
             // release is on the critical path of the pair (release -> first MMA), so nothing else is left for there
-            if (t == 1 || seq1 > 0) ok = spin_until_ge(other, (t ? 16 * seq0 : 16 * (seq1 - 1)) + kHandoff, fail) && ok;
+            if (t == 1 || seq1 > 0) ok = spin_until_ge(other, (t ? kMmasPerPair * seq0 : kMmasPerPair * (seq1 - 1)) + kHandoff, fail) && ok;
             if (leader) MMA_TRACE(2 * t_it + t, 5);
             { MMA_T0(); if (t_it >= 1) ok = mbar_wait(&s.t_empty[t], (t_it - 1) & 1, fail) && ok; MMA_ACC(3); }
             tc_fence_after();
@@ -491,16 +524,26 @@ __global__ void __launch_bounds__(kThreads, 1)
             if (leader) {
               if (ok) {
 #pragma unroll
-                for (int k = 0; k < 16; ++k) {  // k < 8: D1[i][j] = dot(desc1 row i, desc2 row j); then D2[j][i], roles swapped
-                  const uint32_t off = (((k & 7) >> 2) * kHalfBytes + (k & 3) * 32) >> 4;
-                  const uint32_t r_lo = (k < 8 ? a_lo : b_lo) + off, c_lo = (k < 8 ? b_lo : a_lo) + off;
-                  umma_i8(tm + (k < 8 ? 0 : kTile), kDescHi | r_lo, kDescHi | c_lo, (k & 7) > 0);
-                  if (k == kHandoff - 1) *mine = 16 * t_it + kHandoff;
+                for (int k = 0; k < kMmasPerPair; ++k) {
+                  // first half: D1[i][j] = dot(desc1 row i, desc2 row j); second half: D2[j][i], the roles swapped; the
+                  // last step of a half (VSLAM_MMA_BIAS) adds 256 to every accumulator
+                  constexpr int kHalf = kMmasPerPair / 2;
+                  const int kk = k % kHalf;
+                  const bool second = k >= kHalf;
+                  const uint32_t d = tm + (second ? kTile : 0);
+                  if (kk < 8) {
+                    const uint32_t off = ((kk >> 2) * kHalfBytes + (kk & 3) * 32) >> 4;
+                    const uint32_t r_lo = (second ? b_lo : a_lo) + off, c_lo = (second ? a_lo : b_lo) + off;
+                    umma_i8(d, kDescHi | r_lo, kDescHi | c_lo, kk > 0);
+                  } else {
+                    umma_i8(d, kDescHi | bias_lo, kDescHi | bias_lo, 1);
+                  }
+                  if (k == (int)kHandoff - 1) *mine = kMmasPerPair * t_it + kHandoff;
                 }
                 MMA_TRACE(2 * t_it + t, 6);
                 umma_commit(&s.t_full[t]);
               } else {
-                *mine = 16 * t_it + kHandoff;
+                *mine = kMmasPerPair * t_it + kHandoff;
               }
               MMA_TRACE(2 * t_it + t, 1);
             }
@@ -553,7 +596,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           if (ok && q * 32 < (d2 ? n2 - j0 : n1 - i0)) {  // warp-uniform: the warp holds at least one real row
             uint32_t k1, k2;
 #ifdef VSLAM_MMA_PROFILE
-            long long* lc = (lane == 0 && q == 0 && !d2 && 2 * use + t < 256) ? &s.prof_trace[2 * use + t][7] : nullptr;
+            long long* lc = (lane == 0 && q == 0 && !d2 && 2 * use + t < 128) ? &s.prof_trace[2 * use + t][7] : nullptr;
 #else
             long long* lc = nullptr;
 #endif
@@ -643,7 +686,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 #ifdef VSLAM_MMA_PROFILE
   if (blockIdx.x == 0) {
     for (int i = threadIdx.x; i < 32; i += kThreads) g_mma_clk[i] += s.prof_clk[i];
-    for (int i = threadIdx.x; i < 256 * 12; i += kThreads) g_mma_trace[i / 12][i % 12] = s.prof_trace[i / 12][i % 12];
+    for (int i = threadIdx.x; i < 128 * 12; i += kThreads) g_mma_trace[i / 12][i % 12] = s.prof_trace[i / 12][i % 12];
   }
 #endif
   if (warp == 1) {
@@ -739,8 +782,8 @@ int launch_match_jobs_mma(vslam_ctx* ctx, const MatchJob* jobs_dev, int n_jobs, 
 }
 
 #ifdef VSLAM_MMA_PROFILE
-extern "C" int vslam_debug_mma_trace(long long* out3072) {
-  return cudaMemcpyFromSymbol(out3072, g_mma_trace, sizeof(long long) * 3072) == cudaSuccess ? 0 : -1;
+extern "C" int vslam_debug_mma_trace(long long* out1536) {
+  return cudaMemcpyFromSymbol(out1536, g_mma_trace, sizeof(long long) * 1536) == cudaSuccess ? 0 : -1;
 }
 extern "C" int vslam_debug_mma_clocks(long long* out32, int reset) {
   if (cudaMemcpyFromSymbol(out32, g_mma_clk, sizeof(long long) * 32) != cudaSuccess) return -1;
