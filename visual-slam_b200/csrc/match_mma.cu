@@ -514,7 +514,10 @@ __global__ void __launch_bounds__(kThreads, 1)
             const uint32_t bias_lo = 0;
 #endif
             // my turn (true long before it is needed once the pipeline runs), then the stage: what follows the stage's
-            // release is on the critical path of the pair (release -> first MMA), so nothing else is left for there
+            // release is on the critical path of the pair (release -> first MMA), so nothing else is left for there.
+            // (Handing the two halves of a stage over separately -- D1's MMAs as soon as the D1 warps have read columns
+            // 0-127, D2's release waited for between the halves -- measured slower, 1.40 against 1.33 ms: the wait in the
+            // middle of a pair stalls the issuer longer than the earlier start gains.)
             if (t == 1 || seq1 > 0) ok = spin_until_ge(other, (t ? kMmasPerPair * seq0 : kMmasPerPair * (seq1 - 1)) + kHandoff, fail) && ok;
             if (leader) MMA_TRACE(2 * t_it + t, 5);
             { MMA_T0(); if (t_it >= 1) ok = mbar_wait(&s.t_empty[t], (t_it - 1) & 1, fail) && ok; MMA_ACC(3); }
