@@ -4,5 +4,5 @@ T=$1
 mkdir -p gpurun_out
 CMD="python bench.py --no-cpu-baseline --no-extras --steps 1 --warmup 3 --e2e-steps 1"
 timeout 300 $CMD > gpurun_out/${T}_plain.log 2>&1 &&
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'response_kernel|orient_describe|select_kernel|match_mma' -s 12 -c 4 -o gpurun_out/${T}_step $CMD > gpurun_out/${T}_ncu.log 2>&1
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'response_kernel|response_multi|orient_describe|select_kernel|match_mma' -s 15 -c 5 -o gpurun_out/${T}_step $CMD > gpurun_out/${T}_ncu.log 2>&1
 tail -3 gpurun_out/${T}_ncu.log; ls -la gpurun_out/${T}_step.ncu-rep

@@ -2,7 +2,7 @@
 """Summarise ncu outputs brought back in gpurun_out/ into small text files for profiles/.
   ncu_summary.py launches <launches.csv>            per-kernel launch count, total time, share
   ncu_summary.py raw <report.ncu-rep> [metric ...]  selected raw metrics of every captured launch
-  ncu_summary.py traffic <report.ncu-rep> <kernel-regex> <units-per-launch> <source-file> <out.json>
+  ncu_summary.py traffic <report.ncu-rep> <kernel-regex> <units-per-launch> <source-file> <out.json> [also-kernel-regex]
         dram__bytes_read/write of the captured launch of that kernel, per unit, with the sha256 of the kernel's source
         file: bench.py reads the JSON and marks the roofline's traffic stale when the source has changed since
 """
@@ -54,7 +54,7 @@ def raw(path, metrics):
                 print("%-70s %-14s %s" % (m, U[H.index(m)], r[H.index(m)]))
 
 
-def traffic(path, pattern, units, source, out_json):
+def traffic(path, pattern, units, source, out_json, also=None):
     import hashlib, json, os, re
     out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
@@ -69,6 +69,16 @@ def traffic(path, pattern, units, source, out_json):
         v, u = float(best[H.index(m)].replace(",", "")), rows[1][H.index(m)]
         return v * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[u]
     rd, wr = val("dram__bytes_read.sum"), val("dram__bytes_write.sum")
+    extra = None
+    if also:  # a second kernel that shares the launch's work (response_multi_kernel: the narrow strips): its bytes count too
+        for r in rows[2:]:
+            if re.search(also, r[H.index("Kernel Name")]):
+                extra = r
+        if extra is not None:
+            def val2(m):
+                return float(extra[H.index(m)].replace(",", "")) * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[rows[1][H.index(m)]]
+            rd += val2("dram__bytes_read.sum")
+            wr += val2("dram__bytes_write.sum")
     def opt(m):
         try:
             return float(best[H.index(m)].replace(",", ""))
@@ -85,6 +95,7 @@ def traffic(path, pattern, units, source, out_json):
            "dram_bytes_read": rd, "dram_bytes_write": wr, "dram_bytes_per_unit": (rd + wr) / int(units),
            "gpu_time_us": float(best[H.index("gpu__time_duration.sum")].replace(",", "")) *
                           {"ns": 1e-3, "us": 1.0, "ms": 1e3}.get(rows[1][H.index("gpu__time_duration.sum")], 1.0),
+           "also": None if extra is None else extra[H.index("Kernel Name")].split("(")[0],
            "source": source, "source_sha256": hashlib.sha256(open(source, "rb").read()).hexdigest()}
     json.dump(rec, open(out_json, "w"), indent=1)
     print(json.dumps(rec))
@@ -94,6 +105,6 @@ if __name__ == "__main__":
     if sys.argv[1] == "launches":
         launches(sys.argv[2])
     elif sys.argv[1] == "traffic":
-        traffic(*sys.argv[2:7])
+        traffic(*sys.argv[2:8])
     else:
         raw(sys.argv[2], sys.argv[3:] or DEFAULT)
