@@ -73,8 +73,9 @@ typedef struct vslam_desc_store vslam_desc_store;
                              one-pair-at-a-time use of slam.cpp:1125-1143) replay their kernel sequence as one CUDA graph
                              from the third call with the same arguments on; 0: plain launches.  Results identical. */
 #define VSLAM_OPT_RESPONSE_MULTI 9 /* 1 (default): when the last 120-column strip of the image is at most 56 columns wide
-                                    * (752 = 6 x 120 + 32), batched launches give that strip of two or three consecutive
-                                    * images to ONE warp instead of one mostly idle warp per image; 0: one warp per strip.
+                                    * (752 = 6 x 120 + 32), launches of at least two waves of warps give that strip of two or
+                                    * three consecutive images to ONE warp instead of one mostly idle warp per image; 0: one
+                                    * warp per strip; 2: shared strips for any launch of two images or more (tests).
                                     * Results are identical (tests/test_gpu_detect_describe.py). */
 
 /* ---- context ------------------------------------------------------------------------ */

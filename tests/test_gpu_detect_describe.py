@@ -121,7 +121,7 @@ def test_narrow_last_strip_shared_by_images(ctx, oracle_port, w, h):
         ctx.set_option(VSLAM_OPT_RESPONSE_BAND, band)
         try:
             for count in (2, 3, 4, 7):
-                ctx.set_option(VSLAM_OPT_RESPONSE_MULTI, 1)
+                ctx.set_option(VSLAM_OPT_RESPONSE_MULTI, 2)
                 a_xy, _, a_desc, a_n = ctx.detect_describe_batch(imgs[:count], 400)
                 ctx.set_option(VSLAM_OPT_RESPONSE_MULTI, 0)
                 b_xy, _, b_desc, b_n = ctx.detect_describe_batch(imgs[:count], 400)

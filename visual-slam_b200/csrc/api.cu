@@ -136,7 +136,7 @@ int vslam_set_option(vslam_ctx* ctx, int option, int value) {
   else if (option == VSLAM_OPT_MATCH_SPLIT_SMALL) ctx->match_split_small = value != 0;
   else if (option == VSLAM_OPT_MATCH_MMA && value >= 0 && value <= 2) ctx->match_mma = value;
   else if (option == VSLAM_OPT_GRAPH) ctx->use_graph = value != 0;
-  else if (option == VSLAM_OPT_RESPONSE_MULTI) ctx->resp_multi = value != 0;
+  else if (option == VSLAM_OPT_RESPONSE_MULTI && value >= 0 && value <= 2) ctx->resp_multi = value;
   else if (option == VSLAM_OPT_RESPONSE_BAND && (value == 0 || (value >= 8 && value <= 65535))) ctx->resp_band = value;
   else if (option == VSLAM_OPT_BATCH_CHUNK && value >= 1 && value <= 4096) ctx->batch_chunk = value;
   else if (option == VSLAM_OPT_BATCH_DEPTH && value >= 1 && value <= vslam_ctx::kMaxBatchDepth) ctx->batch_depth = value;

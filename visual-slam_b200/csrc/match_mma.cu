@@ -42,7 +42,12 @@ constexpr int kTile = 128;                 // descriptors per operand tile = UMM
 constexpr int kHalfBytes = kTile * 128;    // one K half of a tile: [128 rows][128 B]
 constexpr int kTileBytes = 2 * kHalfBytes; // 32 KB
 constexpr int kGroup = 2;                  // desc1 tiles resident per pass over desc2
-constexpr int kBStages = 3;                // ring of desc2 tiles
+// ring of desc2 tiles: a tile serves two pairs (~2400 cycles), so two stages cover the TMA latency -- three measured the
+// same (1.334 / 1.339 ms) and their 32 KB are what lets sets of 4000 descriptors (config 5) keep their statistics here
+#ifndef VSLAM_MMA_BSTAGES
+#define VSLAM_MMA_BSTAGES 2
+#endif
+constexpr int kBStages = VSLAM_MMA_BSTAGES;
 constexpr int kEpiWarps = 16;              // two groups of 8: group g takes the tile pairs of TMEM stage g
 constexpr int kEpiGroupWarps = 8;
 constexpr int kMmaWarps = 2;               // one MMA-issuing warp per TMEM stage (see the kernel's header)
@@ -371,9 +376,14 @@ __global__ void __launch_bounds__(kThreads, 1)
     match_mma_kernel(const __grid_constant__ CUtensorMap tmap1, const __grid_constant__ CUtensorMap tmap2, const MmaParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   MmaSmem& s = *reinterpret_cast<MmaSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint2* rs = reinterpret_cast<uint2*>(&s + 1);  // [max_n1] row statistics T(d1[i], desc2)
-  uint2* cs = rs + p.max_n1;                     // [2][max_n2] column statistics T(d2[j], desc1), one copy per epilogue
-                                                 // group (both groups meet every desc2 tile); merged at the end
+  // Running statistics of the job, 6 bytes per row: the best key (distance << 20 | index) and the second-best DISTANCE
+  // (its index is never needed).  rk / rd: [max_n1] rows T(d1[i], desc2); ck / cd: [2][max_n2] columns T(d2[j], desc1),
+  // one copy per epilogue group (both groups meet every desc2 tile), merged at the end.
+  const int n1pad = (p.max_n1 + 1) & ~1, n2pad = (p.max_n2 + 1) & ~1;
+  uint32_t* rk = reinterpret_cast<uint32_t*>(&s + 1);
+  uint32_t* ck = rk + n1pad;
+  uint16_t* rd = reinterpret_cast<uint16_t*>(ck + 2 * n2pad);
+  uint16_t* cd = rd + n1pad;
   // (broadcast: ptxas then knows the warp index -- and everything derived from it -- is uniform over the warp)
   const int warp = __shfl_sync(0xFFFFFFFFu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
 
@@ -573,9 +583,8 @@ __global__ void __launch_bounds__(kThreads, 1)
       const int ew = warp - kCtlWarps;           // 0..15
       const int et = threadIdx.x - kCtlWarps * 32;  // 0..511
       const int g = ew >> 3;
-      uint2* csg = cs + (size_t)g * p.max_n2;
-      for (int i = et; i < n1; i += kEpiWarps * 32) rs[i] = make_uint2(kSent, kSent);
-      for (int j = et; j < n2; j += kEpiWarps * 32) cs[j] = cs[p.max_n2 + j] = make_uint2(kSent, kSent);
+      for (int i = et; i < n1; i += kEpiWarps * 32) { rk[i] = kSent; rd[i] = 256; }
+      for (int j = et; j < n2; j += kEpiWarps * 32) { ck[j] = ck[n2pad + j] = kSent; cd[j] = cd[n2pad + j] = 256; }
       epi_barrier();
       const bool d2 = (ew & 4) != 0;
       const int q = ew & 3;  // = warp % 4: the TMEM lane quarter this warp may read
@@ -606,13 +615,11 @@ __global__ void __launch_bounds__(kThreads, 1)
             fold_tile(tmem + ((uint32_t)(q * 32) << 16) + t * 256 + (d2 ? kTile : 0), nvalid, p.key_mul, p.key_one, p.key_neg1,
                       &s.t_empty[t], lane, k1, k2, lc);
             if (row < nrows) {
-              uint2* sp = (d2 ? csg : rs) + row;
-              uint2 acc = *sp;
-              const uint32_t w1 = widen_key(k1, cbase), w2 = widen_key(k2, cbase);
-              const uint32_t hi = max(acc.x, w1);
-              acc.x = min(acc.x, w1);
-              acc.y = min(min(acc.y, w2), hi);
-              *sp = acc;
+              uint32_t* kp = (d2 ? ck + g * n2pad : rk) + row;
+              uint16_t* dp = (d2 ? cd + g * n2pad : rd) + row;
+              const uint32_t old = *kp, w1 = widen_key(k1, cbase);
+              *kp = min(old, w1);
+              *dp = (uint16_t)min(min((uint32_t)*dp, k2 >> 7), max(old, w1) >> kShift);  // (k2 >> 7: the tile's second distance)
             }
           } else {  // nothing to read from this stage: release it at once
             tc_fence_before();
@@ -627,8 +634,9 @@ __global__ void __launch_bounds__(kThreads, 1)
       epi_barrier();
       // one list of column statistics out of the two groups' (the associative merge of the scan)
       for (int j = et; j < n2; j += kEpiWarps * 32) {
-        const uint2 a = cs[j], c = cs[p.max_n2 + j];
-        cs[j] = make_uint2(min(a.x, c.x), min(max(a.x, c.x), min(a.y, c.y)));
+        const uint32_t a = ck[j], c = ck[n2pad + j];
+        ck[j] = min(a, c);
+        cd[j] = (uint16_t)min(max(a, c) >> kShift, (uint32_t)min(cd[j], cd[n2pad + j]));
       }
       epi_barrier();
       MMA_T0();
@@ -638,8 +646,9 @@ __global__ void __launch_bounds__(kThreads, 1)
         // "never matched" sentinel with an impossible index so that the host-visible result is empty, and the global flag
         uint2* rp = p.rowpart + (size_t)jb * p.split_n1;
         uint2* cp = p.colstat + (size_t)jb * p.split_range;
-        for (int i = et; i < n1; i += kEpiWarps * 32) rp[i] = good ? rs[i] : make_uint2(kSent, kSent);
-        for (int j = et; j < n2; j += kEpiWarps * 32) cp[j] = good ? cs[j] : make_uint2(kSent, kSent);
+        // (match.cu's merge / finalize kernels read the second entry as a key: the distance goes to its distance field)
+        for (int i = et; i < n1; i += kEpiWarps * 32) rp[i] = good ? make_uint2(rk[i], (uint32_t)rd[i] << kShift) : make_uint2(kSent, kSent);
+        for (int j = et; j < n2; j += kEpiWarps * 32) cp[j] = good ? make_uint2(ck[j], (uint32_t)cd[j] << kShift) : make_uint2(kSent, kSent);
       } else
       // ---- ratio test both ways, mutual check, compaction in ascending row order (as match_fused_kernel) ----
       if (good) {
@@ -648,11 +657,11 @@ __global__ void __launch_bounds__(kThreads, 1)
           bool hit = false;
           int j = 0;
           if (i < n1) {
-            const uint2 R = rs[i];
-            if (passes(R.x >> kShift, R.y >> kShift, p.threshold, p.ratio)) {
-              j = R.x & kIdxMask;
-              const uint2 C = cs[j];
-              hit = passes(C.x >> kShift, C.y >> kShift, p.threshold, p.ratio) && (int)(C.x & kIdxMask) == i;
+            const uint32_t R = rk[i];
+            if (passes(R >> kShift, rd[i], p.threshold, p.ratio)) {
+              j = R & kIdxMask;
+              const uint32_t C = ck[j];
+              hit = passes(C >> kShift, cd[j], p.threshold, p.ratio) && (int)(C & kIdxMask) == i;
             }
           }
           const unsigned bal = __ballot_sync(0xFFFFFFFFu, hit);
@@ -734,7 +743,7 @@ int make_desc_tmap(vslam_ctx* ctx, const uint8_t* expanded, long long rows, CUte
 }  // namespace
 
 size_t match_mma_smem_bytes(int max_n1, int max_n2) {
-  return sizeof(MmaSmem) + 1024 + (size_t)(max_n1 + 2 * max_n2) * sizeof(uint2);
+  return sizeof(MmaSmem) + 1024 + (size_t)(((max_n1 + 1) & ~1) + 2 * ((max_n2 + 1) & ~1)) * 6;
 }
 
 bool match_mma_fits(int max_n1, int max_n2) {
