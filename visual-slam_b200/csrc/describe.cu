@@ -267,7 +267,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, VSLAM_DESC_CTAS) orient_des
       rotate_pair<kContract>(ci, si, pat[k], xar, yar, xbr, ybr);
       const int axa = round_fix20(xar), aya = round_fix20(yar), axb = round_fix20(xbr), ayb = round_fix20(ybr);
       const int xai = axa >> 20, yai = aya >> 20, xbi = axb >> 20, ybi = ayb >> 20;
-      fmin = min(fmin, min(min(axa - (xai << 20), aya - (yai << 20)), min(axb - (xbi << 20), ayb - (ybi << 20))));
+      // (a - (a >> 20 << 20) = a & 0xFFFFF: one LOP per coordinate, the minima as three-input VIMNMX3)
+      fmin = __vimin3_s32(__vimin3_s32(fmin, axa & 0xFFFFF, aya & 0xFFFFF), axb & 0xFFFFF, ayb & 0xFFFFF);
       const int va = centre[yai * kPatchPitch + xai], vb = centre[ybi * kPatchPitch + xbi];
       const uint32_t word = __ballot_sync(0xFFFFFFFFu, va < vb);
       if (lane == k) my_word = word;
