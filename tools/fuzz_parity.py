@@ -7,14 +7,14 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 import oracle, visnav_b200
 from visnav_b200 import workloads as wl
-from visnav_b200.keypoints import DescStore, VSLAM_OPT_RESPONSE_BAND, VSLAM_OPT_MATCH_MMA
+from visnav_b200.keypoints import DescStore, VSLAM_OPT_RESPONSE_BAND, VSLAM_OPT_MATCH_MMA, VSLAM_OPT_RESPONSE_MULTI
 
 budget = float(os.environ.get("FUZZ_SECONDS", "60"))
 seed = int(os.environ.get("FUZZ_SEED", "1"))
 rng = np.random.default_rng(seed)
 ctx = visnav_b200.Context(0)
 o = oracle.load_oracle()
-stats = dict(seed=seed, images=0, corners=0, descriptors=0, match_calls=0, batch_jobs=0, failures=[])
+stats = dict(seed=seed, images=0, corners=0, descriptors=0, match_calls=0, batch_jobs=0, batched_images=0, failures=[])
 t_end = time.time() + budget
 it = 0
 while time.time() < t_end and len(stats["failures"]) < 5:
@@ -46,6 +46,26 @@ while time.time() < t_end and len(stats["failures"]) < 5:
     stats["images"] += 1; stats["corners"] += len(wxy); stats["descriptors"] += len(wdesc)
     if not ok:
         stats["failures"].append(dict(what="detect_describe", w=w, h=h, kind=kind, nf=nf, got=len(xy), want=len(wxy)))
+    if it % 3 == 0:
+        # batched detection of a few images of this size: the narrow last column strip of two or three images in one
+        # warp (forced for any count), or one warp per strip, against the single-image oracle results
+        cnt = int(rng.integers(2, 6))
+        batch = np.stack([img] + [np.roll(img, int(rng.integers(1, 40)), axis=int(rng.integers(0, 2))) for _ in range(cnt - 1)])
+        ctx.set_option(VSLAM_OPT_RESPONSE_MULTI, 2 if (it // 3) % 2 == 0 else 0)
+        try:
+            bxy, bang, bdesc, bn = ctx.detect_describe_batch(batch, max(nf, 1), True)
+            for k in range(cnt):
+                kxy, kang, kdesc = o.detect_describe(batch[k], max(nf, 1))
+                n = int(bn[k])
+                stats["batched_images"] += 1
+                if n != len(kxy) or not np.array_equal(bxy[k, :n], kxy) or not np.array_equal(bdesc[k, :n], kdesc) or \
+                        (n and np.abs(bang[k, :n] - kang).max() > 1e-5):
+                    stats["failures"].append(dict(what="detect_describe_batch", w=w, h=h, kind=kind, nf=nf, k=k, count=cnt, got=n, want=len(kxy)))
+        except Exception as e:
+            if "overflow" not in str(e):
+                raise
+        finally:
+            ctx.set_option(VSLAM_OPT_RESPONSE_MULTI, 1)
     # matching: random sizes, correlated sets, random threshold / ratio
     n1, n2 = int(rng.integers(0, 2200)), int(rng.integers(0, 2200))
     base = wl.random_descriptors(max(n1, n2, 1), int(rng.integers(0, 1 << 30)))
