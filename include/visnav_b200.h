@@ -77,6 +77,11 @@ typedef struct vslam_desc_store vslam_desc_store;
                                     * three consecutive images to ONE warp instead of one mostly idle warp per image; 0: one
                                     * warp per strip; 2: shared strips for any launch of two images or more (tests).
                                     * Results are identical (tests/test_gpu_detect_describe.py). */
+#define VSLAM_OPT_TWO_STREAMS 10 /* 1 (default): vslam_stereo_plan_run / vslam_stereo_batch chunks of at least four pairs per SM
+                                  * run as two halves on two streams (forked from and joined to the call's stream), so that the
+                                  * last wave of one half's kernel overlaps the other half's next kernel; 0: one stream,
+                                  * whole-batch launches (the per-stage times of vslam_stereo_plan_last_ms then describe
+                                  * kernels that run alone).  Results identical. */
 
 /* ---- context ------------------------------------------------------------------------ */
 int vslam_create(int device, vslam_ctx** out);

@@ -8,7 +8,7 @@ import pytest
 import visnav_b200
 from visnav_b200 import workloads as wl
 from visnav_b200.keypoints import (KeypointsData, VSLAM_OPT_FP_CONTRACT, VSLAM_OPT_RESPONSE_BAND,
-                                   VSLAM_OPT_RESPONSE_MULTI)
+                                   VSLAM_OPT_RESPONSE_MULTI, VSLAM_OPT_TWO_STREAMS, StereoPlan)
 
 pytestmark = pytest.mark.gpu
 
@@ -338,3 +338,38 @@ def test_stereo_batch_single_pair_graph_replay(ctx, oracle_port):
             check(ctx.stereo_batch(pairs[2:3], 1500, True, 70, 1.2), 2, 2)
         finally:
             ctx.set_option(VSLAM_OPT_GRAPH, 1)
+
+
+def test_stereo_plan_two_streams_equal_one_stream(ctx, oracle_port):
+    """Large resident batches run as two halves on two streams (vslam_stereo_plan_run, VSLAM_OPT_TWO_STREAMS): every
+    output equal to the one-stream run, for an odd pair count (halves of 296 and 297 pairs), and equal to the oracle on
+    a pair of each half."""
+    n = 593
+    base = wl.synth_stereo_batch(12, 320, 240, workers=1)
+    imgs = np.ascontiguousarray(base[np.arange(n) % 12])
+    plan = StereoPlan(ctx, 320, 240, n, 600)
+    try:
+        plan.upload(imgs)
+        outs = []
+        for two in (1, 0, 1):
+            ctx.set_option(VSLAM_OPT_TWO_STREAMS, two)
+            plan.run(n, 600, True, 70, 1.2)
+            outs.append(plan.download(n))
+        a, b, c = outs
+        for key in ("n_kp", "n_matches"):
+            assert np.array_equal(a[key], b[key]) and np.array_equal(a[key], c[key]), key
+        for k in range(n):
+            m = a["n_matches"][k]
+            assert np.array_equal(a["matches"][k, :m], b["matches"][k, :m])
+            for side in (2 * k, 2 * k + 1):
+                q = a["n_kp"][side]
+                assert np.array_equal(a["xy"][side, :q], b["xy"][side, :q]) and np.array_equal(a["desc"][side, :q], b["desc"][side, :q])
+                assert np.array_equal(a["angles"][side, :q], b["angles"][side, :q])
+        for k in (5, 400):
+            dl, dr = [oracle_port.detect_describe(imgs[k, s], 600) for s in (0, 1)]
+            assert np.array_equal(a["xy"][2 * k, :a["n_kp"][2 * k]], dl[0]) and np.array_equal(a["desc"][2 * k + 1, :a["n_kp"][2 * k + 1]], dr[2])
+            m = a["n_matches"][k]
+            assert np.array_equal(a["matches"][k, :m], oracle_port.match(dl[2], dr[2], 70, 1.2))
+    finally:
+        ctx.set_option(VSLAM_OPT_TWO_STREAMS, 1)
+        plan.close()

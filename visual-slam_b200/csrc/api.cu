@@ -136,6 +136,7 @@ int vslam_set_option(vslam_ctx* ctx, int option, int value) {
   else if (option == VSLAM_OPT_MATCH_SPLIT_SMALL) ctx->match_split_small = value != 0;
   else if (option == VSLAM_OPT_MATCH_MMA && value >= 0 && value <= 2) ctx->match_mma = value;
   else if (option == VSLAM_OPT_GRAPH) ctx->use_graph = value != 0;
+  else if (option == VSLAM_OPT_TWO_STREAMS) ctx->two_streams = value != 0;
   else if (option == VSLAM_OPT_RESPONSE_MULTI && value >= 0 && value <= 2) ctx->resp_multi = value;
   else if (option == VSLAM_OPT_RESPONSE_BAND && (value == 0 || (value >= 8 && value <= 65535))) ctx->resp_band = value;
   else if (option == VSLAM_OPT_BATCH_CHUNK && value >= 1 && value <= 4096) ctx->batch_chunk = value;
@@ -546,6 +547,8 @@ struct vslam_stereo_plan {
   DetectWorkspace ws{};
   cudaEvent_t ev[6] = {};
   cudaStream_t stream = nullptr;  // null: ctx stream
+  cudaStream_t stream2 = nullptr;  // second half of a large batch (vslam_stereo_plan_run), forked / joined with the events
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool timed = false;
 };
 
@@ -563,6 +566,9 @@ void vslam_stereo_plan_destroy(vslam_stereo_plan* plan) {
     if (plan->ev[i]) cudaEventDestroy(plan->ev[i]);
   if (plan->graph_exec) cudaGraphExecDestroy(plan->graph_exec);
   if (plan->stream) cudaStreamDestroy(plan->stream);
+  if (plan->stream2) cudaStreamDestroy(plan->stream2);
+  if (plan->ev_fork) cudaEventDestroy(plan->ev_fork);
+  if (plan->ev_join) cudaEventDestroy(plan->ev_join);
   delete plan;
 }
 
@@ -696,46 +702,98 @@ int vslam_stereo_plan_run(vslam_stereo_plan* plan, int count, int num_features, 
     plan->graph_state = 3;
     return vslam_stereo_plan_run(plan, count, num_features, rotate, match_threshold, match_dist_2_best);
   }
-#define PLAN_EVENT(i) do { if (!capture) cudaEventRecord(plan->ev[i], ctx->stream); } while (0)
-  const int nimg = 2 * count;
+  const cudaStream_t s0 = ctx->stream;  // the plan's stream (ctx->stream is pointed at the half's stream launch by launch)
+#define PLAN_EVENT(i) do { if (!capture) cudaEventRecord(plan->ev[i], s0); } while (0)
   int rc = VSLAM_OK;
-  PLAN_EVENT(0);
-  if (plan->w < 2 * kEdgeThreshold + 1 || plan->h < 2 * kEdgeThreshold + 1) {
-    cudaMemsetAsync(plan->nkp.p, 0, (size_t)nimg * 4, ctx->stream);
-    PLAN_EVENT(1);
-    PLAN_EVENT(2);
-  } else {
-    rc = launch_response(ctx, plan->im, nimg, plan->ws, nullptr);
-    PLAN_EVENT(1);
-    if (!rc)
-      rc = launch_select(ctx, plan->im, nimg, plan->ws, num_features, kQuality, kMinDistance, kEdgeThreshold,
-                         plan->xy.as<double>(), plan->nkp.as<int32_t>(), plan->cap);
-    PLAN_EVENT(2);
-  }
   // enough jobs to fill the GPU with one CTA per SM: Hamming matrix on the tensor cores (the describe kernel then also
   // writes every descriptor as 256 signed bytes, the matcher's operand format); else the POPC kernels, whose
   // column-split path spreads a few jobs over all SMs
   const bool mma = (ctx->match_mma == 2 || (ctx->match_mma && 2 * count >= ctx->num_sms)) && match_mma_fits(plan->cap, plan->cap);
-  if (!rc && mma && !plan->descx.p) {  // first tensor-core run of this plan (no early return: ctx->stream is swapped)
+  if (mma && !plan->descx.p) {  // first tensor-core run of this plan (no early return: ctx->stream is swapped)
     if (plan->descx.reserve((size_t)2 * plan->max_pairs * plan->cap * 256) != cudaSuccess ||
         cudaMemsetAsync(plan->descx.p, 0, plan->descx.bytes, ctx->stream) != cudaSuccess)
       rc = vs_fail(ctx, VSLAM_E_CUDA, "plan: cannot allocate the signed-byte descriptor slab");
   }
-  if (!rc)
-    rc = launch_orient_describe(ctx, plan->im, nimg, plan->xy.as<double>(), plan->nkp.as<int32_t>(), plan->cap,
-                                rotate ? 1 : 0, plan->ang.as<double>(), plan->desc.as<uint32_t>(),
-                                mma ? plan->descx.as<uint8_t>() : nullptr);
+  // Large resident batches run as TWO halves on two streams, their launches issued stage by stage in turn: every kernel
+  // here fills the registers or the shared memory of an SM by itself, so kernels never share an SM, but the last wave of
+  // one half's kernel leaves SMs idle that the other half's next kernel takes (measured with two plans on two streams:
+  // +5.3 % pairs/s at 2000 pairs).  The halves only share read-only tables; the second stream is forked from and joined
+  // to the plan's stream with events, so the call keeps its stream semantics.  VSLAM_OPT_TWO_STREAMS = 0: one stream,
+  // whole-batch launches (what the per-stage times of vslam_stereo_plan_last_ms describe without overlap).
+  const bool two = ctx->two_streams && !capture && !plan->epi_on && count >= 4 * ctx->num_sms && !rc;
+  if (two && !plan->stream2) {
+    if (cudaStreamCreateWithFlags(&plan->stream2, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&plan->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&plan->ev_join, cudaEventDisableTiming) != cudaSuccess)
+      rc = vs_fail(ctx, VSLAM_E_CUDA, "plan: cannot create the second stream");
+  }
+  const int nhalf = two ? 2 : 1;
+  const int first_pair[2] = {0, two ? count / 2 : 0};
+  const int npairs[2] = {two ? count / 2 : count, count - count / 2};
+  cudaStream_t hs[2] = {s0, plan->stream2};
+  const bool tiny = plan->w < 2 * kEdgeThreshold + 1 || plan->h < 2 * kEdgeThreshold + 1;
+  PLAN_EVENT(0);
+  if (two && !rc) {
+    cudaEventRecord(plan->ev_fork, hs[0]);
+    cudaStreamWaitEvent(hs[1], plan->ev_fork, 0);
+  }
+  auto sub_ws = [&](int img0) {
+    DetectWorkspace w = plan->ws;
+    w.cand += (size_t)img0 * w.cand_cap;
+    w.cand_cnt += img0;
+    w.img_max += img0;
+    w.sel_ws += (size_t)img0 * w.sel_ws_stride;
+    return w;
+  };
+  auto sub_im = [&](int img0) {
+    DevImages im = plan->im;
+    im.base += (size_t)img0 * im.stride;
+    return im;
+  };
+  const size_t cap = plan->cap;
+  // stage 1: response
+  for (int hf = 0; hf < nhalf && !rc; ++hf) {
+    ctx->stream = hs[hf];
+    const int img0 = 2 * first_pair[hf], n = 2 * npairs[hf];
+    if (tiny) cudaMemsetAsync(plan->nkp.as<int32_t>() + img0, 0, (size_t)n * 4, ctx->stream);
+    else rc = launch_response(ctx, sub_im(img0), n, sub_ws(img0), nullptr);
+  }
+  PLAN_EVENT(1);
+  // stage 2: select
+  for (int hf = 0; hf < nhalf && !rc && !tiny; ++hf) {
+    ctx->stream = hs[hf];
+    const int img0 = 2 * first_pair[hf], n = 2 * npairs[hf];
+    rc = launch_select(ctx, sub_im(img0), n, sub_ws(img0), num_features, kQuality, kMinDistance, kEdgeThreshold,
+                       plan->xy.as<double>() + (size_t)img0 * cap * 2, plan->nkp.as<int32_t>() + img0, plan->cap);
+  }
+  PLAN_EVENT(2);
+  // stage 3: orientation + descriptors
+  for (int hf = 0; hf < nhalf && !rc; ++hf) {
+    ctx->stream = hs[hf];
+    const int img0 = 2 * first_pair[hf], n = 2 * npairs[hf];
+    rc = launch_orient_describe(ctx, sub_im(img0), n, plan->xy.as<double>() + (size_t)img0 * cap * 2,
+                                plan->nkp.as<int32_t>() + img0, plan->cap, rotate ? 1 : 0,
+                                plan->ang.as<double>() + (size_t)img0 * cap, plan->desc.as<uint32_t>() + (size_t)img0 * cap * 8,
+                                mma ? plan->descx.as<uint8_t>() + (size_t)img0 * cap * 256 : nullptr);
+  }
   PLAN_EVENT(3);
-  if (!rc) {
+  // stage 4: stereo matching
+  for (int hf = 0; hf < nhalf && !rc; ++hf) {
+    ctx->stream = hs[hf];
+    const MatchJob* jobs = plan->jobs.as<MatchJob>() + first_pair[hf];
     if (mma) {
-      const long long rows = (long long)nimg * plan->cap;
+      const long long rows = (long long)2 * count * plan->cap;
       const MatchExpanded x = {plan->desc.as<uint32_t>(), plan->descx.as<uint8_t>(), rows};
-      rc = launch_match_jobs_mma(ctx, plan->jobs.as<MatchJob>(), count, plan->cap, plan->cap, match_threshold,
-                                 match_dist_2_best, plan->cap, x, x);
+      rc = launch_match_jobs_mma(ctx, jobs, npairs[hf], plan->cap, plan->cap, match_threshold, match_dist_2_best, plan->cap, x, x);
     } else {
-      rc = launch_match_jobs(ctx, plan->jobs.as<MatchJob>(), count, plan->cap, plan->cap, match_threshold,
-                             match_dist_2_best, plan->cap, &plan->mrow, &plan->mcol);
+      rc = launch_match_jobs(ctx, jobs, npairs[hf], plan->cap, plan->cap, match_threshold, match_dist_2_best, plan->cap,
+                             &plan->mrow, &plan->mcol);
     }
+  }
+  ctx->stream = hs[0];
+  if (two) {  // (also after an error: the second stream must not be left forked)
+    cudaEventRecord(plan->ev_join, hs[1]);
+    cudaStreamWaitEvent(hs[0], plan->ev_join, 0);
   }
   PLAN_EVENT(4);
   if (!rc && plan->epi_on) {

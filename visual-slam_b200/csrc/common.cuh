@@ -54,6 +54,7 @@ struct vslam_ctx {
   int harris_on = 0;       // goodFeaturesToTrack(useHarrisDetector): the reference passes false (keypoints.h:139)
   double harris_k = 0.04;  // cv::goodFeaturesToTrack's default k
   int resp_band = 0;  // response kernel: forced box height (0 = chosen per launch)
+  int two_streams = 1; // stereo plans: large batches as two halves on two streams (VSLAM_OPT_TWO_STREAMS)
   int resp_multi = 1; // response kernel: a narrow last column strip of 2-3 images per warp (VSLAM_OPT_RESPONSE_MULTI)
   int match_split_small = 1;  // batches with fewer jobs than SMs/2: split every job's columns over CTAs
   int use_graph = 1;          // small pipeline plans of vslam_stereo_batch replay their launches as one CUDA graph

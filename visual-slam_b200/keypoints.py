@@ -54,6 +54,7 @@ VSLAM_OPT_RESPONSE_BAND = 6
 VSLAM_OPT_MATCH_MMA = 7
 VSLAM_OPT_GRAPH = 8
 VSLAM_OPT_RESPONSE_MULTI = 9
+VSLAM_OPT_TWO_STREAMS = 10
 
 
 class VslamError(RuntimeError):
