@@ -402,7 +402,9 @@ def run_ours(args):
                                "repeated), detect+describe both images (1500 features) + stereo match (70, 1.2)"
                                % (n_pairs, n_distinct),
                    "pairs_per_gpu": n_pairs, "l2": "inputs (1.47 GB per step) larger than L2, no flush needed",
-                   "sharding": "pairs split by rank, no collective on the data path"},
+                   "sharding": "pairs split by rank, no collective on the data path",
+                   "streams": "each step = one vslam_stereo_plan_run call; the library runs the resident batch as two "
+                              "half-batches on two streams (VSLAM_OPT_TWO_STREAMS, default)"},
         "stage_ms": {"response": stage_ms[1], "select": stage_ms[2], "describe": stage_ms[3], "match": stage_ms[4],
                      "serial_step": stage_ms[0],
                      "note": "whole-batch launches on ONE stream, measured right after the timed region; the timed steps run "
