@@ -720,7 +720,8 @@ int vslam_stereo_plan_run(vslam_stereo_plan* plan, int count, int num_features, 
   // +5.3 % pairs/s at 2000 pairs).  The halves only share read-only tables; the second stream is forked from and joined
   // to the plan's stream with events, so the call keeps its stream semantics.  VSLAM_OPT_TWO_STREAMS = 0: one stream,
   // whole-batch launches (what the per-stage times of vslam_stereo_plan_last_ms describe without overlap).
-  const bool two = ctx->two_streams && !capture && !plan->epi_on && count >= 4 * ctx->num_sms && !rc;
+  // (tensor-core matcher only: the POPC matcher's column-split scratch belongs to the plan, not to a half)
+  const bool two = ctx->two_streams && !capture && !plan->epi_on && mma && count >= 4 * ctx->num_sms && !rc;
   if (two && !plan->stream2) {
     if (cudaStreamCreateWithFlags(&plan->stream2, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&plan->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
