@@ -396,6 +396,7 @@ def run_ours(args):
     achieved = RESP_BYTES_PER_IMAGE * 2 * n_pairs / (resp_ms * 1e-3) / 1e9
     resp_traffic, resp_tinfo = kernel_traffic("response")
     desc_traffic, desc_tinfo = kernel_traffic("describe")
+    match_traffic, match_tinfo = kernel_traffic("match")
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": t_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -451,6 +452,8 @@ def run_ours(args):
                               # bias step that keeps the accumulators non-negative, match_mma.cu VSLAM_MMA_BIAS)
                               "frac_executed": 2 * 1.125 * ops / INT8_TOPS_MEASURED,
                               "distances_per_s": n_dist / (match_ms * 1e-3), "ms_per_launch": match_ms,
+                              # DRAM bytes and pipe utilisation of the captured launch (tensor pipe busy % is the one to read)
+                              "traffic": None if match_traffic is None else match_traffic * n_pairs, **match_tinfo,
                               "distances_per_launch": n_dist,
                               "popc_equivalent": {"unit": "popc.b32/s", "algorithmic_8_per_distance": 8.0 * n_dist / (match_ms * 1e-3),
                                                   "popc_peak_measured": popc_peak,
