@@ -61,9 +61,14 @@ typedef struct vslam_desc_store vslam_desc_store;
                                         spreads every job's columns over all SMs (latency of a single stereo
                                         pair); 0: always one CTA per job.  Results identical. */
 
-#define VSLAM_OPT_RESPONSE_BAND 6 /* output rows per box of the corner-response kernel.  0 (default): chosen per launch
-                                    (the whole image height when the batch fills the SMs, else bands of <= 64 rows);
-                                    >= 8: forced.  Results identical. */
+#define VSLAM_OPT_RESPONSE_BAND 6 /* output rows per box of the corner-response kernel.  0 (default): the whole image
+                                    height -- a warp walks whole columns and carries OpenCV's running column sum
+                                    (box_filter.simd.hpp:206-262): every bit of the response as cv::goodFeaturesToTrack
+                                    computes it.  1: row bands chosen per launch for latency (<= 64 rows for a single
+                                    image); >= 8: bands of that height.  Bands sum the three rows of the box directly: the
+                                    response then differs from OpenCV's in the last bits of a few pixels per million
+                                    (where a double addition was inexact), which can swap two corners of equal strength
+                                    (DESIGN.md section 2). */
 #define VSLAM_OPT_MATCH_MMA 7 /* 1 (default): batches of matching jobs that fill the GPU (stereo plans / vslam_stereo_batch
                                  chunks, vslam_match_batch) compute the Hamming matrix on the tensor cores (tcgen05.mma
                                  kind::i8 on descriptors expanded to signed bytes: dot = 256 - 2 * hamming, exact);

@@ -68,6 +68,14 @@ void vso_set_harris(int on, double k) { g_harris_on = on; g_harris_k = k; }
 /* 0 (default): OCV's running column sum; 1: direct three-row sum (see the column pass in vso_response). */
 static int g_box_direct = 0;
 void vso_set_box_direct(int on) { g_box_direct = on; }
+/* Probe for the row-banded evaluation: with band > 0, vso_response counts the (column, channel) pairs at rows y = band,
+ * 2 band, ... whose running SUM differs from the two-term sum R(y-1) + R(y) a band that starts there would seed it with
+ * (a rounding residue of an inexact addition further up the column).  Zero for an image = a banded evaluation that carries
+ * the running sum inside each band reproduces OCV bit for bit. */
+static int g_residue_band = 0;
+static long long g_residue_count = 0;
+void vso_residue_probe(int band) { g_residue_band = band; g_residue_count = 0; }
+long long vso_residue_count(void) { return g_residue_count; }
 
 int vso_response(const uint8_t* img, int w, int h, int pitch, float* lam) {
   if (!img || !lam || w <= 0 || h <= 0 || pitch < w) return -1;
@@ -147,6 +155,11 @@ int vso_response(const uint8_t* img, int w, int h, int pitch, float* lam) {
           v = v + rs[((size_t)yp * w + x) * 3 + k];
           abc[k] = (float)v;
         } else {
+          if (g_residue_band > 0 && y > 0 && y % g_residue_band == 0) {
+            double two = rs[((size_t)ym * w + x) * 3 + k];
+            two = two + rs[((size_t)y * w + x) * 3 + k];
+            if (two != SUM[(size_t)x * 3 + k]) g_residue_count++;
+          }
           double s0 = SUM[(size_t)x * 3 + k] + rs[((size_t)yp * w + x) * 3 + k];
           abc[k] = (float)s0;
           SUM[(size_t)x * 3 + k] = s0 - rs[((size_t)ym * w + x) * 3 + k];

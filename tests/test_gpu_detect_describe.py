@@ -22,17 +22,19 @@ def _image(w, h, seed):
 
 
 # The 3x3 box filter behind the response: OpenCV keeps a RUNNING column sum in double (box_filter.simd.hpp:206-262).
-# A warp that walks a whole image column reproduces it bit for bit (boxes as tall as the image: what batches that fill
-# the GPU use, and VSLAM_OPT_RESPONSE_BAND >= h forces).  Row-banded launches (single images: latency) sum the three rows
-# directly; the two differ only where a double addition was inexact.  Stated tolerance of the banded mode against
-# OpenCV's order: at most MAX_DIFF_PER_MPX pixels per million differ, each by at most MAX_DIFF_ULP float ulps, every one
-# of them below the candidate threshold (0.01 x the image maximum), and the corner list is identical.
+# A warp that walks a whole image column reproduces it bit for bit (boxes as tall as the image: the default).  Row-banded
+# launches (VSLAM_OPT_RESPONSE_BAND = 1 or >= 8: an opt-in for latency) sum the three rows directly; the two differ only
+# where a double addition was inexact.  Stated tolerance of the banded mode against OpenCV's order on these images: at
+# most MAX_DIFF_PER_MPX pixels per million differ, each by at most MAX_DIFF_ULP float ulps, below the candidate threshold
+# (0.01 x the image maximum), and the corner list is identical.  (In general a differing pixel can lie above the
+# threshold and swap two corners of equal strength -- tools/fuzz_parity.py found one such image in 19 000 -- which is
+# why bands are not the default.)
 MAX_DIFF_PER_MPX = 16
 MAX_DIFF_ULP = 16
 
 
 def _default_band_is_full_height(h):
-    return h <= 64       # single image: the host picks bands of <= 64 rows (detect.cu band_rows)
+    return True          # boxes span the image height unless VSLAM_OPT_RESPONSE_BAND asks for bands
 
 
 def _check_response(oracle_port, img, got, full_height):
@@ -88,15 +90,15 @@ def test_response_running_sum_matters(ctx, oracle_port):
     n_diff = 0
     for seed in range(4):
         img = _image(1920, 1080, 300 + seed)
-        n_diff += _check_response(oracle_port, img, ctx.response(img), False)
         want_xy = oracle_port.detect(img, 4000)
-        assert np.array_equal(ctx.detect(img, 4000), want_xy)
-        ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 65535)
+        ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 1)      # bands chosen by the host (latency mode)
         try:
-            _check_response(oracle_port, img, ctx.response(img), True)
+            n_diff += _check_response(oracle_port, img, ctx.response(img), False)
             assert np.array_equal(ctx.detect(img, 4000), want_xy)
         finally:
-            ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 0)
+            ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 0)  # default: full-height boxes
+        _check_response(oracle_port, img, ctx.response(img), True)
+        assert np.array_equal(ctx.detect(img, 4000), want_xy)
     assert n_diff > 0, "direct and running box sums never differed on this set: the test images no longer probe it"
 
 
@@ -117,7 +119,7 @@ def test_narrow_last_strip_shared_by_images(ctx, oracle_port, w, h):
     group count, in row bands and in full-height boxes, and equal to the oracle's."""
     imgs = np.stack([_image(w, h, 4000 + 13 * k + w) for k in range(7)])
     want = [oracle_port.detect(im, 400) for im in imgs]
-    for band in (0, 65535):
+    for band in (1, 0):      # bands chosen by the host (opt-in latency mode), full-height boxes (default)
         ctx.set_option(VSLAM_OPT_RESPONSE_BAND, band)
         try:
             for count in (2, 3, 4, 7):

@@ -116,7 +116,7 @@ def main():
         # response MAP vs cv2.cornerMinEigenVal (scalar dispatch) pixel by pixel, in both kernel modes: OpenCV's box
         # filter keeps a RUNNING column sum in double (ColumnSum<double, float>); where an addition is inexact its
         # rounding residue travels down the column.  Full-height boxes (what launches that fill the GPU use) restate it
-        # and must differ nowhere; row-banded launches (the default for a single image) sum the three rows directly.
+        # and must differ nowhere; row-banded launches (VSLAM_OPT_RESPONSE_BAND = 1: the opt-in latency mode) sum the three rows directly.
         from visnav_b200.keypoints import VSLAM_OPT_RESPONSE_BAND
         rm = []
         for (w, h, seed) in [(752, 480, 1234), (1920, 1080, 77), (1920, 1080, 302), (320, 240, 5)]:
@@ -127,7 +127,7 @@ def main():
             thr = float(want.max()) * 0.01
             rec = dict(size="%dx%d" % (w, h), seed=seed, pixels=w * h,
                        oracle_differing=int((o.response(img).view(np.uint32) != want.view(np.uint32)).sum()))
-            for mode, band in (("full_height", 65535), ("banded_default", 0)):
+            for mode, band in (("full_height_default", 0), ("banded_opt_in", 1)):
                 ctx.set_option(VSLAM_OPT_RESPONSE_BAND, band)
                 got = ctx.response(img)
                 ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 0)

@@ -6,6 +6,9 @@ import numpy as np, visnav_b200
 from visnav_b200 import workloads as wl
 from visnav_b200.keypoints import StereoPlan
 ctx = visnav_b200.Context(0)
+if os.environ.get("RESPONSE_BAND"):      # e.g. 65535: full-height boxes (OpenCV's running column sum, bit-exact)
+    from visnav_b200.keypoints import VSLAM_OPT_RESPONSE_BAND
+    ctx.set_option(VSLAM_OPT_RESPONSE_BAND, int(os.environ["RESPONSE_BAND"]))
 pl, pr = wl.synth_stereo_pair(0)
 one = np.ascontiguousarray(np.stack([pl, pr])[None])
 plan = StereoPlan(ctx, 752, 480, 1, 1500)

@@ -31,7 +31,12 @@ int prepare_detect_ws(vslam_ctx* ctx, int w, int h, int count, DevBuf& cand, Dev
   VS_CUDA(ctx, cand.reserve((size_t)count * ccap * sizeof(uint64_t)));
   VS_CUDA(ctx, candcnt.reserve((size_t)count * sizeof(uint32_t)));
   VS_CUDA(ctx, imgmax.reserve((size_t)count * sizeof(uint32_t)));
-  VS_CUDA(ctx, selws.reserve((size_t)count * wsb));
+  // behind the select workspace: the planes of the small-count response path (13 floats per pixel and image)
+  const int nsmall = count < kRespSmallMaxImages ? count : kRespSmallMaxImages;
+  const size_t sel_bytes = ((size_t)count * wsb + 255) & ~(size_t)255;
+  VS_CUDA(ctx, selws.reserve(sel_bytes + (size_t)nsmall * (((size_t)w * h + 1) & ~(size_t)1) * 13 * sizeof(float)));
+  ws->small_ws = reinterpret_cast<float*>(selws.as<uint8_t>() + sel_bytes);
+  ws->small_images = nsmall;
   ws->cand = cand.as<uint64_t>();
   ws->cand_cnt = candcnt.as<uint32_t>();
   ws->img_max = imgmax.as<uint32_t>();
@@ -138,7 +143,7 @@ int vslam_set_option(vslam_ctx* ctx, int option, int value) {
   else if (option == VSLAM_OPT_GRAPH) ctx->use_graph = value != 0;
   else if (option == VSLAM_OPT_TWO_STREAMS) ctx->two_streams = value != 0;
   else if (option == VSLAM_OPT_RESPONSE_MULTI && value >= 0 && value <= 2) ctx->resp_multi = value;
-  else if (option == VSLAM_OPT_RESPONSE_BAND && (value == 0 || (value >= 8 && value <= 65535))) ctx->resp_band = value;
+  else if (option == VSLAM_OPT_RESPONSE_BAND && (value == 0 || value == 1 || (value >= 8 && value <= 65535))) ctx->resp_band = value;
   else if (option == VSLAM_OPT_BATCH_CHUNK && value >= 1 && value <= 4096) ctx->batch_chunk = value;
   else if (option == VSLAM_OPT_BATCH_DEPTH && value >= 1 && value <= vslam_ctx::kMaxBatchDepth) ctx->batch_depth = value;
   else return vs_fail(ctx, VSLAM_E_ARG, "unknown option");

@@ -118,7 +118,12 @@ struct DetectWorkspace {
   int cand_cap;
   uint8_t* sel_ws;     // global fallback workspace for select, [count][sel_ws_stride]
   size_t sel_ws_stride;
+  // response of a FEW images (launch_response, detect.cu "small-count path"): per image cov [3][h][w] f32, row sums
+  // [3][h][w] f64, box sums [3][h][w] f32, response [h][w] f32; room for small_images images (0: none)
+  float* small_ws;
+  int small_images;
 };
+constexpr int kRespSmallMaxImages = 16;  // up to this many images per launch take the small-count path
 size_t detect_sel_ws_bytes(int w, int h, int cand_cap, int cell);
 // 3-D TMA tensor map {w, h, count} over an image set with a box of box_w x box_h x 1 bytes
 int make_image_tmap(vslam_ctx* ctx, const DevImages& im, int count, int box_w, int box_h, CUtensorMap* tmap);
