@@ -53,7 +53,7 @@ typedef struct vslam_desc_store vslam_desc_store;
                                    multiplies + add (reference built with -ffp-contract=off) */
 #define VSLAM_OPT_MATCH_CSA 2   /* 1 (default): Hamming kernel folds words with carry-save adders
                                    before POPC; 0: one POPC per 32-bit word.  Results identical. */
-#define VSLAM_OPT_BATCH_CHUNK 3 /* stereo pairs per pipeline chunk of vslam_stereo_batch (default 96) */
+#define VSLAM_OPT_BATCH_CHUNK 3 /* stereo pairs per pipeline chunk of vslam_stereo_batch (default 120) */
 #define VSLAM_OPT_BATCH_DEPTH 4 /* chunks in flight in vslam_stereo_batch, 1..4 (default 4): upload,
                                    compute and download of consecutive chunks overlap */
 

@@ -81,7 +81,7 @@ struct vslam_ctx {
   // pipeline plans of vslam_stereo_batch, kept between calls (same geometry -> no reallocation)
   static constexpr int kMaxBatchDepth = 4;
   struct vslam_stereo_plan* batch_plans[kMaxBatchDepth] = {nullptr, nullptr, nullptr, nullptr};
-  int batch_chunk = 96;   // stereo pairs per pipeline chunk (VSLAM_OPT_BATCH_CHUNK)
+  int batch_chunk = 120;  // stereo pairs per pipeline chunk (VSLAM_OPT_BATCH_CHUNK): 240 images x 7 strips = one wave of full-height boxes
   int batch_depth = 4;    // chunks in flight: upload / compute / download overlap (VSLAM_OPT_BATCH_DEPTH)
 };
 
