@@ -125,3 +125,27 @@ def test_response_large_fixture(ctx):
             assert np.array_equal(ctx.detect(img, nf), want), key
         finally:
             ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 0)
+
+
+def test_equal_strength_corners_keep_opencv_order(ctx, oracle_port):
+    """The image the fuzz sweep found (tools/fuzz_parity.py, seed 23, iteration 6026; 379 x 626, quantised content): two
+    corners of bit-equal strength, which cv::goodFeaturesToTrack orders by address (featureselect.cpp:55-60).  With row
+    bands a last-bit difference of the directly summed box filter swapped them; the default paths (the small-count path
+    for one image, full-height boxes for a batch) carry OpenCV's running column sum and keep the order."""
+    import os
+    from visnav_b200.keypoints import VSLAM_OPT_RESPONSE_BAND
+    d = np.load(os.path.join(os.path.dirname(__file__), "golden", "tie_order_case.npz"))
+    img, nf = np.ascontiguousarray(d["img"]), int(d["nf"])
+    want = oracle_port.detect(img, nf)
+    assert np.array_equal(ctx.detect(img, nf), want)                                    # one image: small-count path
+    xy, _, _, n = ctx.detect_describe_batch(np.stack([img] * 20), nf)                   # 20 images: full-height boxes
+    for k in (0, 19):
+        assert n[k] == len(want) and np.array_equal(xy[k, :n[k]], want)
+    ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 65535)                                      # the streaming kernel on one image
+    try:
+        assert np.array_equal(ctx.detect(img, nf), want)
+        ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 1)                                      # bands: same corners, order may differ
+        got = ctx.detect(img, nf)
+        assert len(got) == len(want) and set(map(tuple, got)) == set(map(tuple, want))
+    finally:
+        ctx.set_option(VSLAM_OPT_RESPONSE_BAND, 0)
