@@ -32,9 +32,13 @@ int prepare_detect_ws(vslam_ctx* ctx, int w, int h, int count, DevBuf& cand, Dev
   VS_CUDA(ctx, candcnt.reserve((size_t)count * sizeof(uint32_t)));
   VS_CUDA(ctx, imgmax.reserve((size_t)count * sizeof(uint32_t)));
   // behind the select workspace: the planes of the small-count response path (13 floats per pixel and image)
-  const int nsmall = count < kRespSmallMaxImages ? count : kRespSmallMaxImages;
+  // (at most 1 GiB of them: 16 images of 752 x 480, 9 of 1920 x 1080, 2 of 3840 x 2160; launches of more images than the
+  // planes hold use the streaming kernel)
+  const size_t small_per_image = (((size_t)w * h + 1) & ~(size_t)1) * 13 * sizeof(float);
+  int nsmall = count < kRespSmallMaxImages ? count : kRespSmallMaxImages;
+  if ((size_t)nsmall * small_per_image > ((size_t)1 << 30)) nsmall = (int)(((size_t)1 << 30) / small_per_image);
   const size_t sel_bytes = ((size_t)count * wsb + 255) & ~(size_t)255;
-  VS_CUDA(ctx, selws.reserve(sel_bytes + (size_t)nsmall * (((size_t)w * h + 1) & ~(size_t)1) * 13 * sizeof(float)));
+  VS_CUDA(ctx, selws.reserve(sel_bytes + (size_t)nsmall * small_per_image));
   ws->small_ws = reinterpret_cast<float*>(selws.as<uint8_t>() + sel_bytes);
   ws->small_images = nsmall;
   ws->cand = cand.as<uint64_t>();
