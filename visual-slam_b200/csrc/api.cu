@@ -31,10 +31,10 @@ int prepare_detect_ws(vslam_ctx* ctx, int w, int h, int count, DevBuf& cand, Dev
   VS_CUDA(ctx, cand.reserve((size_t)count * ccap * sizeof(uint64_t)));
   VS_CUDA(ctx, candcnt.reserve((size_t)count * sizeof(uint32_t)));
   VS_CUDA(ctx, imgmax.reserve((size_t)count * sizeof(uint32_t)));
-  // behind the select workspace: the planes of the small-count response path (13 floats per pixel and image)
+  // behind the select workspace: the planes of the small-count response path (10 floats per pixel and image)
   // (at most 1 GiB of them: 16 images of 752 x 480, 9 of 1920 x 1080, 2 of 3840 x 2160; launches of more images than the
   // planes hold use the streaming kernel)
-  const size_t small_per_image = (((size_t)w * h + 1) & ~(size_t)1) * 13 * sizeof(float);
+  const size_t small_per_image = (((size_t)w * h + 1) & ~(size_t)1) * 10 * sizeof(float);
   int nsmall = count < kRespSmallMaxImages ? count : kRespSmallMaxImages;
   if ((size_t)nsmall * small_per_image > ((size_t)1 << 30)) nsmall = (int)(((size_t)1 << 30) / small_per_image);
   const size_t sel_bytes = ((size_t)count * wsb + 255) & ~(size_t)255;

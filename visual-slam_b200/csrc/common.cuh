@@ -118,8 +118,8 @@ struct DetectWorkspace {
   int cand_cap;
   uint8_t* sel_ws;     // global fallback workspace for select, [count][sel_ws_stride]
   size_t sel_ws_stride;
-  // response of a FEW images (launch_response, detect.cu "small-count path"): per image cov [3][h][w] f32, row sums
-  // [3][h][w] f64, box sums [3][h][w] f32, response [h][w] f32; room for small_images images (0: none)
+  // response of a FEW images (launch_response, detect.cu "small-count path"): per image row sums [3][h][w] f64,
+  // box sums [3][h][w] f32, response [h][w] f32; room for small_images images (0: none)
   float* small_ws;
   int small_images;
 };
